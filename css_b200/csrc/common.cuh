@@ -1,0 +1,48 @@
+// Shared helpers for the css_b200 sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#define CSS_NBINS 257   // n_fft/2+1 for the 512-point STFT (conf/*.yaml frame_length 512)
+#define CSS_KP 264      // padded bin pitch (elements) of every "bin-fastest" array
+#define CSS_NFFT 512
+#define CSS_HOP 256
+
+// error plumbing (api.cu)
+void css_set_error(const char* fmt, ...);
+int css_check_launch(const char* what);
+
+#define CSS_REQUIRE(cond, ...)            \
+    do {                                  \
+        if (!(cond)) {                    \
+            css_set_error(__VA_ARGS__);   \
+            return -1;                    \
+        }                                 \
+    } while (0)
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+// a * conj(b)
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) {
+    return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
+}
+
+static inline int ceil_div(long a, long b) { return (int)((a + b - 1) / b); }

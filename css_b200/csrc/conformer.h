@@ -1,0 +1,27 @@
+// Internal launch interface of the Conformer / BLSTM building-block kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+
+int layernorm_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
+                     cudaStream_t st);
+int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
+                     cudaStream_t st);
+
+struct ConvModuleParams {
+    const float* ln_g;      // (d)
+    const float* ln_b;      // (d)
+    float pw1_w0, pw1_b0;   // pw_conv_1 channel 0 (value path)     -- scalar affine (Conv2d(1,2,1))
+    float pw1_w1, pw1_b1;   // pw_conv_1 channel 1 (gate path)
+    const float* dw_w;      // (d, ksize) depthwise taps
+    const float* dw_b;      // (d)
+    const float* bn_scale;  // (d) gamma / sqrt(running_var + eps)
+    const float* bn_shift;  // (d) beta - running_mean * scale
+    float pw2_w, pw2_b;     // pw_conv_2 scalar affine
+    int ksize;
+};
+// out = x + ConvModule(x).  x, out: (N, T, 256), out must not alias x.  ksize odd, <= 33.
+int conv_module_launch(const float* x, float* out, long N, int T, int d, const ConvModuleParams& p, cudaStream_t st);
+
+// (N*T, ldm) rows [c*nb + f] -> masks (N, nb, T, C)
+int masks_layout_launch(const float* m, int ldm, float* out, long N, int T, int nb, int C, cudaStream_t st);

@@ -1,0 +1,324 @@
+// Warp-level kernels of the Conformer block: LayerNorm, relative-position MHSA, conv module,
+// and the mask-head layout transform.  (css/models/conformer.py:188-303, css/executor/separator.py:100-104)
+#include "common.cuh"
+#include "conformer.h"
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm over d (multiple of 128, <= 1024): one warp per row.  Optional fused ReLU.
+// ---------------------------------------------------------------------------------------------
+template <int VPL>   // float4 vectors per lane: d = 128 * VPL
+__global__ void __launch_bounds__(256)
+layernorm_kernel(const float* x, const float* __restrict__ g, const float* __restrict__ b, float* y,
+                 long M, float eps, int relu) {
+    const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= M) return;
+    const int d = 128 * VPL;
+    const float4* xr = reinterpret_cast<const float4*>(x + row * d);
+    float4 v[VPL];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        v[i] = xr[lane + 32 * i];
+        s += v[i].x + v[i].y + v[i].z + v[i].w;
+    }
+    const float mean = warp_sum(s) / d;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        float a = v[i].x - mean, bb = v[i].y - mean, c = v[i].z - mean, dd = v[i].w - mean;
+        q += a * a + bb * bb + c * c + dd * dd;
+    }
+    const float rstd = rsqrtf(warp_sum(q) / d + eps);
+    float4* yr = reinterpret_cast<float4*>(y + row * d);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const float4 gg = reinterpret_cast<const float4*>(g)[lane + 32 * i];
+        const float4 bb = reinterpret_cast<const float4*>(b)[lane + 32 * i];
+        float4 o;
+        o.x = (v[i].x - mean) * rstd * gg.x + bb.x;
+        o.y = (v[i].y - mean) * rstd * gg.y + bb.y;
+        o.z = (v[i].z - mean) * rstd * gg.z + bb.z;
+        o.w = (v[i].w - mean) * rstd * gg.w + bb.w;
+        if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+        yr[lane + 32 * i] = o;
+    }
+}
+
+int layernorm_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
+                     cudaStream_t st) {
+    CSS_REQUIRE(M > 0, "layernorm: empty input");
+    CSS_REQUIRE(d % 128 == 0 && d <= 1024, "layernorm: d=%d must be a multiple of 128 and <= 1024", d);
+    const unsigned grid = (unsigned)((M + 7) / 8);
+    switch (d / 128) {
+        case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
+        case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
+        case 4: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
+        case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
+        default: CSS_REQUIRE(false, "layernorm: unsupported d=%d", d);
+    }
+    return css_check_launch("layernorm");
+}
+
+extern "C" int css_layernorm(const float* x, const float* g, const float* b, float* y, long M, int d, float eps,
+                             int relu, cudaStream_t st) {
+    return layernorm_launch(x, g, b, y, M, d, eps, relu, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Relative-position multi-head self-attention core (css/models/conformer.py:229-250):
+//   scores[i][j] = q_i . (k_j + pe[i - j + maxlen]) / sqrt(dk) ; softmax_j ; out_i = sum_j p_ij v_j
+// One CTA per (sequence, head).  dk = 64.  K and the needed 2T-1 rows of the embedding table are
+// kept transposed in shared memory so that lanes (over j) read conflict-free.
+// qkv: (N*T, 3*H*64) rows = [q | k | v], out: (N*T, H*64).
+// ---------------------------------------------------------------------------------------------
+#define ATT_DK 64
+#define ATT_WARPS 8
+
+__global__ void __launch_bounds__(ATT_WARPS * 32)
+relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ pe, int pe_rows, int use_pe,
+                        float* __restrict__ out, int T, int H) {
+    extern __shared__ float sm[];
+    const int TP = (T + 31) & ~31;             // padded j extent
+    const int RP = 2 * TP;                     // padded relative extent
+    float* Kt = sm;                            // [64][TP]
+    float* Vs = Kt + ATT_DK * TP;              // [T][64]
+    float* Pt = Vs + T * ATT_DK;               // [64][RP]   Pt[d][r] = pe[clamp(r - (T-1)) + maxlen][d]
+    float* Pb = Pt + ATT_DK * RP;              // [warps][TP] probabilities
+    float* Qb = Pb + ATT_WARPS * TP;           // [warps][64]
+    const int n = blockIdx.x / H, h = blockIdx.x % H;
+    const int ld = 3 * H * ATT_DK;
+    const float* base = qkv + (long)n * T * ld;
+    const int maxlen = pe_rows / 2;
+    for (int i = threadIdx.x; i < T * ATT_DK; i += blockDim.x) {
+        const int j = i >> 6, d = i & 63;
+        Kt[d * TP + j] = base[(long)j * ld + (H + h) * ATT_DK + d];
+        Vs[j * ATT_DK + d] = base[(long)j * ld + (2 * H + h) * ATT_DK + d];
+    }
+    for (int i = threadIdx.x; i < ATT_DK * (TP - T); i += blockDim.x) {
+        const int d = i / (TP - T), j = T + i % (TP - T);
+        Kt[d * TP + j] = 0.f;
+    }
+    for (int i = threadIdx.x; i < RP * ATT_DK; i += blockDim.x) {
+        const int r = i >> 6, d = i & 63;
+        float v = 0.f;
+        if (use_pe && r <= 2 * (T - 1)) {
+            int rel = r - (T - 1);
+            rel = max(-maxlen, min(maxlen - 1, rel)) + maxlen;
+            v = pe[(long)rel * ATT_DK + d];
+        }
+        Pt[d * RP + r] = v;
+    }
+    __syncthreads();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float* pb = Pb + warp * TP;
+    float* qb = Qb + warp * ATT_DK;
+    const int NJ = TP / 32;
+    for (int i = warp; i < T; i += ATT_WARPS) {
+        const float* qrow = base + (long)i * ld + h * ATT_DK;
+        qb[lane] = qrow[lane];
+        qb[lane + 32] = qrow[lane + 32];
+        __syncwarp();
+        float s[8];
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj) s[jj] = 0.f;
+        for (int d = 0; d < ATT_DK; ++d) {
+            const float qd = qb[d];
+            const float* kr = Kt + d * TP + lane;
+            const float* pr = Pt + d * RP + (i + T - 1) - lane;    // r = i - j + T - 1
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj)
+                if (jj < NJ) {
+                    const int r = (i + T - 1) - lane - 32 * jj;
+                    const float pv = (r >= 0) ? pr[-32 * jj] : 0.f;
+                    s[jj] = fmaf(qd, kr[32 * jj] + pv, s[jj]);
+                }
+        }
+        float mx = -INFINITY;
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj)
+            if (jj < NJ) {
+                s[jj] = (lane + 32 * jj < T) ? s[jj] * 0.125f : -INFINITY;
+                mx = fmaxf(mx, s[jj]);
+            }
+        mx = warp_max(mx);
+        float sum = 0.f;
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj)
+            if (jj < NJ) {
+                s[jj] = (lane + 32 * jj < T) ? expf(s[jj] - mx) : 0.f;
+                sum += s[jj];
+            }
+        const float inv = 1.f / warp_sum(sum);
+#pragma unroll
+        for (int jj = 0; jj < 8; ++jj)
+            if (jj < NJ) pb[lane + 32 * jj] = s[jj] * inv;
+        __syncwarp();
+        float o0 = 0.f, o1 = 0.f;
+        for (int j = 0; j < T; ++j) {
+            const float p = pb[j];
+            o0 = fmaf(p, Vs[j * ATT_DK + lane], o0);
+            o1 = fmaf(p, Vs[j * ATT_DK + lane + 32], o1);
+        }
+        float* orow = out + ((long)n * T + i) * (H * ATT_DK) + h * ATT_DK;
+        orow[lane] = o0;
+        orow[lane + 32] = o1;
+        __syncwarp();
+    }
+}
+
+size_t attention_smem_bytes(int T) {
+    const int TP = (T + 31) & ~31;
+    return sizeof(float) * ((size_t)ATT_DK * TP + (size_t)T * ATT_DK + (size_t)ATT_DK * 2 * TP + ATT_WARPS * TP +
+                            ATT_WARPS * ATT_DK);
+}
+
+int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
+                     cudaStream_t st) {
+    CSS_REQUIRE(dk == ATT_DK, "attention: head dim %d unsupported (kernel is built for 64)", dk);
+    CSS_REQUIRE(N > 0 && T > 0 && T <= 256, "attention: T=%d out of range (1..256)", T);
+    const size_t smem = attention_smem_bytes(T);
+    CSS_REQUIRE(smem <= 227 * 1024, "attention: T=%d needs %zu B of shared memory", T, smem);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(relpos_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        attr_set = true;
+    }
+    relpos_attention_kernel<<<(unsigned)(N * H), ATT_WARPS * 32, smem, st>>>(qkv, pe, pe_rows, pe != nullptr, out, T, H);
+    return css_check_launch("relpos_attention");
+}
+
+extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H,
+                                    int dk, cudaStream_t st) {
+    return attention_launch(qkv, pe, pe_rows, out, N, T, H, dk, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Conv module (css/models/conformer.py:289-303), fully fused:
+//   LN -> scalar GLU (a*sigmoid(g), both scalar affines of the LN output) -> depthwise conv over
+//   time (k taps, zero padded) -> BatchNorm (folded running stats) -> ReLU -> scalar affine -> + x.
+// One CTA per (sequence, time tile); the gated activations of the tile plus a 16-row halo on each
+// side live in shared memory; thread c then slides the taps of channel c down the time axis.
+// ---------------------------------------------------------------------------------------------
+#define CM_D 256
+#define CM_TT 160
+#define CM_HALO 16
+#define CM_TAPS (2 * CM_HALO + 1)
+
+__global__ void __launch_bounds__(CM_D)
+conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, ConvModuleParams p) {
+    extern __shared__ float U[];   // [(CM_TT + 2*CM_HALO)][CM_D]
+    const long n = blockIdx.x;
+    const int t0 = blockIdx.y * CM_TT;
+    const int tile = min(CM_TT, T - t0);
+    const int rows = tile + 2 * CM_HALO;
+    const float* xs = x + n * (long)T * CM_D;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // phase 1: LN + gate, one warp per row
+    for (int r = warp; r < rows; r += CM_D / 32) {
+        const int t = t0 - CM_HALO + r;
+        float4* urow = reinterpret_cast<float4*>(U + r * CM_D);
+        if (t < 0 || t >= T) {
+            urow[lane] = make_float4(0, 0, 0, 0);
+            urow[lane + 32] = make_float4(0, 0, 0, 0);
+            continue;
+        }
+        const float4* xr = reinterpret_cast<const float4*>(xs + (long)t * CM_D);
+        float4 v[2] = {xr[lane], xr[lane + 32]};
+        float s = v[0].x + v[0].y + v[0].z + v[0].w + v[1].x + v[1].y + v[1].z + v[1].w;
+        const float mean = warp_sum(s) / CM_D;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+            q += a * a + b * b + c * c + d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(q) / CM_D + 1e-5f);
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            const float4 g = reinterpret_cast<const float4*>(p.ln_g)[lane + 32 * i];
+            const float4 b = reinterpret_cast<const float4*>(p.ln_b)[lane + 32 * i];
+            float y[4] = {(v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
+                          (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const float a = y[e] * p.pw1_w0 + p.pw1_b0;
+                const float gt = y[e] * p.pw1_w1 + p.pw1_b1;
+                y[e] = a / (1.f + expf(-gt));
+            }
+            urow[lane + 32 * i] = make_float4(y[0], y[1], y[2], y[3]);
+        }
+    }
+    __syncthreads();
+    // phase 2: depthwise taps of channel c
+    const int c = threadIdx.x;
+    float w[CM_TAPS];
+#pragma unroll
+    for (int k = 0; k < CM_TAPS; ++k) w[k] = p.dw_w[c * CM_TAPS + k];
+    const float bias = p.dw_b[c], sc = p.bn_scale[c], sh = p.bn_shift[c];
+    float* os = out + n * (long)T * CM_D;
+    for (int tt = 0; tt < tile; ++tt) {
+        float acc = bias;
+#pragma unroll
+        for (int k = 0; k < CM_TAPS; ++k) acc = fmaf(w[k], U[(tt + k) * CM_D + c], acc);
+        float v = fmaxf(acc * sc + sh, 0.f) * p.pw2_w + p.pw2_b;
+        const long idx = (long)(t0 + tt) * CM_D + c;
+        os[idx] = xs[idx] + v;
+    }
+}
+
+int conv_module_launch(const float* x, float* out, long N, int T, int d, const ConvModuleParams& p, cudaStream_t st) {
+    CSS_REQUIRE(d == CM_D, "conv_module: d=%d unsupported (kernel is built for 256)", d);
+    CSS_REQUIRE(p.ksize == CM_TAPS, "conv_module: taps must be centre-padded to %d (got %d)", CM_TAPS, p.ksize);
+    CSS_REQUIRE(N > 0 && T > 0 && x != out, "conv_module: bad arguments");
+    const size_t smem = sizeof(float) * (size_t)(CM_TT + 2 * CM_HALO) * CM_D;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        attr_set = true;
+    }
+    dim3 grid((unsigned)N, (T + CM_TT - 1) / CM_TT);
+    conv_module_kernel<<<grid, CM_D, smem, st>>>(x, out, T, p);
+    return css_check_launch("conv_module");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Mask head layout: m[(n*T + t)][c*nb + f]  ->  masks[n][f][t][c]   (css/executor/separator.py:100-104)
+// 32x32 (t, f) tiles through shared memory; reads coalesced along f, writes coalesced along (t, c).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+masks_layout_kernel(const float* __restrict__ m, int ldm, float* __restrict__ out, int T, int nb, int C) {
+    __shared__ float tile[4][32][33];
+    const long n = blockIdx.z;
+    const int f0 = blockIdx.x * 32, t0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 8 rows per pass
+    for (int c = 0; c < C; ++c)
+        for (int r = ty; r < 32; r += 8) {
+            const int t = t0 + r, f = f0 + tx;
+            tile[c][r][tx] = (t < T && f < nb) ? m[(n * T + t) * (long)ldm + c * nb + f] : 0.f;
+        }
+    __syncthreads();
+    // out row (n, f) is T*C contiguous floats; write the [t0, t0+32) x C slab of 32 f rows
+    const int span = 32 * C;
+    for (int r = ty; r < 32; r += 8) {
+        const int f = f0 + r;
+        if (f >= nb) continue;
+        float* orow = out + ((n * nb + f) * (long)T + t0) * C;
+        for (int e = tx; e < span; e += 32) {
+            const int tt = e / C, c = e - tt * C;
+            if (t0 + tt < T) orow[e] = tile[c][tt][r];
+        }
+    }
+}
+
+int masks_layout_launch(const float* m, int ldm, float* out, long N, int T, int nb, int C, cudaStream_t st) {
+    CSS_REQUIRE(C >= 1 && C <= 4, "masks_layout: %d outputs unsupported (max 4)", C);
+    CSS_REQUIRE(N > 0 && N <= 65535, "masks_layout: N=%ld out of range", N);
+    dim3 grid((nb + 31) / 32, (T + 31) / 32, (unsigned)N);
+    masks_layout_kernel<<<grid, 256, 0, st>>>(m, ldm, out, T, nb, C);
+    return css_check_launch("masks_layout");
+}
+
+extern "C" int css_masks_layout(const float* m, int ldm, float* out, long N, int T, int nb, int C, cudaStream_t st) {
+    return masks_layout_launch(m, ldm, out, N, T, nb, C, st);
+}

@@ -1,0 +1,142 @@
+// K2: fused spectral + spatial features (css/executor/feature.py:105-134,156-175) and the
+// model-side input MVN over time (css/models/conformer.py:95, css/models/blstm.py:80).
+#include "common.cuh"
+
+#define FEAT_EPS 1.1920928955078125e-07f
+#define FEAT_THREADS 288   // 9 warps cover 257 bins
+#define FEAT_TT 32         // time tile of the transposing mag store
+
+// unit phasor of a * conj(b); atan2(0,0) = 0 convention -> (1, 0) when a product vanishes
+__device__ __forceinline__ float2 unit_cross(float2 a, float2 b) {
+    float2 p = cmulc(a, b);
+    float n = sqrtf(p.x * p.x + p.y * p.y);
+    if (n == 0.f) {
+        // phase(a) - phase(b) with the zero operand's phase taken as 0
+        float na = sqrtf(a.x * a.x + a.y * a.y), nb = sqrtf(b.x * b.x + b.y * b.y);
+        if (na == 0.f && nb == 0.f) return make_float2(1.f, 0.f);
+        if (na == 0.f) return make_float2(b.x / nb, -b.y / nb);
+        if (nb == 0.f) return make_float2(a.x / na, a.y / na);
+        // underflow of the product: normalise first
+        a.x /= na; a.y /= na; b.x /= nb; b.y /= nb;
+        return cmulc(a, b);
+    }
+    return make_float2(p.x / n, p.y / n);
+}
+
+// One block per chunk; thread k owns bin k.  spec element (d, chunk b, frame t, bin k) lives at
+// spec[(d*stride_d + b*stride_chunk + t) * CSS_KP + k].
+__global__ void __launch_bounds__(FEAT_THREADS)
+features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T,
+                const int* __restrict__ ipd_l, const int* __restrict__ ipd_r, int n_pairs,
+                float* __restrict__ mag, float* __restrict__ feat, int ldf) {
+    __shared__ float tile[FEAT_TT][CSS_NBINS + 1];
+    const long b = blockIdx.x;
+    const int k = threadIdx.x;
+    const bool act = k < CSS_NBINS;
+    const float2* base = spec + (b * stride_chunk) * CSS_KP + k;
+
+    // ---- pass 1: statistics over time ----
+    float m_sum = 0.f;
+    float cs[8], sn[8];
+#pragma unroll
+    for (int p = 0; p < 8; ++p) cs[p] = sn[p] = 0.f;
+    if (act) {
+        for (int t = 0; t < T; ++t) {
+            float2 x0 = base[(long)t * CSS_KP];
+            m_sum += fmaxf(sqrtf(x0.x * x0.x + x0.y * x0.y), FEAT_EPS);
+#pragma unroll
+            for (int p = 0; p < 8; ++p)
+                if (p < n_pairs) {
+                    float2 xl = base[((long)ipd_l[p] * stride_d + t) * CSS_KP];
+                    float2 xr = base[((long)ipd_r[p] * stride_d + t) * CSS_KP];
+                    float2 u = unit_cross(xl, xr);
+                    cs[p] += u.x;
+                    sn[p] += u.y;
+                }
+        }
+    }
+    const float m_mean = m_sum / T;
+    float var = 0.f;
+    if (act)
+        for (int t = 0; t < T; ++t) {
+            float2 x0 = base[(long)t * CSS_KP];
+            float dlt = fmaxf(sqrtf(x0.x * x0.x + x0.y * x0.y), FEAT_EPS) - m_mean;
+            var += dlt * dlt;
+        }
+    const float inv = 1.f / (sqrtf(var / (T - 1)) + FEAT_EPS);
+#pragma unroll
+    for (int p = 0; p < 8; ++p) { cs[p] /= T; sn[p] /= T; }
+
+    // ---- pass 2: emit features (row-major (chunk, t) x feature) and transposed magnitude ----
+    float* frow = feat + (b * T) * (long)ldf;
+    float* mrow = mag + b * (long)CSS_NBINS * T;
+    for (int t0 = 0; t0 < T; t0 += FEAT_TT) {
+        const int tn = min(FEAT_TT, T - t0);
+        if (act)
+            for (int tt = 0; tt < tn; ++tt) {
+                const int t = t0 + tt;
+                float2 x0 = base[(long)t * CSS_KP];
+                float m = sqrtf(x0.x * x0.x + x0.y * x0.y);
+                tile[tt][k] = m;
+                float* fr = frow + (long)t * ldf;
+                fr[k] = (fmaxf(m, FEAT_EPS) - m_mean) * inv;
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < n_pairs) {
+                        float2 xl = base[((long)ipd_l[p] * stride_d + t) * CSS_KP];
+                        float2 xr = base[((long)ipd_r[p] * stride_d + t) * CSS_KP];
+                        float2 u = unit_cross(xl, xr);
+                        fr[(p + 1) * CSS_NBINS + k] = atan2f(u.y - sn[p], u.x - cs[p]);
+                    }
+            }
+        __syncthreads();
+        // mag[b][bin][t]: consecutive threads walk t inside a bin row
+        for (int i = threadIdx.x; i < CSS_NBINS * tn; i += blockDim.x) {
+            const int bin = i / tn, tt = i - bin * tn;
+            mrow[(long)bin * T + t0 + tt] = tile[tt][bin];
+        }
+        __syncthreads();
+    }
+    // zero the K padding of the feature rows
+    const int F = CSS_NBINS * (n_pairs + 1);
+    for (int i = threadIdx.x; i < T * (ldf - F); i += blockDim.x) {
+        const int t = i / (ldf - F), c = i - t * (ldf - F);
+        frow[(long)t * ldf + F + c] = 0.f;
+    }
+}
+
+// In-place MVN over time of x[n][t][0..F) (row pitch ld): (x - mean_T) / (std_T,unbiased + eps).
+__global__ void mvn_time_kernel(float* __restrict__ x, int T, int F, int ld) {
+    const long n = blockIdx.x;
+    const int f = blockIdx.y * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    float* col = x + n * (long)T * ld + f;
+    float s = 0.f;
+    for (int t = 0; t < T; ++t) s += col[(long)t * ld];
+    const float mean = s / T;
+    float v = 0.f;
+    for (int t = 0; t < T; ++t) {
+        float d = col[(long)t * ld] - mean;
+        v += d * d;
+    }
+    const float inv = 1.f / (sqrtf(v / (T - 1)) + FEAT_EPS);
+    for (int t = 0; t < T; ++t) col[(long)t * ld] = (col[(long)t * ld] - mean) * inv;
+}
+
+extern "C" int css_features(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T,
+                            const int* ipd_l, const int* ipd_r, int n_pairs, float* mag, float* feat, int ldf,
+                            cudaStream_t st) {
+    CSS_REQUIRE(n_chunks > 0 && T > 1, "css_features: empty input (chunks=%ld T=%d)", n_chunks, T);
+    CSS_REQUIRE(n_pairs >= 0 && n_pairs <= 8, "css_features: at most 8 IPD pairs supported, got %d", n_pairs);
+    CSS_REQUIRE(ldf >= CSS_NBINS * (n_pairs + 1), "css_features: feature pitch %d too small", ldf);
+    features_kernel<<<(unsigned)n_chunks, FEAT_THREADS, 0, st>>>((const float2*)spec, stride_d, stride_chunk, T, ipd_l,
+                                                                 ipd_r, n_pairs, mag, feat, ldf);
+    return css_check_launch("css_features");
+}
+
+extern "C" int css_mvn_time(float* x, long n, int T, int F, int ld, cudaStream_t st) {
+    CSS_REQUIRE(n > 0 && T > 1 && F > 0 && ld >= F, "css_mvn_time: bad shape");
+    dim3 grid((unsigned)n, (F + 127) / 128);
+    mvn_time_kernel<<<grid, 128, 0, st>>>(x, T, F, ld);
+    return css_check_launch("css_mvn_time");
+}

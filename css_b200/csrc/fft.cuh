@@ -1,0 +1,78 @@
+// Warp-level 512-point real FFT / inverse real FFT staged in shared memory.
+//
+// A 512-point real transform is done as one 256-point complex Stockham radix-4 FFT
+// (4 passes, ping-pong between two per-warp shared buffers) plus the even/odd split.
+// One warp owns one frame; every lane does two radix-4 butterflies per pass.
+#pragma once
+#include "common.cuh"
+
+struct FftTables {
+    float2 tw[512];   // tw[k] = exp(-2*pi*i*k/512)
+    float win[512];   // periodic Hann window (torch.hann_window(512))
+};
+
+__device__ __forceinline__ void fft_tables_init(FftTables* t) {
+    for (int k = threadIdx.x; k < 512; k += blockDim.x) {
+        float s, c;
+        sincospif((float)k / 256.0f, &s, &c);
+        t->tw[k] = make_float2(c, -s);
+        t->win[k] = 0.5f - 0.5f * c;
+    }
+}
+
+// Forward 256-point complex FFT of `a` (natural order in, natural order out).
+// Result pointer is returned (it is `a` again after 4 passes).  Warp-synchronous.
+__device__ __forceinline__ float2* warp_fft256(float2* a, float2* b, const float2* __restrict__ tw, int lane) {
+    float2* in = a;
+    float2* out = b;
+#pragma unroll
+    for (int pass = 0; pass < 4; ++pass) {
+        const int Ns = 1 << (2 * pass);          // 1,4,16,64
+        const int twstep = 128 >> (2 * pass);    // 512/(4*Ns)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int j = lane + 32 * h;         // butterfly index 0..63
+            const int k = j & (Ns - 1);
+            float2 v0 = in[j];
+            float2 v1 = cmul(in[j + 64], tw[k * twstep]);
+            float2 v2 = cmul(in[j + 128], tw[2 * k * twstep]);
+            float2 v3 = cmul(in[j + 192], tw[3 * k * twstep]);
+            float2 s02 = make_float2(v0.x + v2.x, v0.y + v2.y);
+            float2 d02 = make_float2(v0.x - v2.x, v0.y - v2.y);
+            float2 s13 = make_float2(v1.x + v3.x, v1.y + v3.y);
+            float2 d13 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i * (v1 - v3)
+            const int j0 = ((j - k) << 2) + k;
+            out[j0] = make_float2(s02.x + s13.x, s02.y + s13.y);
+            out[j0 + Ns] = make_float2(d02.x + d13.x, d02.y + d13.y);
+            out[j0 + 2 * Ns] = make_float2(s02.x - s13.x, s02.y - s13.y);
+            out[j0 + 3 * Ns] = make_float2(d02.x - d13.x, d02.y - d13.y);
+        }
+        __syncwarp();
+        float2* tmp = in; in = out; out = tmp;
+    }
+    return in;
+}
+
+// After warp_fft256 of z[n] = x[2n] + i x[2n+1]:  X[k], k = 0..256.
+__device__ __forceinline__ float2 rfft_bin(const float2* Z, const float2* __restrict__ tw, int k) {
+    float2 zk = Z[k & 255];
+    float2 zc = Z[(256 - k) & 255];
+    zc.y = -zc.y;                                              // conj(Z[256-k])
+    float2 e = make_float2(0.5f * (zk.x + zc.x), 0.5f * (zk.y + zc.y));
+    float2 o = make_float2(0.5f * (zk.y - zc.y), -0.5f * (zk.x - zc.x));   // -i/2 (zk - zc)
+    float2 wo = cmul(o, tw[k]);
+    return make_float2(e.x + wo.x, e.y + wo.y);
+}
+
+// Inverse: pack one-sided spectrum X[0..256] into conj(Z) so that a forward FFT followed by a
+// conjugate gives z[n] = x[2n] + i x[2n+1] (times 256).  Imag of DC/Nyquist is ignored (c2r).
+__device__ __forceinline__ float2 irfft_pack(float2 xk, float2 xc /* X[256-k] */, const float2* __restrict__ tw, int k) {
+    // E = (X[k] + conj(X[256-k]))/2 ; O = (X[k] - conj(X[256-k]))/2 * conj(tw[k]) ; Z = E + iO
+    float2 e = make_float2(0.5f * (xk.x + xc.x), 0.5f * (xk.y - xc.y));
+    float2 d = make_float2(0.5f * (xk.x - xc.x), 0.5f * (xk.y + xc.y));
+    float2 w = tw[k];
+    float2 o = make_float2(d.x * w.x + d.y * w.y, d.y * w.x - d.x * w.y);   // d * conj(w)
+    float2 z = make_float2(e.x - o.y, e.y + o.x);
+    z.y = -z.y;                                                // conj for the forward-FFT trick
+    return z;
+}

@@ -1,0 +1,84 @@
+/* css_b200 -- C ABI of the B200-native CSS hot path (libcss_b200.so).
+ *
+ * The reference (desh2608/css) is pure Python: it has no FFI boundary of its own.  Its plug-in
+ * points for this path are Python objects; each entry point below is what the
+ * Python class/function named in its comment binds through ctypes (css_b200/_native.py).
+ *
+ * Conventions: every pointer is a DEVICE pointer unless the name ends in _host; the caller owns
+ * and allocates all buffers; calls are stream-ordered on `stream` and never synchronise; the
+ * return value is 0 on success, negative on error with the text in css_last_error().
+ * "KP" = 264 is the padded bin pitch of bin-fastest arrays (257 bins of the 512-point STFT).
+ */
+#ifndef CSS_B200_H
+#define CSS_B200_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* css_stream_t;
+
+const char* css_last_error(void);
+int css_version(void);
+unsigned long long css_launch_count(int reset);   /* kernels launched since last reset */
+
+/* ---- STFT / features: css/executor/feature.py:45-82 (STFT.forward), :105-134, :156-175 ---- */
+/* spec[sig][frame][KP] complex64; frame g covers samples [256 g, 256 g + 512), Hann(512). */
+int css_stft(const float* x, long n_sig, long sig_stride, long n_frames, void* spec, css_stream_t stream);
+/* centred-STFT frame 0 (reflect pad) of every chunk: css/executor/beamformer.py:137-145 */
+int css_stft_edge(const float* x, long n_sig, long sig_stride, long n_chunks, long chunk_hop, void* edge,
+                  css_stream_t stream);
+/* mag (B,257,T), feat (B,T,ldf) = [MVN(mag ch0) | IPD pairs]; spec element (d,b,t,k) at
+ * spec[(d*stride_d + b*stride_chunk + t)*KP + k] */
+int css_features(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
+                 const int* ipd_r, int n_pairs, float* mag, float* feat, int ldf, css_stream_t stream);
+/* css/models/conformer.py:95, css/models/blstm.py:80 */
+int css_mvn_time(float* x, long n, int T, int F, int ld, css_stream_t stream);
+
+/* ---- dense layers: torch.nn.Linear call sites css/models/conformer.py:79-81,124,205-209,314-320 ---- */
+/* C = residual + alpha * act(A . W^T + bias); act 0 none / 1 ReLU; clamp_max > 0 caps after act */
+int css_gemm_f32(const float* A, int lda, const float* W, int ldw, const float* bias, float* C, int ldc, long M,
+                 int N, int K, int act, float alpha, const float* residual, int ldr, float clamp_max,
+                 css_stream_t stream);
+int css_layernorm(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
+                  css_stream_t stream);
+/* css/models/conformer.py:229-250 (MultiHeadedAttention core with relative position keys) */
+int css_relpos_attention(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
+                         css_stream_t stream);
+/* css/executor/separator.py:100-104: (N*T, C*nb) -> (N, nb, T, C) */
+int css_masks_layout(const float* m, int ldm, float* out, long N, int T, int nb, int C, css_stream_t stream);
+
+/* ---- Conformer mask estimator: css/models/conformer.py:83-104 (Conformer.forward) ---- */
+typedef struct {
+    const float *ln_g, *ln_b, *w1, *b1, *w2, *b2;        /* FeedForward: LN, Linear(d,dffn), Linear(dffn,d) */
+} css_ffn_weights;
+typedef struct {
+    css_ffn_weights ff_in;
+    const float *att_ln_g, *att_ln_b, *wqkv, *bqkv, *wo, *bo;   /* wqkv = cat(linear_q,k,v) (3d,d) */
+    const float *conv_ln_g, *conv_ln_b, *dw_w, *dw_b, *bn_scale, *bn_shift;   /* dw_w centre-padded to 33 taps */
+    float pw1_w0, pw1_b0, pw1_w1, pw1_b1, pw2_w, pw2_b;         /* scalar "pointwise" affines (host values) */
+    css_ffn_weights ff_out;
+    const float *out_ln_g, *out_ln_b;
+} css_conformer_block;
+typedef struct {
+    int idim, ldin, d_model, heads, d_ffn, num_blocks, num_bins, num_out, pe_rows;
+    const float *embed_w, *embed_b, *embed_ln_g, *embed_ln_b;   /* embed_w (d, ldin), zero padded */
+    const float* pe;                                            /* (pe_rows, d/heads) or NULL */
+    const float *head_w, *head_b;                               /* (num_bins*num_out, d) */
+} css_conformer_desc;
+
+void* css_conformer_create(const css_conformer_desc* desc_host, const css_conformer_block* blocks_host);
+void css_conformer_destroy(void* model);
+size_t css_conformer_workspace_bytes(const void* model, long N, int T);
+/* feat (N*T, ldin) is normalised IN PLACE when apply_mvn != 0.  Exactly one of masks (N,nb,T,C;
+ * clamped to <= clamp_max when clamp_max > 0) or head (N*T, ld_head; ReLU only) may be non-NULL. */
+int css_conformer_forward(void* model, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks,
+                          float* head, int ld_head, void* workspace, size_t workspace_bytes, css_stream_t stream);
+/* 0 = exact fp32 SIMT, 1 = tcgen05 bf16x3 split (fp32-accurate), 2 = tcgen05 bf16 */
+int css_set_gemm_mode(int mode);
+int css_get_gemm_mode(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
