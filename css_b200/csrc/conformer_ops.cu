@@ -77,13 +77,13 @@ extern "C" int css_layernorm(const float* x, const float* g, const float* b, flo
 
 __global__ void __launch_bounds__(ATT_WARPS * 32)
 relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__ pe, int pe_rows, int use_pe,
-                        float* __restrict__ out, int T, int H) {
+                        float* __restrict__ out, int T, int H, int v_smem) {
     extern __shared__ float sm[];
     const int TP = (T + 31) & ~31;             // padded j extent
     const int RP = 2 * TP;                     // padded relative extent
     float* Kt = sm;                            // [64][TP]
     float* Vs = Kt + ATT_DK * TP;              // [T][64]
-    float* Pt = Vs + T * ATT_DK;               // [64][RP]   Pt[d][r] = pe[clamp(r - (T-1)) + maxlen][d]
+    float* Pt = Vs + (v_smem ? T * ATT_DK : 0);   // [64][RP]   Pt[d][r] = pe[clamp(r - (T-1)) + maxlen][d]
     float* Pb = Pt + ATT_DK * RP;              // [warps][TP] probabilities
     float* Qb = Pb + ATT_WARPS * TP;           // [warps][64]
     const int n = blockIdx.x / H, h = blockIdx.x % H;
@@ -93,7 +93,7 @@ relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__
     for (int i = threadIdx.x; i < T * ATT_DK; i += blockDim.x) {
         const int j = i >> 6, d = i & 63;
         Kt[d * TP + j] = base[(long)j * ld + (H + h) * ATT_DK + d];
-        Vs[j * ATT_DK + d] = base[(long)j * ld + (2 * H + h) * ATT_DK + d];
+        if (v_smem) Vs[j * ATT_DK + d] = base[(long)j * ld + (2 * H + h) * ATT_DK + d];
     }
     for (int i = threadIdx.x; i < ATT_DK * (TP - T); i += blockDim.x) {
         const int d = i / (TP - T), j = T + i % (TP - T);
@@ -114,6 +114,9 @@ relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__
     float* pb = Pb + warp * TP;
     float* qb = Qb + warp * ATT_DK;
     const int NJ = TP / 32;
+    // V rows: shared memory when it fits (T <= ~190), else straight from global (L1/L2 resident)
+    const float* Vsrc = v_smem ? Vs : base + (2 * H + h) * ATT_DK;
+    const int vld = v_smem ? ATT_DK : ld;
     for (int i = warp; i < T; i += ATT_WARPS) {
         const float* qrow = base + (long)i * ld + h * ATT_DK;
         qb[lane] = qrow[lane];
@@ -157,8 +160,8 @@ relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__
         float o0 = 0.f, o1 = 0.f;
         for (int j = 0; j < T; ++j) {
             const float p = pb[j];
-            o0 = fmaf(p, Vs[j * ATT_DK + lane], o0);
-            o1 = fmaf(p, Vs[j * ATT_DK + lane + 32], o1);
+            o0 = fmaf(p, Vsrc[(long)j * vld + lane], o0);
+            o1 = fmaf(p, Vsrc[(long)j * vld + lane + 32], o1);
         }
         float* orow = out + ((long)n * T + i) * (H * ATT_DK) + h * ATT_DK;
         orow[lane] = o0;
@@ -167,24 +170,25 @@ relpos_attention_kernel(const float* __restrict__ qkv, const float* __restrict__
     }
 }
 
-size_t attention_smem_bytes(int T) {
+size_t attention_smem_bytes(int T, int v_smem) {
     const int TP = (T + 31) & ~31;
-    return sizeof(float) * ((size_t)ATT_DK * TP + (size_t)T * ATT_DK + (size_t)ATT_DK * 2 * TP + ATT_WARPS * TP +
-                            ATT_WARPS * ATT_DK);
+    return sizeof(float) * ((size_t)ATT_DK * TP + (v_smem ? (size_t)T * ATT_DK : 0) + (size_t)ATT_DK * 2 * TP +
+                            ATT_WARPS * TP + ATT_WARPS * ATT_DK);
 }
 
 int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
                      cudaStream_t st) {
     CSS_REQUIRE(dk == ATT_DK, "attention: head dim %d unsupported (kernel is built for 64)", dk);
     CSS_REQUIRE(N > 0 && T > 0 && T <= 256, "attention: T=%d out of range (1..256)", T);
-    const size_t smem = attention_smem_bytes(T);
+    const int v_smem = attention_smem_bytes(T, 1) <= 227 * 1024;
+    const size_t smem = attention_smem_bytes(T, v_smem);
     CSS_REQUIRE(smem <= 227 * 1024, "attention: T=%d needs %zu B of shared memory", T, smem);
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(relpos_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;
     }
-    relpos_attention_kernel<<<(unsigned)(N * H), ATT_WARPS * 32, smem, st>>>(qkv, pe, pe_rows, pe != nullptr, out, T, H);
+    relpos_attention_kernel<<<(unsigned)(N * H), ATT_WARPS * 32, smem, st>>>(qkv, pe, pe_rows, pe != nullptr, out, T, H, v_smem);
     return css_check_launch("relpos_attention");
 }
 

@@ -1,0 +1,73 @@
+"""End-to-end CSS of one recording: the loop body of scripts/python/separate_libricss.py:65-82.
+
+    separator.separate -> stitcher.get_stitch -> stitcher.get_connect -> beamformer.continuous_process
+
+``CssPipeline`` wires the three executor objects together without leaving the device: the global
+STFT is computed once and shared by the feature kernel and the MVDR kernel, the permutation bits and
+the stitched masks stay in HBM, and only the two separated waveforms are read back.
+"""
+import torch
+import yaml
+
+from .executor.beamformer import Beamformer
+from .executor.separator import Separator
+from .executor.stitcher import Stitcher
+
+# conf/config_7ch.yaml and conf/config_1ch.yaml of the reference, as dicts (model_path is unused when a
+# model object is handed in).
+CONFIG_7CH = {
+    "sampling_rate": 16000,
+    "separation": {"batch_size": 1, "eval_hop": 0.8, "eval_win": 2.4, "frame_length": 512, "frame_shift": 256,
+                   "model_path": "checkpoints/conformer_large.onnx", "ipd": "1,0;2,0;3,0;4,0;5,0;6,0",
+                   "merge": True, "merge_threshold": 16},
+    "stitching": {"eval_hop": 0.8, "eval_win": 2.4, "hop_size": 256, "n_fft": 512, "connector": "mask", "stitcher": "mask"},
+    "beamforming": {"batch_size": 32, "type": "SoudenMVDRBeamformer", "hop_size": 256, "n_fft": 512, "eval_hop": 0.8,
+                    "proceed_margin": 2, "eval_win": 2.4, "wta_thresh": 0.0001},
+}
+CONFIG_1CH = {
+    "sampling_rate": 16000,
+    "separation": {"batch_size": 1, "eval_hop": 0.8, "eval_win": 2.4, "frame_length": 512, "frame_shift": 256,
+                   "model_path": "checkpoints/1ch_conformer_large.onnx"},
+    "stitching": CONFIG_7CH["stitching"],
+    "beamforming": CONFIG_7CH["beamforming"],
+}
+
+
+def load_config(path):
+    with open(path) as f:
+        return yaml.load(f, Loader=yaml.FullLoader)
+
+
+class CssPipeline:
+    def __init__(self, cfg, model, device="cuda"):
+        sr = cfg.get("sampling_rate", 16000)
+        self.cfg = cfg
+        self.sr = sr
+        self.device = torch.device(device)
+        self.separator = Separator(cfg["separation"], sr=sr, device=device, backend="b200", model=model)
+        self.stitcher = Stitcher(cfg["stitching"], sr=sr)
+        self.beamformer = Beamformer(cfg["beamforming"], sr=sr)
+
+    def __call__(self, wav, beamform=None, return_intermediates=False):
+        """wav: (D, T) fp32, host (pinned for an async copy) or device.  -> (2, T) separated waveforms (CUDA).
+
+        With a single channel (no MVDR possible, as in the reference's 1-ch flow) the stitched masks
+        [3][L][KP] are returned instead.
+        """
+        wav = wav.to(self.device, torch.float32, non_blocking=True)
+        masks, mags = self.separator.separate(wav)
+        swap = self.stitcher.stitch_device(mags, masks)
+        stitched = self.stitcher.connect_device(swap, masks)
+        if beamform is None:
+            beamform = wav.shape[0] > 1
+        out = None
+        if beamform:
+            views = tuple(stitched[c, :, :257].t() for c in range(3))
+            for v in views:
+                v._css_stitched = stitched
+            o0, o1 = self.beamformer.continuous_process(wav, views, spec=self.separator.last["spec"])
+            out = torch.cat([o0, o1], 0)
+        if return_intermediates:
+            return {"masks": masks, "mags": mags, "swap": swap, "stitched": stitched, "wavs": out,
+                    "sims": self.stitcher.last_sims, "doa": self.separator.angle_merge_debug()}
+        return out if beamform else stitched

@@ -74,6 +74,60 @@ size_t css_conformer_workspace_bytes(const void* model, long N, int T);
  * clamped to <= clamp_max when clamp_max > 0) or head (N*T, ld_head; ReLU only) may be non-NULL. */
 int css_conformer_forward(void* model, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks,
                           float* head, int ld_head, void* workspace, size_t workspace_bytes, css_stream_t stream);
+
+/* ---- BLSTM mask estimator: css/models/blstm.py:68-88 (BLSTM.forward) ---- */
+typedef struct {
+    const float *w_ih;      /* (4*hdim, hdim) = cat(weight_ih_l0, weight_ih_l0_reverse) */
+    const float *b_gates;   /* (4*hdim) = cat(bias_ih+bias_hh fwd, bias_ih+bias_hh reverse) */
+    const float *w_hh_f, *w_hh_b;   /* (2*hdim, hdim/2) each */
+    const float *ln_g, *ln_b;
+} css_blstm_layer;
+typedef struct {
+    int idim, ldin, hdim, num_layers, num_bins, num_out;
+    const float *embed_w, *embed_b, *embed_ln_g, *embed_ln_b;
+    const float *head_w, *head_b;
+} css_blstm_desc;
+void* css_blstm_create(const css_blstm_desc* desc_host, const css_blstm_layer* layers_host);
+void css_blstm_destroy(void* model);
+size_t css_blstm_workspace_bytes(const void* model, long N, int T);
+int css_blstm_forward(void* model, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks,
+                      float* head, int ld_head, void* workspace, size_t workspace_bytes, css_stream_t stream);
+
+/* ---- mask post-processing + stitching: css/executor/separator.py:165-250, css/executor/stitcher.py ---- */
+/* svT (30,7,hi-lo) complex64; like (B,2,30); idx (B,3) = {argmax spk0, argmax spk1, merged?}.  masks (B,257,T,C)
+ * are updated in place (output 0 overwritten with 1e-12 where the two DOAs are within thresh degrees). */
+int css_doa_merge(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const void* svT,
+                  const float* angles, int lo, int hi, float thresh, float* masks, int C, float* like, int* idx,
+                  css_stream_t stream);
+/* Stitcher.get_stitch (stitcher.py:14-52): swap[n]=1 <=> perm [1,0]; sims (B-1,4) optional */
+int css_stitch_perm(const float* mags, const float* masks, long n_chunks, int T, int C, int margin, int* swap,
+                    float* sims, css_stream_t stream);
+/* stitcher.py:55-60: state[0]=0, state[n+1]=state[n]^swap[n] */
+int css_perm_states(const int* swap, long n_chunks, int* state, css_stream_t stream);
+/* Stitcher.get_connect (stitcher.py:62-110): out [3][L][KP], L = hop*(B-1)+T */
+int css_stitch_connect(const float* masks, const int* state, long n_chunks, int T, int C, int hop, float* out,
+                       css_stream_t stream);
+
+/* ---- MVDR beamformer: css/executor/beamformer.py:126-183 + asteroid compute_scm / SoudenMVDRBeamformer ---- */
+/* spec [7][frames][KP], edge [7][B][KP], stitched [3][L][KP] -> Y [B][2][T][KP] complex64,
+ * energy [B][2][css_mvdr_energy_blocks()][2] partial sums (|y|^2, |mask x0|^2) */
+int css_mvdr(const void* spec, const void* edge, long frames, long n_chunks, const float* stitched, long L,
+             int hop_frames, int T, void* Y, float* energy, css_stream_t stream);
+int css_mvdr_energy_blocks(void);
+/* normalize_scale (beamformer.py:165-183) + dedup (beamformer.py:68-80), in place; scal (B,5) */
+int css_mvdr_finalize(void* Y, const float* energy, long n_chunks, int T, int rescale, int dedup, float* scal,
+                      css_stream_t stream);
+/* torch.istft + placement (beamformer.py:83-118): plan (n_items,4) int32 {chunk, s_begin, s_end, dst};
+ * out (2, out_len) is accumulated into; items of one call must not overlap in out */
+int css_istft_place(const void* Y, int T, const int* plan, int n_items, float* out, long out_len, css_stream_t stream);
+/* beamformer.py:122-123; scratch: `rows` uint32 */
+int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scratch, css_stream_t stream);
+
+/* ---- PIT-MSE: css/objectives/pit.py:5-62, css/objectives/mse.py:29-37 ---- */
+/* est/tgt (B,K,n); pair_ws (B,K,K) f64; loss_b (B); perm (B,K) int32; loss (1); grad (B,K,n) or NULL */
+int css_pit_mse(const float* est, const float* tgt, long B, int K, long n, double* pair_ws, float* loss_b, int* perm,
+                float* loss, float* grad, float gscale, css_stream_t stream);
+
 /* 0 = exact fp32 SIMT, 1 = tcgen05 bf16x3 split (fp32-accurate), 2 = tcgen05 bf16 */
 int css_set_gemm_mode(int mode);
 int css_get_gemm_mode(void);

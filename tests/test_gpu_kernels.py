@@ -1,0 +1,262 @@
+"""GPU parity tests, kernel level: every C-ABI entry point against the CPU oracle on seeded inputs.
+
+Tolerances (fp32 path): DSP kernels 1e-5 relative, network layers 1e-4, stated per test.
+"""
+import math
+
+import pytest
+import torch
+
+from oracle import css_oracle as O
+from tests.helpers import cpu_state_dict, golden_blstm, golden_conformer, rel_inf
+
+pytestmark = pytest.mark.gpu
+
+
+def _nv():
+    from css_b200 import _native as nv
+
+    return nv
+
+
+def test_library_loaded_and_counts_launches(cuda):
+    nv = _nv()
+    assert nv.lib().css_version() >= 100
+    nv.launch_count(reset=True)
+    from css_b200.executor.feature import stft
+
+    stft(torch.randn(2, 4096, device=cuda))
+    assert nv.launch_count() == 1
+
+
+def test_stft_matches_conv_stft(cuda):
+    from css_b200.executor.feature import stft
+
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(3, 38656, generator=g) * 0.1
+    spec = torch.view_as_complex(stft(x.to(cuda)))[:, :, :257].cpu()      # (sig, frames, bins)
+    _, _, re, im = O.stft_conv(x)
+    assert spec.shape[1] == re.shape[-1] == 150
+    assert rel_inf(spec.real.transpose(1, 2), re) < 1e-5
+    assert rel_inf(spec.imag.transpose(1, 2), im) < 1e-5
+
+
+def test_stft_linearity_large(cuda):
+    """Size-independent property at a BASELINE-scale length (7 ch x 60 s): STFT(a x + y) = a STFT(x) + STFT(y)."""
+    from css_b200.executor.feature import stft
+
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(7, 960000, generator=g, device=cuda)
+    y = torch.randn(7, 960000, generator=g, device=cuda)
+    lhs = stft(2.5 * x + y)
+    rhs = 2.5 * stft(x) + stft(y)
+    assert rel_inf(lhs, rhs) < 2e-5
+
+
+def test_stft_edge_is_centred_frame0(cuda):
+    from css_b200.executor.feature import stft, stft_edge
+
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(2, 12800 * 2 + 38656, generator=g) * 0.1
+    edge = torch.view_as_complex(stft_edge(x.to(cuda), 3, 12800))[:, :, :257].cpu()
+    spec = torch.view_as_complex(stft(x.to(cuda)))[:, :, :257].cpu()
+    for c in range(3):
+        ref = O.centered_stft(x[:, 12800 * c : 12800 * c + 38656])       # (sig, F, 152)
+        assert rel_inf(edge[:, c], ref[:, :, 0]) < 1e-5
+        # centred frame t >= 1 == uncentred global frame 50c + t - 1
+        assert rel_inf(spec[:, 50 * c : 50 * c + 149].transpose(1, 2), ref[:, :, 1:150]) < 1e-5
+
+
+def test_feature_extractor_matches_reference_layout(cuda, golden):
+    from css_b200.executor.feature import FeatureExtractor
+
+    wav = torch.from_numpy(golden["A_wav_i16"]).float() / 32767
+    chunks = wav.unfold(-1, 38656, 12800).permute(1, 0, 2).contiguous()[:2]
+    ipd = "1,0;2,0;3,0;4,0;5,0;6,0"
+    fe = FeatureExtractor(512, 256, ipd_index=ipd)
+    mag, f, re, im = fe.forward(chunks.to(cuda))
+    mag_o, f_o, re_o, im_o = O.feature_extract(chunks, ipd_index=ipd)
+    assert f.shape == f_o.shape == (2, 1799, 150)
+    assert rel_inf(mag, mag_o) < 1e-5 and rel_inf(re, re_o) < 1e-5 and rel_inf(im, im_o) < 1e-5
+    assert rel_inf(f[:, :257], f_o[:, :257]) < 1e-4
+    d = (f[:, 257:].cpu() - f_o[:, 257:]).abs()
+    d = torch.minimum(d, 2 * math.pi - d)                      # IPD is an angle: compare modulo 2 pi
+    # the IPD is atan2 of mean-removed unit phasors: ill-conditioned where both arguments vanish
+    assert float(d.max()) < 2e-2 and float(d.mean()) < 1e-5
+    # golden (reference-generated) subsample
+    assert rel_inf(f.cpu()[:, ::7, ::3][:, :37], torch.from_numpy(golden["A_feat"])[:, :37]) < 1e-4
+    assert rel_inf(re.cpu()[:, :, ::5, ::7], golden["A_re"]) < 1e-5
+
+
+def test_feature_extractor_single_channel(cuda):
+    from css_b200.executor.feature import FeatureExtractor
+
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(3, 38656, generator=g) * 0.05
+    mag, f, re, im = FeatureExtractor(512, 256).forward(x.to(cuda))
+    mag_o, f_o, re_o, im_o = O.feature_extract(x)
+    assert mag.shape == (3, 257, 150) and f.shape == (3, 257, 150) and re.shape == (3, 257, 150)
+    assert rel_inf(mag, mag_o) < 1e-5 and rel_inf(f, f_o) < 1e-4
+
+
+@pytest.mark.parametrize("M,N,K,act,alpha,res,clamp", [
+    (300, 256, 1856, 0, 1.0, False, 0.0),
+    (150, 1024, 256, 1, 1.0, False, 0.0),
+    (1000, 256, 1024, 0, 0.5, True, 0.0),
+    (77, 771, 256, 1, 1.0, False, 1.0),
+    (129, 768, 256, 0, 1.0, False, 0.0),
+])
+def test_gemm_f32(cuda, M, N, K, act, alpha, res, clamp):
+    nv = _nv()
+    g = torch.Generator().manual_seed(M + N)
+    A = torch.randn(M, K, generator=g)
+    W = torch.randn(N, K, generator=g) / math.sqrt(K)
+    bias = torch.randn(N, generator=g)
+    R = torch.randn(M, N, generator=g) if res else None
+    ldc = (N + 7) // 8 * 8
+    C = torch.zeros(M, ldc, device=cuda)
+    Ad, Wd, bd = A.to(cuda), W.to(cuda), bias.to(cuda)
+    Rd = R.to(cuda) if res else None
+    nv.call("css_gemm_f32", nv.ptr(Ad), nv.c_int(K), nv.ptr(Wd), nv.c_int(K), nv.ptr(bd), nv.ptr(C), nv.c_int(ldc),
+            nv.c_long(M), nv.c_int(N), nv.c_int(K), nv.c_int(act), nv.c_float(alpha), nv.ptr(Rd), nv.c_int(N),
+            nv.c_float(clamp))
+    ref = A.double() @ W.double().t() + bias.double()
+    if act:
+        ref = ref.relu()
+    if clamp > 0:
+        ref = ref.clamp(max=clamp)
+    ref = ref * alpha
+    if res:
+        ref = ref + R.double()
+    assert rel_inf(C[:, :N], ref) < 1e-5
+
+
+@pytest.mark.parametrize("d", [256, 512, 1024])
+def test_layernorm(cuda, d):
+    nv = _nv()
+    g = torch.Generator().manual_seed(d)
+    x = torch.randn(333, d, generator=g) * 3 + 1
+    w, b = torch.randn(d, generator=g), torch.randn(d, generator=g)
+    y = torch.empty(333, d, device=cuda)
+    xd, wd, bd = x.to(cuda), w.to(cuda), b.to(cuda)
+    nv.call("css_layernorm", nv.ptr(xd), nv.ptr(wd), nv.ptr(bd), nv.ptr(y), nv.c_long(333), nv.c_int(d), nv.c_float(1e-5), nv.c_int(0))
+    assert rel_inf(y, torch.nn.functional.layer_norm(x, (d,), w, b, 1e-5)) < 1e-5
+
+
+@pytest.mark.parametrize("T", [150, 37, 250])
+def test_relpos_attention(cuda, T):
+    nv = _nv()
+    g = torch.Generator().manual_seed(T)
+    N, H, dk = 3, 4, 64
+    qkv = torch.randn(N * T, 3 * H * dk, generator=g)
+    pe = torch.randn(2000, dk, generator=g) * 0.5
+    out = torch.empty(N * T, H * dk, device=cuda)
+    qd, pd = qkv.to(cuda), pe.to(cuda)
+    nv.call("css_relpos_attention", nv.ptr(qd), nv.ptr(pd), nv.c_int(2000), nv.ptr(out), nv.c_long(N), nv.c_int(T), nv.c_int(H), nv.c_int(dk))
+    q, k, v = (t.view(N, T, H, dk).transpose(1, 2).double() for t in qkv.chunk(3, dim=1))
+    idx = torch.arange(T)
+    pos = pe.double()[(idx[:, None] - idx[None, :]).clamp(-1000, 999) + 1000]        # (T,T,dk)
+    sc = (q @ k.transpose(-1, -2) + torch.einsum("nhid,ijd->nhij", q, pos)) / math.sqrt(dk)
+    ref = (torch.softmax(sc, -1) @ v).transpose(1, 2).reshape(N * T, H * dk)
+    assert rel_inf(out, ref) < 1e-5
+
+
+@pytest.mark.parametrize("N,T", [(2, 150), (3, 37), (1, 250)])
+def test_conformer_forward_vs_oracle(cuda, N, T):
+    """Whole network (2 blocks, idim 1799): LN, GEMMs, rel-pos MHSA, conv module, head.  fp32 path: 1e-4."""
+    model = golden_conformer(num_blocks=2)
+    sd = cpu_state_dict(model)
+    g = torch.Generator().manual_seed(N * 1000 + T)
+    f = torch.randn(N, T, 1799, generator=g) * 2 + 0.3
+    y_pred, masks = model.to(cuda)(f.to(cuda))
+    with torch.no_grad():
+        y_o, m_o = O.model_forward(f, sd)
+    assert y_pred.shape == (N, 2, T, 257) and len(masks) == 3
+    for a, b in zip(masks, m_o):
+        assert rel_inf(a, b) < 1e-4
+    assert rel_inf(y_pred, y_o) < 1e-4
+
+
+def test_conformer_golden_masks(cuda, golden):
+    """Reference-generated masks for the first two chunks of case A (tests/golden/make_golden.py)."""
+    from css_b200.executor.feature import FeatureExtractor
+
+    wav = torch.from_numpy(golden["A_wav_i16"]).float() / 32767
+    chunks = wav.unfold(-1, 38656, 12800).permute(1, 0, 2).contiguous()[:2]
+    _, f, _, _ = FeatureExtractor(512, 256, ipd_index="1,0;2,0;3,0;4,0;5,0;6,0").forward(chunks.to(cuda))
+    model = golden_conformer(num_blocks=2).to(cuda)
+    _, masks = model(f.transpose(1, 2).contiguous())
+    for c in range(3):
+        assert rel_inf(masks[c].cpu()[:, ::3, ::3], golden["A_masks2"][c]) < 1e-3
+
+
+@pytest.mark.parametrize("N,T", [(3, 150), (70, 20)])
+def test_blstm_forward_vs_oracle(cuda, N, T):
+    model = golden_blstm()
+    sd = cpu_state_dict(model)
+    g = torch.Generator().manual_seed(N + T)
+    f = torch.rand(N, T, 257, generator=g) * 3
+    y_pred, masks = model.to(cuda)(f.to(cuda))
+    with torch.no_grad():
+        y_o, m_o = O.model_forward(f, sd)
+    for a, b in zip(masks, m_o):
+        assert rel_inf(a, b) < 1e-4
+    assert rel_inf(y_pred, y_o) < 1e-4
+
+
+def test_session_protocol(cuda):
+    """The ORT-session plug-in contract of css/executor/separator.py:94-103."""
+    from css_b200.utils.model_util import B200Session
+
+    model = golden_blstm()
+    sd = cpu_state_dict(model)
+    sess = B200Session(model.to(cuda))
+    g = torch.Generator().manual_seed(4)
+    f = torch.rand(1, 257, 150, generator=g)
+    res = sess.run(None, {sess.get_inputs()[0].name: f.numpy()})
+    assert len(res) == 3 and res[0].shape == (257, 150)
+    with torch.no_grad():
+        m_o = O.blstm_masks(f.transpose(1, 2), sd)
+    for a, b in zip(res, m_o):
+        assert rel_inf(torch.from_numpy(a), b[0].t()) < 1e-4
+
+
+def test_pit_mse_golden_and_grad(cuda, golden):
+    from css_b200.objectives.pit import pit_loss, pit_mse_batch
+
+    g = torch.Generator().manual_seed(int(golden["D_seed"]))
+    est = torch.rand(6, 2, 50, 257, generator=g)
+    tgt = torch.rand(6, 2, 50, 257, generator=g)
+    tgt[1] = est[1].flip(0) + 0.01 * torch.rand(2, 50, 257, generator=g)
+    tgt[2] = est[2]
+    tgt[3, 1] = tgt[3, 0]; est[3, 1] = est[3, 0]
+    est3 = torch.rand(2, 3, 20, 257, generator=g)
+    tgt3 = est3[:, [2, 0, 1]] + 0.01 * torch.rand(2, 3, 20, 257, generator=g)
+    e = est.to(cuda).requires_grad_(True)
+    loss, perm, loss_b = pit_mse_batch(e, tgt.to(cuda))
+    assert perm.cpu().tolist() == golden["D_perm"].tolist()                 # permutation choices bit-exact
+    assert rel_inf(loss_b, golden["D_loss"]) < 1e-5
+    loss.backward()
+    e_cpu = est.clone().requires_grad_(True)
+    O.pit_mse(e_cpu, tgt).backward()
+    assert rel_inf(e.grad, e_cpu.grad) < 1e-5
+    _, perm3, loss3 = pit_mse_batch(est3.to(cuda), tgt3.to(cuda))
+    assert perm3.cpu().tolist() == golden["D_perm3"].tolist() and rel_inf(loss3, golden["D_loss3"]) < 1e-5
+    l, p = pit_loss(est[1].to(cuda), tgt[1].to(cuda), axis=0, return_permutation=True)
+    assert p == (1, 0) and abs(float(l) - float(golden["D_loss"][1])) < 1e-6
+    with pytest.raises(AssertionError):
+        pit_loss(est[0].to(cuda), tgt[0, :, :10].to(cuda), axis=0)
+
+
+def test_no_cpu_fallback(cuda):
+    nv = _nv()
+    from css_b200.executor.feature import FeatureExtractor, stft
+
+    with pytest.raises(nv.NativeError):
+        stft(torch.randn(2, 4096))
+    with pytest.raises(nv.NativeError):
+        golden_blstm()(torch.rand(1, 10, 257))
+    with pytest.raises(RuntimeError):
+        stft(torch.randn(2, 100, device=cuda))                # shorter than one frame
+    with pytest.raises(RuntimeError):
+        FeatureExtractor().forward(torch.randn(2, 2, 2, 2, device=cuda))
