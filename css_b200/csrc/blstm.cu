@@ -173,7 +173,9 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         dim3 grid((unsigned)((N + LS_BN - 1) / LS_BN), H / LS_BJ, 2);
         float *hp = hs0, *hn = hs1;
         for (int s = 0; s < T; ++s) {
+            css_prof_begin(4, 2.0 * 2.0 * (double)N * H * 4 * H, st);
             lstm_step_kernel<<<grid, 256, 0, st>>>(xp, L.w_hh_f, L.w_hh_b, hp, hn, cs, y, N, T, H, s);
+            css_prof_end(st);
             if ((rc = css_check_launch("lstm_step"))) return rc;
             float* tmp = hp; hp = hn; hn = tmp;
         }

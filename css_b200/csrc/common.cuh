@@ -12,6 +12,10 @@
 // error plumbing (api.cu)
 void css_set_error(const char* fmt, ...);
 int css_check_launch(const char* what);
+// per-category event timing (api.cu); categories: 0 gemm(flops) 1 attention(flops) 2 conv module(bytes)
+// 3 layernorm(bytes) 4 lstm step(flops)
+void css_prof_begin(int cat, double work, cudaStream_t st);
+void css_prof_end(cudaStream_t st);
 
 #define CSS_REQUIRE(cond, ...)            \
     do {                                  \

@@ -50,6 +50,7 @@ int layernorm_launch(const float* x, const float* g, const float* b, float* y, l
     CSS_REQUIRE(M > 0, "layernorm: empty input");
     CSS_REQUIRE(d % 128 == 0 && d <= 1024, "layernorm: d=%d must be a multiple of 128 and <= 1024", d);
     const unsigned grid = (unsigned)((M + 7) / 8);
+    css_prof_begin(3, 2.0 * (double)M * d * 4, st);
     switch (d / 128) {
         case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
         case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
@@ -57,6 +58,7 @@ int layernorm_launch(const float* x, const float* g, const float* b, float* y, l
         case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
         default: CSS_REQUIRE(false, "layernorm: unsupported d=%d", d);
     }
+    css_prof_end(st);
     return css_check_launch("layernorm");
 }
 
@@ -188,7 +190,9 @@ int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out,
         cudaFuncSetAttribute(relpos_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;
     }
+    css_prof_begin(1, 6.0 * (double)N * H * T * T * ATT_DK, st);   // QK^T + Q.PE^T + PV
     relpos_attention_kernel<<<(unsigned)(N * H), ATT_WARPS * 32, smem, st>>>(qkv, pe, pe_rows, pe != nullptr, out, T, H, v_smem);
+    css_prof_end(st);
     return css_check_launch("relpos_attention");
 }
 
@@ -282,7 +286,9 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
         attr_set = true;
     }
     dim3 grid((unsigned)N, (T + CM_TT - 1) / CM_TT);
+    css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
     conv_module_kernel<<<grid, CM_D, smem, st>>>(x, out, T, p);
+    css_prof_end(st);
     return css_check_launch("conv_module");
 }
 

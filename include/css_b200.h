@@ -21,6 +21,9 @@ typedef struct CUstream_st* css_stream_t;
 const char* css_last_error(void);
 int css_version(void);
 unsigned long long css_launch_count(int reset);   /* kernels launched since last reset */
+/* optional CUDA-event timing per kernel category: 0 gemm, 1 attention, 2 conv module, 3 layernorm, 4 lstm step */
+void css_profile_enable(int on);
+int css_profile_collect(double* ms_host, double* work_host, long* count_host, int n_cat);
 
 /* ---- STFT / features: css/executor/feature.py:45-82 (STFT.forward), :105-134, :156-175 ---- */
 /* spec[sig][frame][KP] complex64; frame g covers samples [256 g, 256 g + 512), Hann(512). */
