@@ -8,6 +8,14 @@
 
 // unit phasor of a * conj(b); atan2(0,0) = 0 convention -> (1, 0) when a product vanishes
 __device__ __forceinline__ float2 unit_cross(float2 a, float2 b) {
+    if (a.y == 0.f && b.y == 0.f) {
+        // purely real bins (DC, Nyquist): the reference takes atan2(+0, re) in {0, pi_f}, so the phase
+        // difference is 0 or +-pi_f and (cos, sin) = (-1, -+sin(pi_f)); the sign of that 8.7e-8 residue
+        // decides between +pi and -pi in the final atan2 (feature.py:118-133) and must be reproduced.
+        const bool na = signbit(a.x), nb = signbit(b.x);
+        if (na == nb) return make_float2(1.f, 0.f);
+        return make_float2(-1.f, na ? -8.742278e-8f : 8.742278e-8f);
+    }
     float2 p = cmulc(a, b);
     float n = sqrtf(p.x * p.x + p.y * p.y);
     if (n == 0.f) {

@@ -80,6 +80,10 @@ def test_feature_extractor_matches_reference_layout(cuda, golden):
     assert rel_inf(mag, mag_o) < 1e-5 and rel_inf(re, re_o) < 1e-5 and rel_inf(im, im_o) < 1e-5
     assert rel_inf(f[:, :257], f_o[:, :257]) < 1e-4
     d = (f[:, 257:].cpu() - f_o[:, 257:]).abs()
+    # purely real bins (DC / Nyquist): the +-pi choice follows the reference's sin(pi_f) residue exactly
+    real_rows = [p * 257 + k for p in range(6) for k in (0, 256)]
+    assert float(d[:, real_rows].max()) < 1e-5
+    assert int((d > 1).sum()) == 0                             # no 2 pi flips anywhere on this input
     d = torch.minimum(d, 2 * math.pi - d)                      # IPD is an angle: compare modulo 2 pi
     # the IPD is atan2 of mean-removed unit phasors: ill-conditioned where both arguments vanish
     assert float(d.max()) < 2e-2 and float(d.mean()) < 1e-5
