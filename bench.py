@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""Headline benchmark: audio-seconds separated per second (xRT), 7-ch Conformer CSS (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]             # this repo's CUDA path
+    python bench.py --impl reference [--steps K] [--warmup W]       # the reference's CPU algorithm (oracle)
+
+One step = one synthetic 7-mic LibriCSS-shaped session (default 600 s, 747 chunks) through the whole hot path:
+global STFT -> IPD features -> 16-block Conformer masks -> DOA merge -> stitch -> MVDR -> iSTFT/placement ->
+peak normalisation.  `value` times the path with the waveform already resident in HBM; `e2e` times the
+public call (`CssPipeline.__call__`) from a pinned HOST waveform to the two separated waveforms back in
+pinned host memory.  N > 1 (torchrun, one rank per GPU): every rank separates its own session (weak scaling,
+no data-path collective -- sessions are independent, run.sh:21-36 of the reference); time = max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "audio_seconds_separated_per_second_7ch_conformer_css"
+UNIT = "xRT"
+SR = 16000
+CONF_7CH = dict(idim=1799, num_bins=257, num_spk=2, num_noise=1, conformer_attention_dim=256,
+                conformer_attention_heads=4, conformer_linear_units=1024, conformer_num_blocks=16,
+                conformer_kernel_size=33, conformer_dropout_rate=0.1, conformer_relative_pos_emb=True)
+
+
+def parse():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=5)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--seconds", type=float, default=600.0, help="session length (LibriCSS sessions are ~10 min)")
+    p.add_argument("--blocks", type=int, default=16)
+    p.add_argument("--gemm-mode", type=int, default=-1, help="-1 library default, 0 fp32 SIMT, 1 bf16x3 tcgen05, 2 bf16 tcgen05")
+    p.add_argument("--cpu-seconds", type=float, default=24.0, help="audio length of the bounded CPU-baseline sample")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    return p.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            d = json.load(f)
+        return {"hbm": d["hbm_gbs"], "tensor_burst": d["bf16_tflops"], "tensor": d["bf16_tflops_sustained"], "src": "measured"}
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor": 1400.0, "src": "fallback"}
+
+
+def build_cfg(conf_blocks):
+    from css_b200.pipeline import CONFIG_7CH
+    import copy
+
+    return copy.deepcopy(CONFIG_7CH), dict(CONF_7CH, conformer_num_blocks=conf_blocks)
+
+
+def make_model(conf):
+    """Random-init weights of the reference architecture (torch.manual_seed(0), default init), eval mode."""
+    import torch
+    import css_b200.models as M
+
+    torch.manual_seed(0)
+    return M.build_model("Conformer", conf).eval()
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms during the timed region (B200_PROFILING.md)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out = self.proc.communicate(timeout=5)[0]
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out = self.proc.communicate()[0]
+        sm, mx, reasons, power = [], [], set(), []
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in out.strip().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); power.append(float(c[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm),
+                "power_w_max": max(power)}
+
+
+def cpu_reference_run(seconds, blocks, steps, warmup, threads=None):
+    """The reference's CPU algorithm for the path (oracle/css_oracle.py; the reference is Python and does not
+    travel to the GPU box) on a bounded `seconds`-long 7-ch sample, all host threads.  -> (xRT, ms/step, cores)."""
+    import torch
+    from css_b200.synth import make_recording
+    from oracle import css_oracle as O
+
+    cores = threads or os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg, conf = build_cfg(blocks)
+    model = make_model(conf)
+    sd = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    wav = make_recording(seconds, channels=7, seed=1234)
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            O.css_pipeline(wav, cfg, lambda f: O.conformer_masks(f, sd))
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+    mean = sum(times) / len(times)
+    return seconds / mean, mean * 1e3, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    secs = args.cpu_seconds
+    xrt, ms, cores = cpu_reference_run(secs, args.blocks, max(1, args.steps), max(0, args.warmup))
+    sample = f"{secs:g} s 7-ch session, {args.blocks}-block Conformer, oracle/css_oracle.py (torch CPU fp32), {cores} threads"
+    line = {"impl": "reference", "metric": METRIC, "value": xrt, "unit": UNIT, "n_gpus": args.gpus, "steps": max(1, args.steps),
+            "warmup": max(0, args.warmup), "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"7-ch Conformer CSS (conf/config_7ch.yaml), bounded CPU sample of {secs:g} s per step",
+                       "blocks": args.blocks, "session_seconds": secs},
+            "cpu_baseline": {"value": xrt, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": xrt, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from css_b200 import _native as nv
+    from css_b200.dist import init_from_env
+    from css_b200.pipeline import CssPipeline
+    from css_b200.synth import make_recording, n_chunks
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- css_b200 has no CPU fallback (use --impl reference for the CPU arm)")
+    rank, world, local = init_from_env("nccl")
+    if world != args.gpus:
+        raise SystemExit(f"bench.py: --gpus {args.gpus} but WORLD_SIZE={world} (launch N>1 with torch.distributed.run)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    lib = nv.lib()
+    if args.gemm_mode >= 0:
+        nv.check(lib.css_set_gemm_mode(args.gemm_mode), "css_set_gemm_mode")
+    gemm_mode = int(lib.css_get_gemm_mode())
+
+    cfg, conf = build_cfg(args.blocks)
+    model = make_model(conf).to(dev)
+    pipe = CssPipeline(cfg, model, device=dev)
+    T = int(args.seconds * SR)
+    wav_host = make_recording(args.seconds, channels=7, seed=1234 + rank).pin_memory()
+    wav_dev = wav_host.to(dev)
+    out_host = torch.empty(2, T, dtype=torch.float32).pin_memory()
+    B = n_chunks(T)
+    audio_s = T / SR
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def step_resident():
+        return pipe(wav_dev)
+
+    def step_e2e():
+        out = pipe(wav_host)                       # H2D of the session inside the public call
+        out_host.copy_(out, non_blocking=True)     # D2H of the two separated waveforms
+        return out
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    step_e2e()
+    barrier()
+
+    # ---- timed region 1: inputs resident in HBM (value) ----
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    lib.css_profile_enable(1)
+    nv.launch_count(reset=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step_resident()
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = nv.launch_count()
+    clocks = sampler.stop() if rank == 0 else None
+    import ctypes
+    ncat = 5
+    ms_c, work_c, cnt_c = (ctypes.c_double * ncat)(), (ctypes.c_double * ncat)(), (ctypes.c_long * ncat)()
+    nv.check(lib.css_profile_collect(ms_c, work_c, cnt_c, ncat), "css_profile_collect")
+    lib.css_profile_enable(0)
+
+    # ---- timed region 2: public call from pinned host memory, result back on the host (e2e) ----
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step_e2e()
+    e1.record()
+    barrier()
+    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    ms_step = ms_total / args.steps
+    value = world * audio_s * args.steps / (ms_total * 1e-3)
+    e2e = world * audio_s * args.steps / (ms_e2e * 1e-3)
+    # dominant kernel: the dense Linear GEMMs of the Conformer (category 0)
+    g_ms, g_flop, g_n = ms_c[0], work_c[0], cnt_c[0]
+    achieved = g_flop / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
+    names = ("gemm", "attention", "conv_module", "layernorm", "lstm_step")
+    shares = {names[i]: round(ms_c[i] / ms_total, 4) for i in range(ncat) if cnt_c[i]}
+    roof = {"kernel": {0: "gemm_simt_f32", 1: "gemm_tc_bf16x3 (tcgen05)", 2: "gemm_tc_bf16 (tcgen05)"}[gemm_mode],
+            "bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
+            "frac": achieved / pk["tensor"], "peak_source": f"{pk['src']} bf16 sustained (kernel timed inside a long step)",
+            "traffic": None, "launches": int(g_n), "avg_launch_ms": g_ms / max(1, g_n),
+            "algorithmic_flop_per_step": g_flop / args.steps, "share_of_step": shares}
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {0: "f32", 1: "bf16x3->f32", 2: "bf16"}[gemm_mode], "data": "synthetic",
+            "config": {"workload": "configs[2]: 7-ch Conformer (conf/config_7ch.yaml) mask estimation + MVDR on a synthetic "
+                                   f"7-mic LibriCSS-shaped {audio_s:g} s session per GPU per step",
+                       "session_seconds": audio_s, "chunks_per_session": B, "blocks": args.blocks, "sessions_per_step": world,
+                       "l2": f"inputs larger than L2 (waveform {wav_dev.numel() * 4 / 1e6:.0f} MB, features {B * 150 * 1856 * 4 / 1e6:.0f} MB vs 126 MB L2)",
+                       "parallelism": f"dp{world} (independent sessions, no data-path collective)", "gemm_mode": gemm_mode},
+            "clocks": clocks, "roofline": roof,
+            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
+                    "h2d_bytes_per_step": wav_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
+            "gpu_launches": int(launches)}
+    if world == 1 and not args.no_cpu_baseline:
+        torch.cuda.synchronize()
+        xrt, ms, cores = cpu_reference_run(args.cpu_seconds, args.blocks, 1, 0)
+        line["cpu_baseline"] = {"value": xrt, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": f"{args.cpu_seconds:g} s 7-ch session through oracle/css_oracle.py (torch CPU fp32, "
+                                          f"{args.blocks}-block Conformer), 1 pass, {cores} threads"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
