@@ -18,9 +18,7 @@ extern "C" int css_get_gemm_mode(void) { return g_gemm_mode; }
 int gemm_dispatch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,
                   GemmEpilogue ep, cudaStream_t st) {
     css_prof_begin(0, 2.0 * (double)M * N * K, st);
-    int rc = GEMM_TC_UNSUPPORTED;
-    if (g_gemm_mode != 0) rc = gemm_tc_launch(A, lda, W, ldw, C, ldc, M, N, K, ep, g_gemm_mode, st);
-    if (rc == GEMM_TC_UNSUPPORTED) rc = gemm_simt_launch(A, lda, W, ldw, C, ldc, M, N, K, ep, st);
+    int rc = gemm_simt_launch(A, lda, W, ldw, C, ldc, M, N, K, ep, st);
     css_prof_end(st);
     return rc;
 }

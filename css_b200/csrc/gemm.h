@@ -14,8 +14,16 @@ struct GemmEpilogue {
 int gemm_simt_launch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,
                      GemmEpilogue ep, cudaStream_t st);
 
-// tcgen05/TMEM path (gemm_tc.cu).  mode 1 = bf16x3 split (fp32-accurate), 2 = plain bf16.
-// Returns GEMM_TC_UNSUPPORTED when the shape cannot be handled (caller falls back to SIMT fp32).
-#define GEMM_TC_UNSUPPORTED 1000
-int gemm_tc_launch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,
-                   GemmEpilogue ep, int mode, cudaStream_t st);
+// ---- tcgen05/TMEM path (gemm_tc.cu) ----
+// A matrix stored as `planes` bf16 split-float planes: element (p, r, k) at ptr[p*plane_stride + r*ld + k].
+struct PlaneMat {
+    void* ptr;
+    long plane_stride;   // elements
+    int ld;              // elements, multiple of 8
+    int planes;
+};
+// C (fp32, optional) and/or `out` planes (optional) = epilogue(A . W^T) with P-plane operands
+// (P = 1 bf16, 2 bf16x3, 3 bf16x6).  K must be a multiple of 64.
+int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, const GemmEpilogue& e, float* C, int ldc,
+                   const PlaneMat* out, cudaStream_t st);
+int split_planes_launch(const float* x, long rows, int cols, int ld, const PlaneMat& out, cudaStream_t st);

@@ -1,7 +1,454 @@
-// tcgen05 GEMM path -- placeholder until the UMMA kernel lands.
+// tcgen05 / TMEM / TMA GEMM for the dense contractions of the mask networks
+// (torch.nn.Linear call sites: css/models/conformer.py:79-81,124,205-209,314-320; css/models/blstm.py:100,110,139).
+//
+//   C[m][n] = epilogue( sum_k A[m][k] * W[n][k] )          A: (M,K) K-major,  W: (N,K) K-major
+//
+// Operands live in HBM as P "planes" of bf16 (split-float: x = p0 + p1 (+ p2), each plane the bf16 rounding of
+// the remaining residue), written by the producing kernel (LayerNorm, attention, the previous GEMM's epilogue).
+//   P = 1 : plain bf16                       1 MMA  per k-step
+//   P = 2 : bf16x3  (p0q0 + p0q1 + p1q0)      3 MMAs per k-step, ~2^-17 relative product error
+//   P = 3 : bf16x6  (all terms of order < 3)  6 MMAs per k-step, fp32-class accuracy (fp32 accumulation in TMEM)
+//
+// Structure (one persistent CTA per SM, 256 threads):
+//   warp 0  TMA producer: cp.async.bulk.tensor.3d (k, row, plane) into a STAGES-deep smem ring, 128B swizzle
+//   warp 1  MMA issuer : one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16),
+//                         accumulators in TMEM, double buffered (2 x BN columns) so the epilogue overlaps the
+//                         next tile's main loop; tcgen05.commit releases smem slots / signals the epilogue
+//   warp 2  TMEM allocator
+//   warps 4-7 epilogue : tcgen05.ld (32 lanes x 32 columns per warp) -> bias / ReLU / clamp / alpha / residual ->
+//                         fp32 row-major and/or bf16 planes for the next GEMM
 #include "common.cuh"
 #include "gemm.h"
+#include <cuda.h>
+#include <cuda_bf16.h>
 
-int gemm_tc_launch(const float*, int, const float*, int, float*, int, long, int, int, GemmEpilogue, int, cudaStream_t) {
-    return GEMM_TC_UNSUPPORTED;
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;            // 64 bf16 = 128 B rows -> SWIZZLE_128B
+constexpr int UMMA_K = 16;
+constexpr int SMEM_BUDGET = 220 * 1024;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp receives lane (base_lane + t)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major operand tile, rows of 128 B, SWIZZLE_128B: 8-row groups are 1024 B apart (SBO), LBO unused (=1).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;                  // leading byte offset (ignored for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;        // stride byte offset
+    d |= (uint64_t)1 << 46;                  // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                  // SWIZZLE_128B
+    return d;
+}
+
+struct TcEpilogue {
+    const float* bias;
+    int act;
+    float alpha;
+    const float* residual;
+    int ldr;
+    float clamp_max;
+    float* c;                 // fp32 output (may be null)
+    int ldc;
+    __nv_bfloat16* planes;    // bf16 plane output (may be null)
+    long plane_stride;        // elements between planes
+    int ldp;
+    int n_planes;
+};
+
+template <int P> struct Terms;
+template <> struct Terms<1> { static constexpr int N = 1; };
+template <> struct Terms<2> { static constexpr int N = 3; };
+template <> struct Terms<3> { static constexpr int N = 6; };
+// product terms in decreasing order of magnitude: (plane of A, plane of W)
+__device__ __forceinline__ constexpr int term_a(int t) { return t == 2 ? 1 : (t == 4 ? 2 : (t == 5 ? 1 : 0)); }
+__device__ __forceinline__ constexpr int term_b(int t) { return t == 1 ? 1 : (t == 3 ? 2 : (t == 5 ? 1 : 0)); }
+
+template <int P, int BN>
+struct Cfg {
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = P * (A_BYTES + B_BYTES);
+    static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static_assert(STAGES >= 2, "tile does not fit a 2-stage ring");
+};
+
+template <int P, int BN>
+__global__ void __launch_bounds__(256, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
+               TcEpilogue ep) {
+    using C = Cfg<P, BN>;
+    constexpr int STAGES = C::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;                    // [STAGES]
+    uint64_t* empty = bars + STAGES;          // [STAGES]
+    uint64_t* tfull = bars + 2 * STAGES;      // [2]
+    uint64_t* tempty = bars + 2 * STAGES + 2; // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m_tiles = (int)((M + BM - 1) / BM), n_tiles = (N + BN - 1) / BN;
+    const int total = m_tiles * n_tiles;
+    const int kblocks = K / BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                const int mb = t / n_tiles, nb = t - mb * n_tiles;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    mbar_expect_tx(&full[stage], C::STAGE_BYTES);
+                    uint8_t* sa = smem + stage * C::STAGE_BYTES;
+                    uint8_t* sb = sa + P * C::A_BYTES;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        tma_load_3d(sa + p * C::A_BYTES, &tmA, &full[stage], kb * BK, mb * BM, p);
+                        tma_load_3d(sb + p * C::B_BYTES, &tmB, &full[stage], kb * BK, nb * BN, p);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            // instruction descriptor: D=f32, A=B=bf16, both K-major, N, M=128
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                mbar_wait(&tempty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
+                    const uint32_t sb = sa + P * C::A_BYTES;
+#pragma unroll
+                    for (int ks = 0; ks < BK / UMMA_K; ++ks) {
+#pragma unroll
+                        for (int tm = 0; tm < Terms<P>::N; ++tm) {
+                            const int pa = term_a(tm), pb = term_b(tm);
+                            const uint64_t da = make_desc(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
+                            const uint64_t db = make_desc(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
+                            tc_mma(d_tmem, da, db, idesc, (kb | ks | tm) != 0);
+                        }
+                    }
+                    tc_commit(&empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc_commit(&tfull[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue =====
+        const int q = warp - 4;               // TMEM lane quadrant == warp % 4
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int mb = t / n_tiles, nb = t - mb * n_tiles;
+            mbar_wait(&tfull[acc], acc_phase);
+            tc_fence_after();
+            const long row = (long)mb * BM + q * 32 + lane;
+            const bool row_ok = row < M;
+#pragma unroll 1
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                const int col0 = nb * BN + c0;
+                if (col0 >= N) break;                       // warp-uniform
+                uint32_t r[32];
+                tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c0, r);
+                if (row_ok) {
+                    float v[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int col = col0 + j;
+                        float x = __uint_as_float(r[j]);
+                        if (ep.bias && col < N) x += __ldg(ep.bias + col);
+                        if (ep.act == 1) x = fmaxf(x, 0.f);
+                        if (ep.clamp_max > 0.f) x = fminf(x, ep.clamp_max);
+                        v[j] = x * ep.alpha;
+                    }
+                    const bool full32 = col0 + 32 <= N;
+                    if (ep.residual) {
+                        const float* rr = ep.residual + row * ep.ldr + col0;
+                        if (full32 && (ep.ldr & 3) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) {
+                                const float4 t4 = reinterpret_cast<const float4*>(rr)[j];
+                                v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) if (col0 + j < N) v[j] += rr[j];
+                        }
+                    }
+                    if (ep.c) {
+                        float* cr = ep.c + row * ep.ldc + col0;
+                        if (full32 && (ep.ldc & 3) == 0) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                reinterpret_cast<float4*>(cr)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) if (col0 + j < N) cr[j] = v[j];
+                        }
+                    }
+                    if (ep.planes) {
+                        // split-float planes of the output (next GEMM's A operand); columns >= N are written as 0
+                        // up to the pitch so the K padding of the consumer stays clean
+                        for (int p = 0; p < ep.n_planes; ++p) {
+                            __nv_bfloat16* pr = ep.planes + p * ep.plane_stride + row * ep.ldp + col0;
+                            uint32_t w[16];
+#pragma unroll
+                            for (int j = 0; j < 16; ++j) {
+                                const float a = (col0 + 2 * j < N) ? v[2 * j] : 0.f;
+                                const float b = (col0 + 2 * j + 1 < N) ? v[2 * j + 1] : 0.f;
+                                const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
+                                v[2 * j] = a - __bfloat162float(ha);
+                                v[2 * j + 1] = b - __bfloat162float(hb);
+                                w[j] = (uint32_t)__bfloat16_as_ushort(ha) | ((uint32_t)__bfloat16_as_ushort(hb) << 16);
+                            }
+                            if (col0 + 32 <= ep.ldp) {
+#pragma unroll
+                                for (int j = 0; j < 4; ++j)
+                                    reinterpret_cast<uint4*>(pr)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+                            } else {
+                                for (int j = 0; j < 32 && col0 + j < ep.ldp; ++j)
+                                    pr[j] = __ushort_as_bfloat16((unsigned short)((w[j >> 1] >> ((j & 1) * 16)) & 0xFFFF));
+                            }
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tempty[acc]);
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    }
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) == cudaSuccess &&
+            qr == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// planes of a (rows, K) K-major bf16 matrix: element (p, r, k) at base[p*plane_stride + r*ld + k]
+static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld, long plane_stride, int planes, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    CSS_REQUIRE(fn, "gemm_tc: cuTensorMapEncodeTiled is not available from the driver");
+    CSS_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0 && (plane_stride * 2) % 16 == 0,
+                "gemm_tc: operand planes must be 16-byte aligned (ld=%d plane_stride=%ld)", ld, plane_stride);
+    cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)planes};
+    cuuint64_t strides[2] = {(cuuint64_t)ld * 2, (cuuint64_t)plane_stride * 2};
+    cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CSS_REQUIRE(r == CUDA_SUCCESS, "gemm_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return 0;
+}
+
+static int sm_count() {
+    static int n = 0;
+    if (!n) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+        if (n <= 0) n = 148;
+    }
+    return n;
+}
+
+template <int P, int BN>
+static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
+    using C = Cfg<P, BN>;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
+        attr = true;
+    }
+    const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    gemm_tc_kernel<P, BN><<<grid, 256, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    return css_check_launch("gemm_tc");
+}
+
+int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, const GemmEpilogue& e, float* C, int ldc,
+                   const PlaneMat* out, cudaStream_t st) {
+    CSS_REQUIRE(P >= 1 && P <= 3, "gemm_tc: %d planes unsupported", P);
+    CSS_REQUIRE(A.planes >= P && W.planes >= P, "gemm_tc: operands carry %d/%d planes, need %d", A.planes, W.planes, P);
+    CSS_REQUIRE(K % BK == 0 && K > 0, "gemm_tc: K=%d must be a positive multiple of %d", K, BK);
+    CSS_REQUIRE(M > 0 && N > 0 && A.ld >= K && W.ld >= K, "gemm_tc: bad shape M=%ld N=%d K=%d", M, N, K);
+    CSS_REQUIRE(C || out, "gemm_tc: no output");
+    const int BN = (P == 3 || N <= 128) ? 128 : 256;
+    CUtensorMap ta, tb;
+    int rc;
+    if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM))) return rc;
+    if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN))) return rc;
+    TcEpilogue ep = {e.bias, e.act, e.alpha, e.residual, e.ldr, e.clamp_max, C, ldc,
+                     out ? reinterpret_cast<__nv_bfloat16*>(out->ptr) : nullptr, out ? out->plane_stride : 0,
+                     out ? out->ld : 0, out ? out->planes : 0};
+    if (P == 1) return BN == 256 ? launch_cfg<1, 256>(ta, tb, M, N, K, ep, st) : launch_cfg<1, 128>(ta, tb, M, N, K, ep, st);
+    if (P == 2) return BN == 256 ? launch_cfg<2, 256>(ta, tb, M, N, K, ep, st) : launch_cfg<2, 128>(ta, tb, M, N, K, ep, st);
+    return launch_cfg<3, 128>(ta, tb, M, N, K, ep, st);
+}
+
+// fp32 (rows, cols; pitch ld) -> n_planes bf16 planes with pitch ldp; columns [cols, ldp) are zero filled
+__global__ void __launch_bounds__(256)
+split_planes_kernel(const float* __restrict__ x, long rows, int cols, int ld, __nv_bfloat16* __restrict__ out, long plane_stride,
+                    int ldp, int n_planes) {
+    const int pairs = ldp >> 1;
+    const long total = rows * pairs;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long r = i / pairs;
+        const int c = (int)(i - r * pairs) * 2;
+        float a = c < cols ? x[r * ld + c] : 0.f;
+        float b = c + 1 < cols ? x[r * ld + c + 1] : 0.f;
+        for (int p = 0; p < n_planes; ++p) {
+            const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
+            a -= __bfloat162float(ha);
+            b -= __bfloat162float(hb);
+            __nv_bfloat162 v;
+            v.x = ha; v.y = hb;
+            *reinterpret_cast<__nv_bfloat162*>(out + p * plane_stride + r * ldp + c) = v;
+        }
+    }
+}
+
+int split_planes_launch(const float* x, long rows, int cols, int ld, const PlaneMat& out, cudaStream_t st) {
+    CSS_REQUIRE(rows > 0 && cols > 0 && out.ld >= cols && (out.ld & 1) == 0, "split_planes: bad shape");
+    const long total = rows * (out.ld >> 1);
+    long grid = (total + 255) / 256;
+    if (grid > 148 * 16) grid = 148 * 16;
+    split_planes_kernel<<<(unsigned)grid, 256, 0, st>>>(x, rows, cols, ld, reinterpret_cast<__nv_bfloat16*>(out.ptr),
+                                                       out.plane_stride, out.ld, out.planes);
+    return css_check_launch("split_planes");
+}
+
+// Public test/utility entry: C = epilogue(A . W^T) on the tcgen05 path from fp32 operands.  The operands are split
+// into `planes` bf16 planes in `scratch` first (the network path keeps its activations in plane form instead).
+extern "C" size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes) {
+    const size_t kp = (size_t)((K + BK - 1) / BK) * BK;
+    return (size_t)planes * ((size_t)M + N) * kp * 2 + 512;
+}
+extern "C" int css_gemm_tc(const float* A, int lda, const float* W, int ldw, const float* bias, float* C, int ldc, long M,
+                           int N, int K, int act, float alpha, const float* residual, int ldr, float clamp_max, int planes,
+                           void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    CSS_REQUIRE(planes >= 1 && planes <= 3, "css_gemm_tc: planes must be 1..3");
+    CSS_REQUIRE(M > 0 && N > 0 && K > 0, "css_gemm_tc: empty shape");
+    CSS_REQUIRE(scratch && scratch_bytes >= css_gemm_tc_scratch_bytes(M, N, K, planes), "css_gemm_tc: scratch too small");
+    const int kp = (K + BK - 1) / BK * BK;
+    char* base = reinterpret_cast<char*>(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+    PlaneMat a = {base, M * (long)kp, kp, planes};
+    PlaneMat w = {base + (size_t)planes * M * kp * 2, (long)N * kp, kp, planes};
+    int rc;
+    if ((rc = split_planes_launch(A, M, K, lda, a, st))) return rc;
+    if ((rc = split_planes_launch(W, N, K, ldw, w, st))) return rc;
+    GemmEpilogue e = {bias, act, alpha, residual, ldr, clamp_max};
+    return gemm_tc_planes(a, w, planes, M, N, kp, e, C, ldc, nullptr, st);
 }
