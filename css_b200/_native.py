@@ -35,6 +35,10 @@ def lib():
         _lib.css_conformer_workspace_bytes.restype = ctypes.c_size_t
         _lib.css_blstm_create.restype = ctypes.c_void_p
         _lib.css_blstm_workspace_bytes.restype = ctypes.c_size_t
+        _lib.css_gemm_tc_scratch_bytes.restype = ctypes.c_size_t
+        if os.environ.get("CSS_B200_GEMM_MODE"):
+            if _lib.css_set_gemm_mode(int(os.environ["CSS_B200_GEMM_MODE"])) != 0:
+                raise NativeError(_lib.css_last_error().decode())
     return _lib
 
 
@@ -62,6 +66,15 @@ def call(name, *args):
     """Call an `int css_xxx(...)` entry point, appending the current stream, raising on error."""
     fn = getattr(lib(), name)
     check(fn(*args, stream()), name)
+
+
+def set_gemm_mode(mode):
+    """0 = fp32 SIMT, 1 = tcgen05 bf16x3 (fp32-class accuracy), 2 = tcgen05 bf16."""
+    check(lib().css_set_gemm_mode(int(mode)), "css_set_gemm_mode")
+
+
+def get_gemm_mode():
+    return int(lib().css_get_gemm_mode())
 
 
 def launch_count(reset=False):

@@ -5,8 +5,15 @@
 
 int layernorm_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
                      cudaStream_t st);
+int layernorm_planes_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
+                            void* planes, long plane_stride, int n_planes, cudaStream_t st);
 int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
                      cudaStream_t st);
+
+// warp-level tensor-core attention (attention_tc.cu): T <= 160, dk = 64; fp32 and/or bf16 plane output
+bool attention_tc_supported(int T, int dk);
+int attention_tc_launch(const float* qkv, const float* pe, int pe_rows, float* out, void* planes, long plane_stride,
+                        int n_planes, long N, int T, int H, int dk, cudaStream_t st);
 
 struct ConvModuleParams {
     const float* ln_g;      // (d)
@@ -25,3 +32,7 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
 
 // (N*T, ldm) rows [c*nb + f] -> masks (N, nb, T, C)
 int masks_layout_launch(const float* m, int ldm, float* out, long N, int T, int nb, int C, cudaStream_t st);
+
+// (x - mean_T) / (std_T + eps) over time, emitted as bf16 split planes (features.cu)
+int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* planes, long plane_stride, int ldp, int n_planes,
+                           cudaStream_t st);

@@ -7,7 +7,7 @@
 #include <new>
 #include <vector>
 
-static int g_gemm_mode = 0;
+static int g_gemm_mode = 1;   // tcgen05 bf16x3: fp32-class accuracy (masks within 1e-4 of the fp32 oracle)
 extern "C" int css_set_gemm_mode(int mode) {
     CSS_REQUIRE(mode >= 0 && mode <= 2, "css_set_gemm_mode: unknown mode %d", mode);
     g_gemm_mode = mode;
@@ -23,10 +23,49 @@ int gemm_dispatch(const float* A, int lda, const float* W, int ldw, float* C, in
     return rc;
 }
 
+// bf16 split planes of every Linear weight (tcgen05 path), built lazily on the first tensor-core forward
+struct BlockPlanes { PlaneMat ff_in_w1, ff_in_w2, wqkv, wo, ff_out_w1, ff_out_w2; };
 struct ConformerModel {
     css_conformer_desc d;
     std::vector<css_conformer_block> blk;
+    void* plane_mem = nullptr;
+    PlaneMat embed_w{}, head_w{};
+    std::vector<BlockPlanes> bp;
 };
+constexpr int kWeightPlanes = 2;
+
+static int build_weight_planes(ConformerModel* m, cudaStream_t st) {
+    if (m->plane_mem) return 0;
+    const css_conformer_desc& c = m->d;
+    const size_t d = c.d_model, f = c.d_ffn, nh = (size_t)c.num_bins * c.num_out;
+    auto bytes = [](size_t rows, size_t k) { return (kWeightPlanes * rows * k * 2 + 255) & ~(size_t)255; };
+    size_t total = bytes(d, c.ldin) + bytes(nh, d) + c.num_blocks * (2 * bytes(f, d) + 2 * bytes(d, f) + bytes(3 * d, d) + bytes(d, d));
+    cudaError_t e = cudaMalloc(&m->plane_mem, total);
+    CSS_REQUIRE(e == cudaSuccess, "conformer: cannot allocate %zu B for the bf16 weight planes: %s", total, cudaGetErrorString(e));
+    char* wp = static_cast<char*>(m->plane_mem);
+    int rc = 0;
+    auto mk = [&](const float* w, size_t rows, size_t k) {
+        PlaneMat pm = {wp, (long)(rows * k), (int)k, kWeightPlanes};
+        wp += bytes(rows, k);
+        if (!rc) rc = split_planes_launch(w, (long)rows, (int)k, (int)k, pm, st);
+        return pm;
+    };
+    m->embed_w = mk(c.embed_w, d, c.ldin);
+    m->head_w = mk(c.head_w, nh, d);
+    m->bp.resize(c.num_blocks);
+    for (int l = 0; l < c.num_blocks; ++l) {
+        const css_conformer_block& b = m->blk[l];
+        BlockPlanes& q = m->bp[l];
+        q.ff_in_w1 = mk(b.ff_in.w1, f, d);
+        q.ff_in_w2 = mk(b.ff_in.w2, d, f);
+        q.wqkv = mk(b.wqkv, 3 * d, d);
+        q.wo = mk(b.wo, d, d);
+        q.ff_out_w1 = mk(b.ff_out.w1, f, d);
+        q.ff_out_w2 = mk(b.ff_out.w2, d, f);
+    }
+    if (rc) { cudaFree(m->plane_mem); m->plane_mem = nullptr; }
+    return rc;
+}
 
 extern "C" void* css_conformer_create(const css_conformer_desc* desc, const css_conformer_block* blocks) {
     if (!desc || !blocks) { css_set_error("css_conformer_create: null descriptor"); return nullptr; }
@@ -46,7 +85,11 @@ extern "C" void* css_conformer_create(const css_conformer_desc* desc, const css_
     return m;
 }
 
-extern "C" void css_conformer_destroy(void* model) { delete static_cast<ConformerModel*>(model); }
+extern "C" void css_conformer_destroy(void* model) {
+    ConformerModel* m = static_cast<ConformerModel*>(model);
+    if (m && m->plane_mem) cudaFree(m->plane_mem);
+    delete m;
+}
 
 static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 static inline int head_pitch(const css_conformer_desc& d) { return ((d.num_bins * d.num_out + 7) / 8) * 8; }
@@ -55,7 +98,10 @@ extern "C" size_t css_conformer_workspace_bytes(const void* model, long N, int T
     const ConformerModel* m = static_cast<const ConformerModel*>(model);
     const size_t M = (size_t)N * T, d = m->d.d_model;
     const size_t wide = (size_t)(m->d.d_ffn > 3 * m->d.d_model ? m->d.d_ffn : 3 * m->d.d_model);
-    return 3 * align256(M * d * 4) + align256(M * wide * 4) + align256(M * head_pitch(m->d) * 4);
+    // fp32 path: x, y, a (M x d), h (M x wide), head;  tensor-core path adds the bf16 plane buffers of the GEMM inputs:
+    // LN output, attention output (2 x M x d each), FFN hidden (2 x M x d_ffn), features (2 x M x ldin)
+    return 3 * align256(M * d * 4) + align256(M * wide * 4) + align256(M * head_pitch(m->d) * 4) +
+           2 * align256(2 * M * d * 2) + align256(2 * M * (size_t)m->d.d_ffn * 2) + align256(2 * M * (size_t)m->d.ldin * 2);
 }
 
 static int ffn(const css_ffn_weights& w, float* x, float* y, float* h, long M, int d, int dffn, cudaStream_t st) {
@@ -67,6 +113,87 @@ static int ffn(const css_ffn_weights& w, float* x, float* y, float* h, long M, i
     if (rc) return rc;
     GemmEpilogue e2 = {w.b2, 0, 0.5f, x, d, 0.f};
     return gemm_dispatch(h, dffn, w.w2, dffn, x, d, M, d, dffn, e2, st);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core forward: every Linear runs on the tcgen05 GEMM (gemm_tc.cu) over bf16 split planes.
+// The producers of GEMM inputs (input MVN, LayerNorm, the FFN-in GEMM epilogue, attention) write planes directly.
+// ---------------------------------------------------------------------------------------------
+static int tc_gemm(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, GemmEpilogue e, float* C, int ldc,
+                   const PlaneMat* out, cudaStream_t st) {
+    css_prof_begin(0, 2.0 * (double)M * N * K, st);
+    int rc = gemm_tc_planes(A, W, P, M, N, K, e, C, ldc, out, st);
+    css_prof_end(st);
+    return rc;
+}
+
+static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& w2, float* x, const PlaneMat& yP, const PlaneMat& hP,
+                  int P, long M, int d, int dffn, cudaStream_t st) {
+    int rc = layernorm_planes_launch(x, w.ln_g, w.ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st);
+    if (rc) return rc;
+    GemmEpilogue e1 = {w.b1, 1, 1.f, nullptr, 0, 0.f};
+    if ((rc = tc_gemm(yP, w1, P, M, dffn, d, e1, nullptr, 0, &hP, st))) return rc;
+    GemmEpilogue e2 = {w.b2, 0, 0.5f, x, d, 0.f};
+    return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, nullptr, st);
+}
+
+static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks, float* head,
+                      int ld_head, char* wp, int mode, cudaStream_t st) {
+    const css_conformer_desc& c = m->d;
+    const long M = N * T;
+    const int d = c.d_model, dffn = c.d_ffn, nh = c.num_bins * c.num_out, P = (mode == 1) ? 2 : 1;
+    const size_t wide = (size_t)(dffn > 3 * d ? dffn : 3 * d);
+    float* x = (float*)wp;  wp += align256((size_t)M * d * 4);
+    float* y = (float*)wp;  wp += align256((size_t)M * d * 4);
+    float* a = (float*)wp;  wp += align256((size_t)M * d * 4);
+    float* h = (float*)wp;  wp += align256((size_t)M * wide * 4);
+    float* hd = (float*)wp; wp += align256((size_t)M * head_pitch(c) * 4);
+    PlaneMat yP = {wp, M * (long)d, d, P};        wp += align256(2 * (size_t)M * d * 2);
+    PlaneMat aP = {wp, M * (long)d, d, P};        wp += align256(2 * (size_t)M * d * 2);
+    PlaneMat hP = {wp, M * (long)dffn, dffn, P};  wp += align256(2 * (size_t)M * dffn * 2);
+    PlaneMat fP = {wp, M * (long)c.ldin, c.ldin, P};
+    int rc;
+    if ((rc = build_weight_planes(m, st))) return rc;
+    if (apply_mvn) rc = mvn_time_planes_launch(feat, N, T, c.idim, c.ldin, fP.ptr, fP.plane_stride, c.ldin, P, st);
+    else rc = split_planes_launch(feat, M, c.idim, c.ldin, fP, st);
+    if (rc) return rc;
+    GemmEpilogue ee = {c.embed_b, 0, 1.f, nullptr, 0, 0.f};
+    if ((rc = tc_gemm(fP, m->embed_w, P, M, d, c.ldin, ee, y, d, nullptr, st))) return rc;
+    if ((rc = layernorm_launch(y, c.embed_ln_g, c.embed_ln_b, x, M, d, 1e-5f, 1, st))) return rc;
+    for (int l = 0; l < c.num_blocks; ++l) {
+        const css_conformer_block& b = m->blk[l];
+        const BlockPlanes& q = m->bp[l];
+        if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, st))) return rc;
+        if ((rc = layernorm_planes_launch(x, b.att_ln_g, b.att_ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st))) return rc;
+        GemmEpilogue eq = {b.bqkv, 0, 1.f, nullptr, 0, 0.f};
+        if ((rc = tc_gemm(yP, q.wqkv, P, M, 3 * d, d, eq, h, 3 * d, nullptr, st))) return rc;
+        if (attention_tc_supported(T, d / c.heads)) {
+            if ((rc = attention_tc_launch(h, c.pe, c.pe_rows, nullptr, aP.ptr, aP.plane_stride, P, N, T, c.heads, d / c.heads, st))) return rc;
+        } else {
+            if ((rc = attention_launch(h, c.pe, c.pe_rows, a, N, T, c.heads, d / c.heads, st))) return rc;
+            if ((rc = split_planes_launch(a, M, d, d, aP, st))) return rc;
+        }
+        GemmEpilogue eo = {b.bo, 0, 1.f, x, d, 0.f};
+        if ((rc = tc_gemm(aP, q.wo, P, M, d, d, eo, x, d, nullptr, st))) return rc;
+        ConvModuleParams cp = {b.conv_ln_g, b.conv_ln_b, b.pw1_w0, b.pw1_b0, b.pw1_w1, b.pw1_b1, b.dw_w, b.dw_b,
+                               b.bn_scale, b.bn_shift, b.pw2_w, b.pw2_b, 33};
+        if ((rc = conv_module_launch(x, a, N, T, d, cp, st))) return rc;
+        { float* t = x; x = a; a = t; }
+        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, st))) return rc;
+        // block output LN: fp32 for the residual stream; the last block also feeds the head GEMM
+        const bool last = l == c.num_blocks - 1;
+        if ((rc = layernorm_planes_launch(x, b.out_ln_g, b.out_ln_b, x, M, d, 1e-5f, 0, last ? yP.ptr : nullptr, yP.plane_stride,
+                                          last ? P : 0, st))) return rc;
+    }
+    if (c.num_blocks == 0 && (rc = split_planes_launch(x, M, d, d, yP, st))) return rc;
+    if (head) {
+        GemmEpilogue eh = {c.head_b, 1, 1.f, nullptr, 0, 0.f};
+        return tc_gemm(yP, m->head_w, P, M, nh, d, eh, head, ld_head, nullptr, st);
+    }
+    const int ldh = head_pitch(c);
+    GemmEpilogue eh = {c.head_b, 1, 1.f, nullptr, 0, clamp_max};
+    if ((rc = tc_gemm(yP, m->head_w, P, M, nh, d, eh, hd, ldh, nullptr, st))) return rc;
+    return masks_layout_launch(hd, ldh, masks, N, T, c.num_bins, c.num_out, st);
 }
 
 extern "C" int css_conformer_forward(void* model, float* feat, long N, int T, int apply_mvn, float clamp_max,
@@ -82,6 +209,7 @@ extern "C" int css_conformer_forward(void* model, float* feat, long N, int T, in
     const int d = c.d_model, dffn = c.d_ffn, nh = c.num_bins * c.num_out;
     const size_t wide = (size_t)(dffn > 3 * d ? dffn : 3 * d);
     char* wp = static_cast<char*>(workspace);
+    if (g_gemm_mode != 0) return forward_tc(m, feat, N, T, apply_mvn, clamp_max, masks, head, ld_head, wp, g_gemm_mode, st);
     float* x = (float*)wp;  wp += align256((size_t)M * d * 4);
     float* y = (float*)wp;  wp += align256((size_t)M * d * 4);
     float* a = (float*)wp;  wp += align256((size_t)M * d * 4);

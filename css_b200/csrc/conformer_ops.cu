@@ -2,6 +2,23 @@
 // and the mask-head layout transform.  (css/models/conformer.py:188-303, css/executor/separator.py:100-104)
 #include "common.cuh"
 #include "conformer.h"
+#include <cuda_bf16.h>
+
+// split 4 fp32 values into bf16 planes: plane p receives the bf16 rounding of what planes < p left over
+__device__ __forceinline__ void store_split4(float4 o, __nv_bfloat16* base, long plane_stride, int n_planes) {
+    float v[4] = {o.x, o.y, o.z, o.w};
+    for (int p = 0; p < n_planes; ++p) {
+        unsigned short h[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const __nv_bfloat16 b = __float2bfloat16_rn(v[e]);
+            v[e] -= __bfloat162float(b);
+            h[e] = __bfloat16_as_ushort(b);
+        }
+        *reinterpret_cast<uint2*>(base + p * plane_stride) =
+            make_uint2((unsigned)h[0] | ((unsigned)h[1] << 16), (unsigned)h[2] | ((unsigned)h[3] << 16));
+    }
+}
 
 // ---------------------------------------------------------------------------------------------
 // LayerNorm over d (multiple of 128, <= 1024): one warp per row.  Optional fused ReLU.
@@ -9,7 +26,7 @@
 template <int VPL>   // float4 vectors per lane: d = 128 * VPL
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* x, const float* __restrict__ g, const float* __restrict__ b, float* y,
-                 long M, float eps, int relu) {
+                 long M, float eps, int relu, __nv_bfloat16* planes, long plane_stride, int n_planes) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= M) return;
@@ -41,21 +58,29 @@ layernorm_kernel(const float* x, const float* __restrict__ g, const float* __res
         o.z = (v[i].z - mean) * rstd * gg.z + bb.z;
         o.w = (v[i].w - mean) * rstd * gg.w + bb.w;
         if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
-        yr[lane + 32 * i] = o;
+        if (y) yr[lane + 32 * i] = o;
+        if (planes) store_split4(o, planes + row * d + 4 * (lane + 32 * i), plane_stride, n_planes);
     }
 }
 
 int layernorm_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
                      cudaStream_t st) {
-    CSS_REQUIRE(M > 0, "layernorm: empty input");
+    return layernorm_planes_launch(x, g, b, y, M, d, eps, relu, nullptr, 0, 0, st);
+}
+
+// y (fp32, optional) and/or bf16 split planes (pitch d) of LayerNorm(x)
+int layernorm_planes_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
+                            void* planes_v, long plane_stride, int n_planes, cudaStream_t st) {
+    __nv_bfloat16* planes = static_cast<__nv_bfloat16*>(planes_v);
+    CSS_REQUIRE(M > 0 && (y || planes), "layernorm: empty input or no output");
     CSS_REQUIRE(d % 128 == 0 && d <= 1024, "layernorm: d=%d must be a multiple of 128 and <= 1024", d);
     const unsigned grid = (unsigned)((M + 7) / 8);
-    css_prof_begin(3, 2.0 * (double)M * d * 4, st);
+    css_prof_begin(3, (double)M * d * (4.0 + (y ? 4.0 : 0.0) + 2.0 * (planes ? n_planes : 0)), st);
     switch (d / 128) {
-        case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
-        case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
-        case 4: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
-        case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu); break;
+        case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
+        case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
+        case 4: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
+        case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
         default: CSS_REQUIRE(false, "layernorm: unsupported d=%d", d);
     }
     css_prof_end(st);

@@ -1,6 +1,7 @@
 // K2: fused spectral + spatial features (css/executor/feature.py:105-134,156-175) and the
 // model-side input MVN over time (css/models/conformer.py:95, css/models/blstm.py:80).
 #include "common.cuh"
+#include <cuda_bf16.h>
 
 #define FEAT_EPS 1.1920928955078125e-07f
 #define FEAT_THREADS 288   // 9 warps cover 257 bins
@@ -140,6 +141,47 @@ extern "C" int css_features(const void* spec, long stride_d, long stride_chunk, 
     features_kernel<<<(unsigned)n_chunks, FEAT_THREADS, 0, st>>>((const float2*)spec, stride_d, stride_chunk, T, ipd_l,
                                                                  ipd_r, n_pairs, mag, feat, ldf);
     return css_check_launch("css_features");
+}
+
+// Same normalisation, written as bf16 split planes (pitch ldp >= F, padding columns zeroed) for the tcgen05 embed GEMM;
+// x is left untouched.
+__global__ void mvn_time_planes_kernel(const float* __restrict__ x, int T, int F, int ld, __nv_bfloat16* __restrict__ planes,
+                                       long plane_stride, int ldp, int n_planes) {
+    const long n = blockIdx.x;
+    const int f = blockIdx.y * blockDim.x + threadIdx.x;
+    if (f >= ldp) return;
+    __nv_bfloat16* out = planes + n * (long)T * ldp + f;
+    if (f >= F) {
+        for (int p = 0; p < n_planes; ++p)
+            for (int t = 0; t < T; ++t) out[p * plane_stride + (long)t * ldp] = __float2bfloat16_rn(0.f);
+        return;
+    }
+    const float* col = x + n * (long)T * ld + f;
+    float s = 0.f;
+    for (int t = 0; t < T; ++t) s += col[(long)t * ld];
+    const float mean = s / T;
+    float v = 0.f;
+    for (int t = 0; t < T; ++t) {
+        float d = col[(long)t * ld] - mean;
+        v += d * d;
+    }
+    const float inv = 1.f / (sqrtf(v / (T - 1)) + FEAT_EPS);
+    for (int t = 0; t < T; ++t) {
+        float r = (col[(long)t * ld] - mean) * inv;
+        for (int p = 0; p < n_planes; ++p) {
+            const __nv_bfloat16 h = __float2bfloat16_rn(r);
+            r -= __bfloat162float(h);
+            out[p * plane_stride + (long)t * ldp] = h;
+        }
+    }
+}
+
+int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* planes, long plane_stride, int ldp, int n_planes,
+                           cudaStream_t st) {
+    CSS_REQUIRE(n > 0 && T > 1 && F > 0 && ld >= F && ldp >= F, "mvn_time_planes: bad shape");
+    dim3 grid((unsigned)n, (ldp + 127) / 128);
+    mvn_time_planes_kernel<<<grid, 128, 0, st>>>(x, T, F, ld, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, n_planes);
+    return css_check_launch("mvn_time_planes");
 }
 
 extern "C" int css_mvn_time(float* x, long n, int T, int F, int ld, cudaStream_t st) {

@@ -9,14 +9,14 @@
 //   P = 2 : bf16x3  (p0q0 + p0q1 + p1q0)      3 MMAs per k-step, ~2^-17 relative product error
 //   P = 3 : bf16x6  (all terms of order < 3)  6 MMAs per k-step, fp32-class accuracy (fp32 accumulation in TMEM)
 //
-// Structure (one persistent CTA per SM, 256 threads):
+// Structure (one persistent CTA per SM, 384 threads):
 //   warp 0  TMA producer: cp.async.bulk.tensor.3d (k, row, plane) into a STAGES-deep smem ring, 128B swizzle
 //   warp 1  MMA issuer : one elected lane issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=BN, K=16),
 //                         accumulators in TMEM, double buffered (2 x BN columns) so the epilogue overlaps the
 //                         next tile's main loop; tcgen05.commit releases smem slots / signals the epilogue
 //   warp 2  TMEM allocator
-//   warps 4-7 epilogue : tcgen05.ld (32 lanes x 32 columns per warp) -> bias / ReLU / clamp / alpha / residual ->
-//                         fp32 row-major and/or bf16 planes for the next GEMM
+//   warps 4-11 epilogue: tcgen05.ld (32 lanes x 32 columns per warp) -> swizzled smem transpose -> bias / ReLU /
+//                         clamp / alpha / residual -> coalesced fp32 rows and/or bf16 planes for the next GEMM
 #include "common.cuh"
 #include "gemm.h"
 #include <cuda.h>
@@ -25,9 +25,10 @@
 namespace {
 
 constexpr int BM = 128;
-constexpr int BK = 64;            // 64 bf16 = 128 B rows -> SWIZZLE_128B
+constexpr int KPAD = 64;          // K granularity of the plane buffers (both BK choices divide it)
 constexpr int UMMA_K = 16;
-constexpr int SMEM_BUDGET = 220 * 1024;
+constexpr int EPI_STAGING = 8 * 4096;      // 8 epilogue warps x (32 rows x 32 fp32)
+constexpr int SMEM_BUDGET = 227 * 1024 - EPI_STAGING - 1024 - 256;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -84,13 +85,16 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t* r) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// K-major operand tile, rows of 128 B, SWIZZLE_128B: 8-row groups are 1024 B apart (SBO), LBO unused (=1).
+// K-major operand tile with rows of BK bf16 (128 B -> SWIZZLE_128B, 64 B -> SWIZZLE_64B): 8-row groups are
+// 8*row bytes apart (SBO), LBO unused (=1).
+template <int BK>
 __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
+    static_assert(BK == 64 || BK == 32, "BK must be 64 (128B swizzle) or 32 (64B swizzle)");
     uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)1 << 16;                  // leading byte offset (ignored for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;        // stride byte offset
-    d |= (uint64_t)1 << 46;                  // descriptor version (Blackwell)
-    d |= (uint64_t)2 << 61;                  // SWIZZLE_128B
+    d |= (uint64_t)1 << 16;                              // leading byte offset (ignored for swizzled K-major)
+    d |= (uint64_t)((8 * BK * 2) >> 4) << 32;            // stride byte offset
+    d |= (uint64_t)1 << 46;                              // descriptor version (Blackwell)
+    d |= (uint64_t)(BK == 64 ? 2 : 4) << 61;             // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
 
@@ -117,22 +121,22 @@ template <> struct Terms<3> { static constexpr int N = 6; };
 __device__ __forceinline__ constexpr int term_a(int t) { return t == 2 ? 1 : (t == 4 ? 2 : (t == 5 ? 1 : 0)); }
 __device__ __forceinline__ constexpr int term_b(int t) { return t == 1 ? 1 : (t == 3 ? 2 : (t == 5 ? 1 : 0)); }
 
-template <int P, int BN>
+template <int P, int BN, int BK>
 struct Cfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = P * (A_BYTES + B_BYTES);
     static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
-    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_STAGING;
     static_assert(STAGES >= 2, "tile does not fit a 2-stage ring");
 };
 
-template <int P, int BN>
-__global__ void __launch_bounds__(256, 1)
+template <int P, int BN, int BK>
+__global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
                TcEpilogue ep) {
-    using C = Cfg<P, BN>;
+    using C = Cfg<P, BN, BK>;
     constexpr int STAGES = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -154,7 +158,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     if (warp == 1 && lane == 0) {
         for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 4); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 2) {
@@ -207,8 +211,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                         for (int tm = 0; tm < Terms<P>::N; ++tm) {
                             const int pa = term_a(tm), pb = term_b(tm);
-                            const uint64_t da = make_desc(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
-                            const uint64_t db = make_desc(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
+                            const uint64_t da = make_desc<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
+                            const uint64_t db = make_desc<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
                             tc_mma(d_tmem, da, db, idesc, (kb | ks | tm) != 0);
                         }
                     }
@@ -221,83 +225,100 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
         }
     } else if (warp >= 4) {
-        // ===== epilogue =====
-        const int q = warp - 4;               // TMEM lane quadrant == warp % 4
+        // ===== epilogue (8 warps): warp e drains TMEM lanes 32*(e%4).. of the column half e/4 =====
+        const int e = warp - 4;
+        const int q = e & 3;                  // TMEM lane quadrant == warp % 4
+        const int chalf = e >> 2;
+        float4* stg = reinterpret_cast<float4*>(smem + STAGES * C::STAGE_BYTES + 256) + e * 256;   // 4 KB per warp
+        const int cg = lane & 7, rsub = lane >> 3;
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int mb = t / n_tiles, nb = t - mb * n_tiles;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
-            const long row = (long)mb * BM + q * 32 + lane;
-            const bool row_ok = row < M;
+            const long row_base = (long)mb * BM + q * 32;
 #pragma unroll 1
-            for (int c0 = 0; c0 < BN; c0 += 32) {
+            for (int cc = 0; cc < BN / 64; ++cc) {
+                const int c0 = chalf * (BN / 2) + cc * 32;
                 const int col0 = nb * BN + c0;
-                if (col0 >= N) break;                       // warp-uniform
+                if (col0 >= N && (!ep.planes || col0 >= ep.ldp)) break;          // warp-uniform
                 uint32_t r[32];
                 tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c0, r);
-                if (row_ok) {
-                    float v[32];
+                // phase A: thread = row; 16-byte pieces XOR-swizzled by the row so both phases are conflict-free
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const int col = col0 + j;
-                        float x = __uint_as_float(r[j]);
-                        if (ep.bias && col < N) x += __ldg(ep.bias + col);
-                        if (ep.act == 1) x = fmaxf(x, 0.f);
-                        if (ep.clamp_max > 0.f) x = fminf(x, ep.clamp_max);
-                        v[j] = x * ep.alpha;
-                    }
-                    const bool full32 = col0 + 32 <= N;
-                    if (ep.residual) {
-                        const float* rr = ep.residual + row * ep.ldr + col0;
-                        if (full32 && (ep.ldr & 3) == 0) {
+                for (int j = 0; j < 8; ++j)
+                    stg[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                                                    __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+                __syncwarp();
+                // phase B: 8 lanes cover one 128-byte row segment -> coalesced global traffic
+                const int col = col0 + cg * 4;
+                float b4[4] = {0.f, 0.f, 0.f, 0.f};
+                if (ep.bias) {
 #pragma unroll
-                            for (int j = 0; j < 8; ++j) {
-                                const float4 t4 = reinterpret_cast<const float4*>(rr)[j];
-                                v[4 * j] += t4.x; v[4 * j + 1] += t4.y; v[4 * j + 2] += t4.z; v[4 * j + 3] += t4.w;
-                            }
-                        } else {
+                    for (int i = 0; i < 4; ++i) if (col + i < N) b4[i] = __ldg(ep.bias + col + i);
+                }
+                const bool vec_ok = col + 4 <= N;
+                // the residual may alias C (x <- x + ...): fetch all of this chunk's residual rows before any store,
+                // otherwise every load would have to wait for the previous store
+                float4 res4[8];
+                if (ep.residual) {
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) if (col0 + j < N) v[j] += rr[j];
-                        }
-                    }
-                    if (ep.c) {
-                        float* cr = ep.c + row * ep.ldc + col0;
-                        if (full32 && (ep.ldc & 3) == 0) {
-#pragma unroll
-                            for (int j = 0; j < 8; ++j)
-                                reinterpret_cast<float4*>(cr)[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                        } else {
-#pragma unroll
-                            for (int j = 0; j < 32; ++j) if (col0 + j < N) cr[j] = v[j];
-                        }
-                    }
-                    if (ep.planes) {
-                        // split-float planes of the output (next GEMM's A operand); columns >= N are written as 0
-                        // up to the pitch so the K padding of the consumer stays clean
-                        for (int p = 0; p < ep.n_planes; ++p) {
-                            __nv_bfloat16* pr = ep.planes + p * ep.plane_stride + row * ep.ldp + col0;
-                            uint32_t w[16];
-#pragma unroll
-                            for (int j = 0; j < 16; ++j) {
-                                const float a = (col0 + 2 * j < N) ? v[2 * j] : 0.f;
-                                const float b = (col0 + 2 * j + 1 < N) ? v[2 * j + 1] : 0.f;
-                                const __nv_bfloat16 ha = __float2bfloat16_rn(a), hb = __float2bfloat16_rn(b);
-                                v[2 * j] = a - __bfloat162float(ha);
-                                v[2 * j + 1] = b - __bfloat162float(hb);
-                                w[j] = (uint32_t)__bfloat16_as_ushort(ha) | ((uint32_t)__bfloat16_as_ushort(hb) << 16);
-                            }
-                            if (col0 + 32 <= ep.ldp) {
-#pragma unroll
-                                for (int j = 0; j < 4; ++j)
-                                    reinterpret_cast<uint4*>(pr)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+                    for (int it = 0; it < 8; ++it) {
+                        const long row = row_base + it * 4 + rsub;
+                        res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (row < M) {
+                            const float* rp = ep.residual + row * ep.ldr + col;
+                            if (vec_ok && (ep.ldr & 3) == 0) {
+                                res4[it] = *reinterpret_cast<const float4*>(rp);
                             } else {
-                                for (int j = 0; j < 32 && col0 + j < ep.ldp; ++j)
-                                    pr[j] = __ushort_as_bfloat16((unsigned short)((w[j >> 1] >> ((j & 1) * 16)) & 0xFFFF));
+                                if (col < N) res4[it].x = rp[0];
+                                if (col + 1 < N) res4[it].y = rp[1];
+                                if (col + 2 < N) res4[it].z = rp[2];
+                                if (col + 3 < N) res4[it].w = rp[3];
                             }
                         }
                     }
                 }
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int rr = it * 4 + rsub;
+                    const long row = row_base + rr;
+                    const float4 x4 = stg[rr * 8 + (cg ^ (rr & 7))];
+                    if (row >= M) continue;
+                    float v[4] = {x4.x + b4[0], x4.y + b4[1], x4.z + b4[2], x4.w + b4[3]};
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        if (ep.act == 1) v[i] = fmaxf(v[i], 0.f);
+                        if (ep.clamp_max > 0.f) v[i] = fminf(v[i], ep.clamp_max);
+                        v[i] *= ep.alpha;
+                    }
+                    if (ep.residual) { v[0] += res4[it].x; v[1] += res4[it].y; v[2] += res4[it].z; v[3] += res4[it].w; }
+                    if (ep.c) {
+                        float* cp = ep.c + row * ep.ldc + col;
+                        if (vec_ok && (ep.ldc & 3) == 0) {
+                            *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) if (col + i < N) cp[i] = v[i];
+                        }
+                    }
+                    if (ep.planes && col + 4 <= ep.ldp) {
+                        // split-float planes of the output (next GEMM's A operand); columns in [N, ldp) are zeroed
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) if (col + i >= N) v[i] = 0.f;
+                        for (int p = 0; p < ep.n_planes; ++p) {
+                            const __nv_bfloat162 h01 = __floats2bfloat162_rn(v[0], v[1]);
+                            const __nv_bfloat162 h23 = __floats2bfloat162_rn(v[2], v[3]);
+                            v[0] -= __bfloat162float(h01.x); v[1] -= __bfloat162float(h01.y);
+                            v[2] -= __bfloat162float(h23.x); v[3] -= __bfloat162float(h23.y);
+                            uint2 w;
+                            w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                            w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                            *reinterpret_cast<uint2*>(ep.planes + p * ep.plane_stride + row * ep.ldp + col) = w;
+                        }
+                    }
+                }
+                __syncwarp();
             }
             tc_fence_before();
             __syncwarp();
@@ -336,7 +357,8 @@ static EncodeTiledFn encode_fn() {
 }
 
 // planes of a (rows, K) K-major bf16 matrix: element (p, r, k) at base[p*plane_stride + r*ld + k]
-static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld, long plane_stride, int planes, int box_rows) {
+static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld, long plane_stride, int planes, int box_rows,
+                    int BK) {
     EncodeTiledFn fn = encode_fn();
     CSS_REQUIRE(fn, "gemm_tc: cuTensorMapEncodeTiled is not available from the driver");
     CSS_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0 && (plane_stride * 2) % 16 == 0,
@@ -346,7 +368,7 @@ static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld
     cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     CSS_REQUIRE(r == CUDA_SUCCESS, "gemm_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
     return 0;
@@ -363,39 +385,49 @@ static int sm_count() {
     return n;
 }
 
-template <int P, int BN>
-static int launch_cfg(const CUtensorMap& ta, const CUtensorMap& tb, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
-    using C = Cfg<P, BN>;
+template <int P, int BN, int BK>
+static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
+    using C = Cfg<P, BN, BK>;
+    CUtensorMap ta, tb;
+    int rc;
+    if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
+    if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
         attr = true;
     }
     const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    gemm_tc_kernel<P, BN><<<grid, 256, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    gemm_tc_kernel<P, BN, BK><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     return css_check_launch("gemm_tc");
 }
+
+static int g_tc_variant = 1;   // 0: BK=64 / 128B swizzle, 1: BK=32 / 64B swizzle (deeper ring)
+extern "C" void css_gemm_tc_variant(int v) { g_tc_variant = v; }
 
 int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, const GemmEpilogue& e, float* C, int ldc,
                    const PlaneMat* out, cudaStream_t st) {
     CSS_REQUIRE(P >= 1 && P <= 3, "gemm_tc: %d planes unsupported", P);
     CSS_REQUIRE(A.planes >= P && W.planes >= P, "gemm_tc: operands carry %d/%d planes, need %d", A.planes, W.planes, P);
-    CSS_REQUIRE(K % BK == 0 && K > 0, "gemm_tc: K=%d must be a positive multiple of %d", K, BK);
     CSS_REQUIRE(M > 0 && N > 0 && A.ld >= K && W.ld >= K, "gemm_tc: bad shape M=%ld N=%d K=%d", M, N, K);
     CSS_REQUIRE(C || out, "gemm_tc: no output");
-    const int BN = (P == 3 || N <= 128) ? 128 : 256;
-    CUtensorMap ta, tb;
-    int rc;
-    if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM))) return rc;
-    if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN))) return rc;
+    CSS_REQUIRE(K % KPAD == 0 && K > 0, "gemm_tc: K=%d must be a positive multiple of %d", K, KPAD);
     TcEpilogue ep = {e.bias, e.act, e.alpha, e.residual, e.ldr, e.clamp_max, C, ldc,
                      out ? reinterpret_cast<__nv_bfloat16*>(out->ptr) : nullptr, out ? out->plane_stride : 0,
                      out ? out->ld : 0, out ? out->planes : 0};
-    if (P == 1) return BN == 256 ? launch_cfg<1, 256>(ta, tb, M, N, K, ep, st) : launch_cfg<1, 128>(ta, tb, M, N, K, ep, st);
-    if (P == 2) return BN == 256 ? launch_cfg<2, 256>(ta, tb, M, N, K, ep, st) : launch_cfg<2, 128>(ta, tb, M, N, K, ep, st);
-    return launch_cfg<3, 128>(ta, tb, M, N, K, ep, st);
+    const bool wide = N > 128;
+    const int v = g_tc_variant;
+    if (P == 1) {
+        if (!wide) return launch_cfg<1, 128, 64>(A, W, M, N, K, ep, st);
+        return v == 1 ? launch_cfg<1, 256, 32>(A, W, M, N, K, ep, st) : launch_cfg<1, 256, 64>(A, W, M, N, K, ep, st);
+    }
+    if (P == 2) {
+        if (!wide) return launch_cfg<2, 128, 64>(A, W, M, N, K, ep, st);
+        return v == 1 ? launch_cfg<2, 256, 32>(A, W, M, N, K, ep, st) : launch_cfg<2, 256, 64>(A, W, M, N, K, ep, st);
+    }
+    return v == 1 ? launch_cfg<3, 256, 32>(A, W, M, N, K, ep, st) : launch_cfg<3, 128, 64>(A, W, M, N, K, ep, st);
 }
 
 // fp32 (rows, cols; pitch ld) -> n_planes bf16 planes with pitch ldp; columns [cols, ldp) are zero filled
@@ -433,7 +465,7 @@ int split_planes_launch(const float* x, long rows, int cols, int ld, const Plane
 // Public test/utility entry: C = epilogue(A . W^T) on the tcgen05 path from fp32 operands.  The operands are split
 // into `planes` bf16 planes in `scratch` first (the network path keeps its activations in plane form instead).
 extern "C" size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes) {
-    const size_t kp = (size_t)((K + BK - 1) / BK) * BK;
+    const size_t kp = (size_t)((K + KPAD - 1) / KPAD) * KPAD;
     return (size_t)planes * ((size_t)M + N) * kp * 2 + 512;
 }
 extern "C" int css_gemm_tc(const float* A, int lda, const float* W, int ldw, const float* bias, float* C, int ldc, long M,
@@ -442,7 +474,7 @@ extern "C" int css_gemm_tc(const float* A, int lda, const float* W, int ldw, con
     CSS_REQUIRE(planes >= 1 && planes <= 3, "css_gemm_tc: planes must be 1..3");
     CSS_REQUIRE(M > 0 && N > 0 && K > 0, "css_gemm_tc: empty shape");
     CSS_REQUIRE(scratch && scratch_bytes >= css_gemm_tc_scratch_bytes(M, N, K, planes), "css_gemm_tc: scratch too small");
-    const int kp = (K + BK - 1) / BK * BK;
+    const int kp = (K + KPAD - 1) / KPAD * KPAD;
     char* base = reinterpret_cast<char*>(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
     PlaneMat a = {base, M * (long)kp, kp, planes};
     PlaneMat w = {base + (size_t)planes * M * kp * 2, (long)N * kp, kp, planes};
@@ -450,5 +482,8 @@ extern "C" int css_gemm_tc(const float* A, int lda, const float* W, int ldw, con
     if ((rc = split_planes_launch(A, M, K, lda, a, st))) return rc;
     if ((rc = split_planes_launch(W, N, K, ldw, w, st))) return rc;
     GemmEpilogue e = {bias, act, alpha, residual, ldr, clamp_max};
-    return gemm_tc_planes(a, w, planes, M, N, kp, e, C, ldc, nullptr, st);
+    css_prof_begin(0, 2.0 * (double)M * N * K, st);
+    rc = gemm_tc_planes(a, w, planes, M, N, kp, e, C, ldc, nullptr, st);
+    css_prof_end(st);
+    return rc;
 }

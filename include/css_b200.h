@@ -48,6 +48,9 @@ int css_layernorm(const float* x, const float* g, const float* b, float* y, long
 /* css/models/conformer.py:229-250 (MultiHeadedAttention core with relative position keys) */
 int css_relpos_attention(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
                          css_stream_t stream);
+/* same contract on the warp-level tensor-core path (mma.sync bf16, three-term split, fp32 accumulate); T <= 160 */
+int css_relpos_attention_tc(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
+                            css_stream_t stream);
 /* css/executor/separator.py:100-104: (N*T, C*nb) -> (N, nb, T, C) */
 int css_masks_layout(const float* m, int ldm, float* out, long N, int T, int nb, int C, css_stream_t stream);
 
@@ -131,7 +134,14 @@ int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scrat
 int css_pit_mse(const float* est, const float* tgt, long B, int K, long n, double* pair_ws, float* loss_b, int* perm,
                 float* loss, float* grad, float gscale, css_stream_t stream);
 
-/* 0 = exact fp32 SIMT, 1 = tcgen05 bf16x3 split (fp32-accurate), 2 = tcgen05 bf16 */
+/* tcgen05/TMEM GEMM from fp32 operands (same contract as css_gemm_f32): operands are split into `planes` bf16 planes
+ * in `scratch` (1 = bf16, 2 = bf16x3, 3 = bf16x6 product terms), accumulation in fp32 */
+size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes);
+int css_gemm_tc(const float* A, int lda, const float* W, int ldw, const float* bias, float* C, int ldc, long M, int N,
+                int K, int act, float alpha, const float* residual, int ldr, float clamp_max, int planes, void* scratch,
+                size_t scratch_bytes, css_stream_t stream);
+
+/* GEMM engine of the mask networks: 0 = fp32 SIMT, 1 = tcgen05 bf16x3 split (fp32-class accuracy), 2 = tcgen05 bf16 */
 int css_set_gemm_mode(int mode);
 int css_get_gemm_mode(void);
 

@@ -135,6 +135,42 @@ def test_gemm_f32(cuda, M, N, K, act, alpha, res, clamp):
     assert rel_inf(C[:, :N], ref) < 1e-5
 
 
+@pytest.mark.parametrize("planes,tol", [(1, 1.5e-2), (2, 3e-5), (3, 1.5e-5)])
+@pytest.mark.parametrize("M,N,K,act,alpha,res,clamp", [
+    (300, 256, 1799, 0, 1.0, False, 0.0),
+    (150, 1024, 256, 1, 1.0, False, 0.0),
+    (1000, 256, 1024, 0, 0.5, True, 0.0),
+    (77, 771, 256, 1, 1.0, False, 1.0),
+    (40000, 768, 256, 0, 1.0, False, 0.0),
+])
+def test_gemm_tcgen05(cuda, planes, tol, M, N, K, act, alpha, res, clamp):
+    """tcgen05/TMEM GEMM over bf16 split planes against fp64 (1 plane = bf16, 2 = bf16x3, 3 = bf16x6)."""
+    nv = _nv()
+    g = torch.Generator().manual_seed(M + N)
+    A = torch.randn(M, K, generator=g)
+    W = torch.randn(N, K, generator=g) / math.sqrt(K)
+    bias = torch.randn(N, generator=g)
+    R = torch.randn(M, N, generator=g) if res else None
+    ldc = (N + 7) // 8 * 8
+    C = torch.zeros(M, ldc, device=cuda)
+    Ad, Wd, bd = A.to(cuda), W.to(cuda), bias.to(cuda)
+    Rd = R.to(cuda) if res else None
+    nb = nv.lib().css_gemm_tc_scratch_bytes(nv.c_long(M), nv.c_int(N), nv.c_int(K), nv.c_int(planes))
+    scratch = torch.empty(nb, dtype=torch.uint8, device=cuda)
+    nv.call("css_gemm_tc", nv.ptr(Ad), nv.c_int(K), nv.ptr(Wd), nv.c_int(K), nv.ptr(bd), nv.ptr(C), nv.c_int(ldc),
+            nv.c_long(M), nv.c_int(N), nv.c_int(K), nv.c_int(act), nv.c_float(alpha), nv.ptr(Rd), nv.c_int(N),
+            nv.c_float(clamp), nv.c_int(planes), nv.ptr(scratch), nv.c_size_t(nb))
+    ref = A.double() @ W.double().t() + bias.double()
+    if act:
+        ref = ref.relu()
+    if clamp > 0:
+        ref = ref.clamp(max=clamp)
+    ref = ref * alpha
+    if res:
+        ref = ref + R.double()
+    assert rel_inf(C[:, :N], ref) < tol
+
+
 @pytest.mark.parametrize("d", [256, 512, 1024])
 def test_layernorm(cuda, d):
     nv = _nv()
@@ -147,8 +183,10 @@ def test_layernorm(cuda, d):
     assert rel_inf(y, torch.nn.functional.layer_norm(x, (d,), w, b, 1e-5)) < 1e-5
 
 
-@pytest.mark.parametrize("T", [150, 37, 250])
-def test_relpos_attention(cuda, T):
+@pytest.mark.parametrize("T,entry", [(150, "css_relpos_attention"), (37, "css_relpos_attention"), (250, "css_relpos_attention"),
+                                     (150, "css_relpos_attention_tc"), (37, "css_relpos_attention_tc"),
+                                     (160, "css_relpos_attention_tc"), (1, "css_relpos_attention_tc")])
+def test_relpos_attention(cuda, T, entry):
     nv = _nv()
     g = torch.Generator().manual_seed(T)
     N, H, dk = 3, 4, 64
@@ -156,18 +194,29 @@ def test_relpos_attention(cuda, T):
     pe = torch.randn(2000, dk, generator=g) * 0.5
     out = torch.empty(N * T, H * dk, device=cuda)
     qd, pd = qkv.to(cuda), pe.to(cuda)
-    nv.call("css_relpos_attention", nv.ptr(qd), nv.ptr(pd), nv.c_int(2000), nv.ptr(out), nv.c_long(N), nv.c_int(T), nv.c_int(H), nv.c_int(dk))
+    nv.call(entry, nv.ptr(qd), nv.ptr(pd), nv.c_int(2000), nv.ptr(out), nv.c_long(N), nv.c_int(T), nv.c_int(H), nv.c_int(dk))
     q, k, v = (t.view(N, T, H, dk).transpose(1, 2).double() for t in qkv.chunk(3, dim=1))
     idx = torch.arange(T)
     pos = pe.double()[(idx[:, None] - idx[None, :]).clamp(-1000, 999) + 1000]        # (T,T,dk)
     sc = (q @ k.transpose(-1, -2) + torch.einsum("nhid,ijd->nhij", q, pos)) / math.sqrt(dk)
     ref = (torch.softmax(sc, -1) @ v).transpose(1, 2).reshape(N * T, H * dk)
-    assert rel_inf(out, ref) < 1e-5
+    # fp32 SIMT kernel: 1e-5; tensor-core kernel (three-term bf16 split, ~2^-17 per product): 3e-5
+    assert rel_inf(out, ref) < (3e-5 if entry.endswith("_tc") else 1e-5)
+
+
+@pytest.fixture(params=[0, 1])
+def gemm_mode(request):
+    """0 = fp32 SIMT GEMMs, 1 = tcgen05 bf16x3 GEMMs (both are fp32-parity modes)."""
+    nv = _nv()
+    old = nv.get_gemm_mode()
+    nv.set_gemm_mode(request.param)
+    yield request.param
+    nv.set_gemm_mode(old)
 
 
 @pytest.mark.parametrize("N,T", [(2, 150), (3, 37), (1, 250)])
-def test_conformer_forward_vs_oracle(cuda, N, T):
-    """Whole network (2 blocks, idim 1799): LN, GEMMs, rel-pos MHSA, conv module, head.  fp32 path: 1e-4."""
+def test_conformer_forward_vs_oracle(cuda, gemm_mode, N, T):
+    """Whole network (2 blocks, idim 1799): LN, GEMMs, rel-pos MHSA, conv module, head.  fp32-parity modes: 1e-4."""
     model = golden_conformer(num_blocks=2)
     sd = cpu_state_dict(model)
     g = torch.Generator().manual_seed(N * 1000 + T)
@@ -181,7 +230,26 @@ def test_conformer_forward_vs_oracle(cuda, N, T):
     assert rel_inf(y_pred, y_o) < 1e-4
 
 
-def test_conformer_golden_masks(cuda, golden):
+def test_conformer_bf16_mode_bound(cuda):
+    """Plain bf16 tensor-core mode: stated looser bound (masks abs <= 5e-2 on a 2-block net)."""
+    nv = _nv()
+    model = golden_conformer(num_blocks=2)
+    sd = cpu_state_dict(model)
+    g = torch.Generator().manual_seed(5)
+    f = torch.randn(2, 150, 1799, generator=g) * 2 + 0.3
+    old = nv.get_gemm_mode()
+    nv.set_gemm_mode(2)
+    try:
+        _, masks = model.to(cuda)(f.to(cuda))
+    finally:
+        nv.set_gemm_mode(old)
+    with torch.no_grad():
+        _, m_o = O.model_forward(f, sd)
+    for a, b in zip(masks, m_o):
+        assert float((a.cpu() - b).abs().max()) < 5e-2
+
+
+def test_conformer_golden_masks(cuda, gemm_mode, golden):
     """Reference-generated masks for the first two chunks of case A (tests/golden/make_golden.py)."""
     from css_b200.executor.feature import FeatureExtractor
 
