@@ -12,8 +12,9 @@ int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out,
 
 // warp-level tensor-core attention (attention_tc.cu): T <= 160, dk = 64; fp32 and/or bf16 plane output
 bool attention_tc_supported(int T, int dk);
-int attention_tc_launch(const float* qkv, const float* pe, int pe_rows, float* out, void* planes, long plane_stride,
-                        int n_planes, long N, int T, int H, int dk, cudaStream_t st);
+int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_planes, const void* pe_planes, long pe_plane_stride,
+                        int pe_rows, float* out, void* planes, long plane_stride, int n_planes, long N, int T, int H, int dk,
+                        cudaStream_t st);
 
 struct ConvModuleParams {
     const float* ln_g;      // (d)

@@ -29,7 +29,7 @@ struct ConformerModel {
     css_conformer_desc d;
     std::vector<css_conformer_block> blk;
     void* plane_mem = nullptr;
-    PlaneMat embed_w{}, head_w{};
+    PlaneMat embed_w{}, head_w{}, pe{};
     std::vector<BlockPlanes> bp;
 };
 constexpr int kWeightPlanes = 2;
@@ -39,7 +39,8 @@ static int build_weight_planes(ConformerModel* m, cudaStream_t st) {
     const css_conformer_desc& c = m->d;
     const size_t d = c.d_model, f = c.d_ffn, nh = (size_t)c.num_bins * c.num_out;
     auto bytes = [](size_t rows, size_t k) { return (kWeightPlanes * rows * k * 2 + 255) & ~(size_t)255; };
-    size_t total = bytes(d, c.ldin) + bytes(nh, d) + c.num_blocks * (2 * bytes(f, d) + 2 * bytes(d, f) + bytes(3 * d, d) + bytes(d, d));
+    const size_t dk = d / c.heads;
+    size_t total = bytes(d, c.ldin) + bytes(nh, d) + (c.pe ? bytes(c.pe_rows, dk) : 0) + c.num_blocks * (2 * bytes(f, d) + 2 * bytes(d, f) + bytes(3 * d, d) + bytes(d, d));
     cudaError_t e = cudaMalloc(&m->plane_mem, total);
     CSS_REQUIRE(e == cudaSuccess, "conformer: cannot allocate %zu B for the bf16 weight planes: %s", total, cudaGetErrorString(e));
     char* wp = static_cast<char*>(m->plane_mem);
@@ -52,6 +53,7 @@ static int build_weight_planes(ConformerModel* m, cudaStream_t st) {
     };
     m->embed_w = mk(c.embed_w, d, c.ldin);
     m->head_w = mk(c.head_w, nh, d);
+    if (c.pe) m->pe = mk(c.pe, c.pe_rows, dk);
     m->bp.resize(c.num_blocks);
     for (int l = 0; l < c.num_blocks; ++l) {
         const css_conformer_block& b = m->blk[l];
@@ -166,10 +168,14 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
         if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, st))) return rc;
         if ((rc = layernorm_planes_launch(x, b.att_ln_g, b.att_ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st))) return rc;
         GemmEpilogue eq = {b.bqkv, 0, 1.f, nullptr, 0, 0.f};
-        if ((rc = tc_gemm(yP, q.wqkv, P, M, 3 * d, d, eq, h, 3 * d, nullptr, st))) return rc;
         if (attention_tc_supported(T, d / c.heads)) {
-            if ((rc = attention_tc_launch(h, c.pe, c.pe_rows, nullptr, aP.ptr, aP.plane_stride, P, N, T, c.heads, d / c.heads, st))) return rc;
+            // Q, K, V leave the GEMM epilogue as bf16 planes (in the `h` region) and feed the tensor-core attention directly
+            PlaneMat qP = {h, M * (long)(3 * d), 3 * d, P};
+            if ((rc = tc_gemm(yP, q.wqkv, P, M, 3 * d, d, eq, nullptr, 0, &qP, st))) return rc;
+            if ((rc = attention_tc_launch(qP.ptr, qP.plane_stride, P, c.pe ? m->pe.ptr : nullptr, m->pe.plane_stride, c.pe_rows,
+                                          nullptr, aP.ptr, aP.plane_stride, P, N, T, c.heads, d / c.heads, st))) return rc;
         } else {
+            if ((rc = tc_gemm(yP, q.wqkv, P, M, 3 * d, d, eq, h, 3 * d, nullptr, st))) return rc;
             if ((rc = attention_launch(h, c.pe, c.pe_rows, a, N, T, c.heads, d / c.heads, st))) return rc;
             if ((rc = split_planes_launch(a, M, d, d, aP, st))) return rc;
         }

@@ -234,21 +234,26 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 // side live in shared memory; thread c then slides the taps of channel c down the time axis.
 // ---------------------------------------------------------------------------------------------
 #define CM_D 256
-#define CM_TT 160
 #define CM_HALO 16
 #define CM_TAPS (2 * CM_HALO + 1)
+#define CM_THREADS 1024
+#define CM_MAX_ROWS 220          // (tile + 2*halo) rows of 1 KB each must fit in shared memory
+#define CM_OUT 8                 // outputs per register pass of the depthwise filter
 
-__global__ void __launch_bounds__(CM_D)
-conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, ConvModuleParams p) {
-    extern __shared__ float U[];   // [(CM_TT + 2*CM_HALO)][CM_D]
+// One CTA per (sequence, time tile); the whole 150-frame chunk is one tile, so nothing is recomputed.
+// Phase 1: 32 warps, one row each: LayerNorm + scalar GLU into shared memory (zero rows outside [0, T)).
+// Phase 2: thread = (channel, quarter of the tile); 8 outputs are produced per pass from 40 shared-memory
+// reads (5 per output instead of 33), taps and accumulators in registers.
+__global__ void __launch_bounds__(CM_THREADS, 1)
+conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, int tile_len, ConvModuleParams p) {
+    extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D]
     const long n = blockIdx.x;
-    const int t0 = blockIdx.y * CM_TT;
-    const int tile = min(CM_TT, T - t0);
+    const int t0 = blockIdx.y * tile_len;
+    const int tile = min(tile_len, T - t0);
     const int rows = tile + 2 * CM_HALO;
     const float* xs = x + n * (long)T * CM_D;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // phase 1: LN + gate, one warp per row
-    for (int r = warp; r < rows; r += CM_D / 32) {
+    for (int r = warp; r < rows; r += CM_THREADS / 32) {
         const int t = t0 - CM_HALO + r;
         float4* urow = reinterpret_cast<float4*>(U + r * CM_D);
         if (t < 0 || t >= T) {
@@ -283,20 +288,34 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
         }
     }
     __syncthreads();
-    // phase 2: depthwise taps of channel c
-    const int c = threadIdx.x;
+    const int c = threadIdx.x & (CM_D - 1), part = threadIdx.x >> 8;
     float w[CM_TAPS];
 #pragma unroll
     for (int k = 0; k < CM_TAPS; ++k) w[k] = p.dw_w[c * CM_TAPS + k];
     const float bias = p.dw_b[c], sc = p.bn_scale[c], sh = p.bn_shift[c];
     float* os = out + n * (long)T * CM_D;
-    for (int tt = 0; tt < tile; ++tt) {
-        float acc = bias;
+    const int per = ((tile + 4 * CM_OUT - 1) / (4 * CM_OUT)) * CM_OUT;       // multiple of CM_OUT
+    const int t_end = min(tile, (part + 1) * per);
+    for (int tt = part * per; tt < t_end; tt += CM_OUT) {
+        float acc[CM_OUT];
 #pragma unroll
-        for (int k = 0; k < CM_TAPS; ++k) acc = fmaf(w[k], U[(tt + k) * CM_D + c], acc);
-        float v = fmaxf(acc * sc + sh, 0.f) * p.pw2_w + p.pw2_b;
-        const long idx = (long)(t0 + tt) * CM_D + c;
-        os[idx] = xs[idx] + v;
+        for (int j = 0; j < CM_OUT; ++j) acc[j] = bias;
+#pragma unroll
+        for (int kk = 0; kk < CM_TAPS + CM_OUT - 1; ++kk) {
+            const int r = tt + kk;
+            const float u = (r < rows) ? U[r * CM_D + c] : 0.f;
+#pragma unroll
+            for (int j = 0; j < CM_OUT; ++j)
+                if (kk - j >= 0 && kk - j < CM_TAPS) acc[j] = fmaf(w[kk - j], u, acc[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < CM_OUT; ++j) {
+            if (tt + j < t_end) {
+                const float v = fmaxf(acc[j] * sc + sh, 0.f) * p.pw2_w + p.pw2_b;
+                const long idx = (long)(t0 + tt + j) * CM_D + c;
+                os[idx] = xs[idx] + v;
+            }
+        }
     }
 }
 
@@ -304,15 +323,18 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
     CSS_REQUIRE(d == CM_D, "conv_module: d=%d unsupported (kernel is built for 256)", d);
     CSS_REQUIRE(p.ksize == CM_TAPS, "conv_module: taps must be centre-padded to %d (got %d)", CM_TAPS, p.ksize);
     CSS_REQUIRE(N > 0 && T > 0 && x != out, "conv_module: bad arguments");
-    const size_t smem = sizeof(float) * (size_t)(CM_TT + 2 * CM_HALO) * CM_D;
+    const int max_tile = CM_MAX_ROWS - 2 * CM_HALO;
+    const int n_tiles = (T + max_tile - 1) / max_tile;
+    const int tile_len = (T + n_tiles - 1) / n_tiles;
+    const size_t smem = sizeof(float) * (size_t)(tile_len + 2 * CM_HALO) * CM_D;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_MAX_ROWS * CM_D * 4);
         attr_set = true;
     }
-    dim3 grid((unsigned)N, (T + CM_TT - 1) / CM_TT);
+    dim3 grid((unsigned)N, n_tiles);
     css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
-    conv_module_kernel<<<grid, CM_D, smem, st>>>(x, out, T, p);
+    conv_module_kernel<<<grid, CM_THREADS, smem, st>>>(x, out, T, tile_len, p);
     css_prof_end(st);
     return css_check_launch("conv_module");
 }
