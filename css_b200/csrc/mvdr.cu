@@ -12,8 +12,64 @@
 
 #define MV_M 7
 #define MV_TRI 28          // upper triangle incl. diagonal
+#define MV_E (2 * MV_TRI)  // packed reals per covariance: (re, im) of (i, j >= i), row-major
 #define MV_BINS 32
 
+__device__ __forceinline__ float2 load_x(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
+                                         long n_chunks, long b, int hop_frames, int d, int t, int k) {
+    return (t == 0) ? edge[((long)d * n_chunks + b) * CSS_KP + k]
+                    : spec[((long)d * frames + b * hop_frames + t - 1) * CSS_KP + k];
+}
+
+// ---- kernel 1: masked covariances.  grid (9 bin tiles, B); block (32 bins, 3 masks); 56 accumulators per thread.
+// scm[b][mask][e][KP] fp32 (normalised by the mask sum, compute_scm(normalize=True)); energy slot 1 = sum |mask x0|^2.
+__global__ void __launch_bounds__(96)
+mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
+                const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
+                float* __restrict__ energy) {
+    const long b = blockIdx.y;
+    const int lane = threadIdx.x, mk = threadIdx.y;
+    const int k = blockIdx.x * MV_BINS + lane;
+    const bool act = k < CSS_NBINS;
+    float acc[MV_E];
+#pragma unroll
+    for (int i = 0; i < MV_E; ++i) acc[i] = 0.f;
+    float msum = 0.f, e_mask = 0.f;
+    if (act) {
+        const float* mrow = stitched + ((long)mk * L + b * hop_frames) * CSS_KP + k;
+        for (int t = 0; t < T; ++t) {
+            const float w = mrow[(long)t * CSS_KP];
+            float2 x[MV_M];
+#pragma unroll
+            for (int d = 0; d < MV_M; ++d) x[d] = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k);
+            msum += w;
+            const float ar = w * x[0].x, ai = w * x[0].y;
+            e_mask += ar * ar + ai * ai;
+            int q = 0;
+#pragma unroll
+            for (int i = 0; i < MV_M; ++i) {
+                const float wr = w * x[i].x, wi = w * x[i].y;
+#pragma unroll
+                for (int j = i; j < MV_M; ++j) {
+                    acc[q++] += wr * x[j].x + wi * x[j].y;      // (w x_i) * conj(x_j)
+                    acc[q++] += wi * x[j].x - wr * x[j].y;
+                }
+            }
+        }
+        float* dst = scm + ((b * 3 + mk) * (long)MV_E) * CSS_KP + k;
+#pragma unroll
+        for (int i = 0; i < MV_E; ++i) dst[(long)i * CSS_KP] = acc[i] / msum;
+    }
+    if (mk < 2) {   // warp-uniform
+        e_mask = warp_sum(e_mask);
+        if (lane == 0) energy[((b * 2 + mk) * gridDim.x + blockIdx.x) * 2 + 1] = e_mask;
+    }
+}
+
+// ---- kernel 2: N = solve(Phi_n, Phi_s) in complex128, w = (N / (tr N + eps))[:, 0].
+// Eight lanes share one 7x7 system (lane r owns row r of [Phi_n | Phi_s]); Gauss-Jordan with partial pivoting
+// (largest |re|+|im| among the rows not yet used as pivot, as LAPACK's izamax) entirely in registers: the pivot
+// row is broadcast with shuffles, no row is ever moved.  grid (9, B, 2 speakers); block 256 = 32 systems.
 struct cd { double x, y; };
 __device__ __forceinline__ cd cd_mul(cd a, cd b) { return {a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x}; }
 __device__ __forceinline__ cd cd_sub(cd a, cd b) { return {a.x - b.x, a.y - b.y}; }
@@ -26,114 +82,104 @@ __device__ __forceinline__ cd cd_div(cd a, cd b) {
     const double r = b.x / b.y, den = b.x * r + b.y;
     return {(a.x * r + a.y) / den, (a.y * r - a.x) / den};
 }
-
-__device__ __forceinline__ float2 load_x(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
-                                         long n_chunks, long b, int hop_frames, int d, int t, int k) {
-    return (t == 0) ? edge[((long)d * n_chunks + b) * CSS_KP + k]
-                    : spec[((long)d * frames + b * hop_frames + t - 1) * CSS_KP + k];
+__device__ __forceinline__ cd cd_shfl(cd v, int src) {
+    return {__shfl_sync(0xffffffffu, v.x, src), __shfl_sync(0xffffffffu, v.y, src)};
+}
+// element (r, j) of a Hermitian matrix packed as the upper triangle in shared memory [e][32 bins]
+__device__ __forceinline__ cd herm_at(const float* __restrict__ m, int r, int j, int bin) {
+    const int i0 = r < j ? r : j, j0 = r < j ? j : r;
+    const int q = i0 * MV_M - (i0 * (i0 - 1)) / 2 + (j0 - i0);
+    const float re = m[(2 * q) * MV_BINS + bin], im = m[(2 * q + 1) * MV_BINS + bin];
+    return {(double)re, r <= j ? (double)im : -(double)im};
 }
 
-// grid (ceil(257/32), B); block (32 bins, 3 masks)
-__global__ void __launch_bounds__(96)
-mvdr_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
-            const float* __restrict__ stitched, long L, int hop_frames, int T, float2* __restrict__ Y,
-            float* __restrict__ energy /* [B][2][nblk][2] : sum|y|^2, sum|mask*x0|^2 */) {
-    __shared__ float scm[3][MV_BINS][2 * MV_TRI];     // per mask, per bin: 7 real diag + 21 complex
-    __shared__ float2 wv[2][MV_BINS][MV_M];
-    __shared__ float esum[2][2];
+__global__ void __launch_bounds__(256)
+mvdr_solve_kernel(const float* __restrict__ scm, float2* __restrict__ wout /* [B][2][7][KP] */) {
+    __shared__ float sn[MV_E * MV_BINS], ss[MV_E * MV_BINS];
+    const long b = blockIdx.y;
+    const int spk = blockIdx.z;
+    const int k0 = blockIdx.x * MV_BINS;
+    for (int i = threadIdx.x; i < MV_E * MV_BINS; i += blockDim.x) {
+        const int e = i >> 5, kk = i & 31;
+        const bool ok = k0 + kk < CSS_NBINS;
+        sn[i] = ok ? scm[((b * 3 + 2) * (long)MV_E + e) * CSS_KP + k0 + kk] : 0.f;
+        ss[i] = ok ? scm[((b * 3 + spk) * (long)MV_E + e) * CSS_KP + k0 + kk] : 0.f;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, r = lane & 7;
+    const int bin = (threadIdx.x >> 5) * 4 + (lane >> 3);        // 0..31
+    const int grp = lane & ~7;
+    const bool real_row = r < MV_M;
+    cd A[MV_M], Bm[MV_M];
+#pragma unroll
+    for (int j = 0; j < MV_M; ++j) {
+        A[j] = real_row ? herm_at(sn, r, j, bin) : cd{0.0, 0.0};
+        Bm[j] = real_row ? herm_at(ss, r, j, bin) : cd{0.0, 0.0};
+    }
+    bool used = !real_row;      // the dummy eighth lane never pivots
+    int my_col = -1;
+#pragma unroll
+    for (int c = 0; c < MV_M; ++c) {
+        double v = used ? -1.0 : fabs(A[c].x) + fabs(A[c].y);
+        int p = lane;
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            const double vo = __shfl_xor_sync(0xffffffffu, v, o);
+            const int po = __shfl_xor_sync(0xffffffffu, p, o);
+            if (vo > v || (vo == v && po < p)) { v = vo; p = po; }
+        }
+        const bool is_piv = lane == p;
+        const cd pivc = cd_shfl(A[c], p);
+        const cd f = (is_piv || !real_row) ? cd{0.0, 0.0} : cd_div(A[c], pivc);
+#pragma unroll
+        for (int j = 0; j < MV_M; ++j) {
+            if (j > c) { const cd pj = cd_shfl(A[j], p); A[j] = cd_sub(A[j], cd_mul(f, pj)); }
+            const cd pb = cd_shfl(Bm[j], p);
+            Bm[j] = cd_sub(Bm[j], cd_mul(f, pb));
+        }
+        if (!is_piv) A[c] = cd{0.0, 0.0};
+        if (is_piv) { used = true; my_col = c; }
+    }
+    // the lane that pivoted column c now holds row c of N: N[c][j] = Bm[j] / A[c]
+    cd diag = {1.0, 0.0}, n0 = {0.0, 0.0}, ncc = {0.0, 0.0};
+#pragma unroll
+    for (int c = 0; c < MV_M; ++c)
+        if (my_col == c) { diag = A[c]; ncc = Bm[c]; }
+    if (real_row) { n0 = cd_div(Bm[0], diag); ncc = cd_div(ncc, diag); }
+    // back to complex64 (asteroid casts the solve result to the input dtype), trace in fp32, divide
+    float tr_r = real_row ? (float)ncc.x : 0.f, tr_i = real_row ? (float)ncc.y : 0.f;
+    // sum in column order 0..6 like the sequential fp32 trace: gather each column's term from its owner lane
+    float sr = 0.f, si = 0.f;
+#pragma unroll
+    for (int c = 0; c < MV_M; ++c) {
+        const unsigned m = __ballot_sync(0xffffffffu, my_col == c);
+        const int owner = __ffs((m >> grp) & 0xffu) - 1 + grp;
+        sr += __shfl_sync(0xffffffffu, tr_r, owner);
+        si += __shfl_sync(0xffffffffu, tr_i, owner);
+    }
+    sr += 1e-8f;
+    const float den = sr * sr + si * si;
+    const int k = k0 + bin;
+    if (real_row && k < CSS_NBINS) {
+        const float nr = (float)n0.x, ni = (float)n0.y;
+        wout[((b * 2 + spk) * MV_M + my_col) * (long)CSS_KP + k] = make_float2((nr * sr + ni * si) / den, (ni * sr - nr * si) / den);
+    }
+}
+
+// ---- kernel 3: y[t] = sum_m conj(w_m) x_m[t];  grid (9, B); block (32 bins, 2 speakers); energy slot 0 = sum |y|^2
+__global__ void __launch_bounds__(64)
+mvdr_apply_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
+                  int hop_frames, int T, const float2* __restrict__ wv, float2* __restrict__ Y, float* __restrict__ energy) {
     const long b = blockIdx.y;
     const int lane = threadIdx.x, mk = threadIdx.y;
     const int k = blockIdx.x * MV_BINS + lane;
     const bool act = k < CSS_NBINS;
-    if (lane < 2 && mk < 2) esum[mk][lane] = 0.f;
-    // ---- phase 1: masked covariance, 49 real accumulators per thread ----
-    float acc[2 * MV_TRI];
-#pragma unroll
-    for (int i = 0; i < 2 * MV_TRI; ++i) acc[i] = 0.f;
-    float msum = 0.f, e_mask = 0.f, e_y = 0.f;
+    float e_y = 0.f;
+    float2* yrow = Y + ((b * 2 + mk) * (long)T) * CSS_KP + k;
     if (act) {
-        const float* mrow = stitched + ((long)mk * L + b * hop_frames) * CSS_KP + k;
-        for (int t = 0; t < T; ++t) {
-            const float w = mrow[(long)t * CSS_KP];
-            float2 x[MV_M];
-#pragma unroll
-            for (int d = 0; d < MV_M; ++d) x[d] = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k);
-            msum += w;
-            if (mk < 2) {
-                const float ar = w * x[0].x, ai = w * x[0].y;
-                e_mask += ar * ar + ai * ai;
-            }
-            int q = 0;
-#pragma unroll
-            for (int i = 0; i < MV_M; ++i) {
-                const float wr = w * x[i].x, wi = w * x[i].y;
-#pragma unroll
-                for (int j = i; j < MV_M; ++j) {
-                    // (w x_i) * conj(x_j)
-                    acc[q++] += wr * x[j].x + wi * x[j].y;
-                    acc[q++] += wi * x[j].x - wr * x[j].y;
-                }
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 2 * MV_TRI; ++i) scm[mk][lane][i] = acc[i] / msum;   // compute_scm(normalize=True)
-    }
-    __syncthreads();
-    // ---- phase 2: N = solve(Phi_n, Phi_s) in complex128; w = (N / (tr N + eps))[:, 0] ----
-    if (act && mk < 2) {
-        cd A[MV_M][MV_M], Bm[MV_M][MV_M];
-        int q = 0;
-        for (int i = 0; i < MV_M; ++i)
-            for (int j = i; j < MV_M; ++j) {
-                const float nr = scm[2][lane][q], ni = scm[2][lane][q + 1];
-                const float sr = scm[mk][lane][q], si = scm[mk][lane][q + 1];
-                q += 2;
-                A[i][j] = {(double)nr, (double)ni};
-                Bm[i][j] = {(double)sr, (double)si};
-                if (j != i) {
-                    A[j][i] = {(double)nr, -(double)ni};
-                    Bm[j][i] = {(double)sr, -(double)si};
-                }
-            }
-        // LU with partial pivoting (pivot by |re|+|im| as LAPACK izamax), applied to all 7 RHS
-        for (int c = 0; c < MV_M; ++c) {
-            int p = c;
-            double best = fabs(A[c][c].x) + fabs(A[c][c].y);
-            for (int r = c + 1; r < MV_M; ++r) {
-                const double v = fabs(A[r][c].x) + fabs(A[r][c].y);
-                if (v > best) { best = v; p = r; }
-            }
-            if (p != c)
-                for (int j = 0; j < MV_M; ++j) {
-                    cd t = A[c][j]; A[c][j] = A[p][j]; A[p][j] = t;
-                    t = Bm[c][j]; Bm[c][j] = Bm[p][j]; Bm[p][j] = t;
-                }
-            for (int r = c + 1; r < MV_M; ++r) {
-                const cd f = cd_div(A[r][c], A[c][c]);
-                for (int j = c + 1; j < MV_M; ++j) A[r][j] = cd_sub(A[r][j], cd_mul(f, A[c][j]));
-                for (int j = 0; j < MV_M; ++j) Bm[r][j] = cd_sub(Bm[r][j], cd_mul(f, Bm[c][j]));
-            }
-        }
-        for (int j = 0; j < MV_M; ++j)
-            for (int r = MV_M - 1; r >= 0; --r) {
-                cd s = Bm[r][j];
-                for (int c = r + 1; c < MV_M; ++c) s = cd_sub(s, cd_mul(A[r][c], Bm[c][j]));
-                Bm[r][j] = cd_div(s, A[r][r]);
-            }
-        // back to complex64 (asteroid casts the solve result to the input dtype), trace, divide
-        float tr_r = 0.f, tr_i = 0.f;
-        for (int i = 0; i < MV_M; ++i) { tr_r += (float)Bm[i][i].x; tr_i += (float)Bm[i][i].y; }
-        tr_r += 1e-8f;
-        const float den = tr_r * tr_r + tr_i * tr_i;
-        for (int i = 0; i < MV_M; ++i) {
-            const float nr = (float)Bm[i][0].x, ni = (float)Bm[i][0].y;
-            wv[mk][lane][i] = make_float2((nr * tr_r + ni * tr_i) / den, (ni * tr_r - nr * tr_i) / den);
-        }
-        // ---- phase 3: y[t] = sum_m conj(w_m) x_m[t] ----
         float2 w[MV_M];
 #pragma unroll
-        for (int i = 0; i < MV_M; ++i) w[i] = wv[mk][lane][i];
-        float2* yrow = Y + ((b * 2 + mk) * (long)T) * CSS_KP + k;
+        for (int i = 0; i < MV_M; ++i) w[i] = wv[((b * 2 + mk) * MV_M + i) * (long)CSS_KP + k];
         for (int t = 0; t < T; ++t) {
             float yr = 0.f, yi = 0.f;
 #pragma unroll
@@ -145,22 +191,11 @@ mvdr_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, lo
             yrow[(long)t * CSS_KP] = make_float2(yr, yi);
             e_y += yr * yr + yi * yi;
         }
-    }
-    if (mk < 2) {   // warp-uniform: every lane of the two speech warps takes part
-        e_y = warp_sum(e_y);
-        e_mask = warp_sum(e_mask);
-        if (lane == 0) { esum[mk][0] = e_y; esum[mk][1] = e_mask; }
-    }
-    __syncthreads();
-    if (mk == 0 && lane < 4) {
-        const int s = lane >> 1, w = lane & 1;
-        energy[((b * 2 + s) * gridDim.x + blockIdx.x) * 2 + w] = esum[s][w];
-    }
-    // zero the bin padding of Y so later stages can read whole rows
-    if (mk < 2 && !act && k < CSS_KP) {
-        float2* yrow = Y + ((b * 2 + mk) * (long)T) * CSS_KP + k;
+    } else if (k < CSS_KP) {   // zero the bin padding of Y so later stages can read whole rows
         for (int t = 0; t < T; ++t) yrow[(long)t * CSS_KP] = make_float2(0.f, 0.f);
     }
+    e_y = warp_sum(e_y);
+    if (lane == 0) energy[((b * 2 + mk) * gridDim.x + blockIdx.x) * 2] = e_y;
 }
 
 extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_chunks, const float* stitched, long L,
@@ -169,10 +204,28 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
     CSS_REQUIRE(L >= (n_chunks - 1) * hop_frames + T, "css_mvdr: stitched masks too short (L=%ld)", L);
     CSS_REQUIRE(frames >= (n_chunks - 1) * hop_frames + T - 1, "css_mvdr: spectrogram too short (frames=%ld)", frames);
     CSS_REQUIRE(n_chunks <= 65535, "css_mvdr: more than 65535 chunks per call");
-    dim3 grid((CSS_NBINS + MV_BINS - 1) / MV_BINS, (unsigned)n_chunks), block(MV_BINS, 3);
-    mvdr_kernel<<<grid, block, 0, st>>>((const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L,
-                                        hop_frames, T, (float2*)Y, energy);
-    return css_check_launch("css_mvdr");
+    // stream-ordered scratch: covariances [B][3][56][KP] fp32 and beamformer weights [B][2][7][KP] complex64
+    const size_t scm_bytes = (size_t)n_chunks * 3 * MV_E * CSS_KP * 4, w_bytes = (size_t)n_chunks * 2 * MV_M * CSS_KP * 8;
+    void* scratch = nullptr;
+    cudaError_t e = cudaMallocAsync(&scratch, scm_bytes + w_bytes, st);
+    CSS_REQUIRE(e == cudaSuccess, "css_mvdr: scratch allocation of %zu B failed: %s", scm_bytes + w_bytes, cudaGetErrorString(e));
+    float* scm = static_cast<float*>(scratch);
+    float2* wv = reinterpret_cast<float2*>(static_cast<char*>(scratch) + scm_bytes);
+    const unsigned nblk = (CSS_NBINS + MV_BINS - 1) / MV_BINS;
+    mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 3), 0, st>>>(
+        (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
+    int rc = css_check_launch("css_mvdr(scm)");
+    if (!rc) {
+        mvdr_solve_kernel<<<dim3(nblk, (unsigned)n_chunks, 2), 256, 0, st>>>(scm, wv);
+        rc = css_check_launch("css_mvdr(solve)");
+    }
+    if (!rc) {
+        mvdr_apply_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 2), 0, st>>>(
+            (const float2*)spec, (const float2*)edge, frames, n_chunks, hop_frames, T, wv, (float2*)Y, energy);
+        rc = css_check_launch("css_mvdr(apply)");
+    }
+    cudaFreeAsync(scratch, st);
+    return rc;
 }
 extern "C" int css_mvdr_energy_blocks(void) { return (CSS_NBINS + MV_BINS - 1) / MV_BINS; }
 
