@@ -9,6 +9,10 @@ struct GemmEpilogue {
     const float* residual;   // added last, may be null (may alias C)
     int ldr;
     float clamp_max;         // > 0: min(v, clamp_max) after the activation
+    // training (tcgen05 path only)
+    const void* relu_mask = nullptr;   // bf16 plane 0 of the forward activation: result zeroed where it is <= 0
+    int ldmask = 0;
+    int accumulate = 0;                // 1: C += result (split-K over the SMs, fp32 atomics); bias/act/residual/planes unsupported
 };
 
 int gemm_simt_launch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,
@@ -27,3 +31,4 @@ struct PlaneMat {
 int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, const GemmEpilogue& e, float* C, int ldc,
                    const PlaneMat* out, cudaStream_t st);
 int split_planes_launch(const float* x, long rows, int cols, int ld, const PlaneMat& out, cudaStream_t st);
+int sm_count();

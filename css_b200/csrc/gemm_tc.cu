@@ -111,6 +111,10 @@ struct TcEpilogue {
     long plane_stride;        // elements between planes
     int ldp;
     int n_planes;
+    // training extensions
+    const __nv_bfloat16* mask;   // forward activation (plane 0): output zeroed where mask <= 0 (ReLU backward)
+    int ldmask;
+    int ksplit;                  // > 1: the K range is split over `ksplit` work items that accumulate into c atomically
 };
 
 template <int P> struct Terms;
@@ -149,8 +153,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = (int)((M + BM - 1) / BM), n_tiles = (N + BN - 1) / BN;
-    const int total = m_tiles * n_tiles;
+    const int ksplit = ep.ksplit > 1 ? ep.ksplit : 1;
+    const int tiles = m_tiles * n_tiles;
+    const int total = tiles * ksplit;
     const int kblocks = K / BK;
+    const int kper = (kblocks + ksplit - 1) / ksplit;
 
     if (warp == 0 && lane == 0) {
         asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -175,8 +182,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int mb = t / n_tiles, nb = t - mb * n_tiles;
-                for (int kb = 0; kb < kblocks; ++kb) {
+                const int tt = t % tiles, sp = t / tiles;
+                const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
+                const int kb0 = sp * kper, kb1 = min(kblocks, kb0 + kper);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], C::STAGE_BYTES);
                     uint8_t* sa = smem + stage * C::STAGE_BYTES;
@@ -201,7 +210,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                for (int kb = 0; kb < kblocks; ++kb) {
+                const int sp = t / tiles;
+                const int kb0 = sp * kper, kb1 = min(kblocks, kb0 + kper);
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
                     const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
@@ -213,7 +224,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                             const int pa = term_a(tm), pb = term_b(tm);
                             const uint64_t da = make_desc<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
                             const uint64_t db = make_desc<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
-                            tc_mma(d_tmem, da, db, idesc, (kb | ks | tm) != 0);
+                            tc_mma(d_tmem, da, db, idesc, ((kb - kb0) | ks | tm) != 0);
                         }
                     }
                     tc_commit(&empty[stage]);
@@ -233,7 +244,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int cg = lane & 7, rsub = lane >> 3;
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int mb = t / n_tiles, nb = t - mb * n_tiles;
+            const int tt = t % tiles;
+            const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             const long row_base = (long)mb * BM + q * 32;
@@ -293,6 +305,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         v[i] *= ep.alpha;
                     }
                     if (ep.residual) { v[0] += res4[it].x; v[1] += res4[it].y; v[2] += res4[it].z; v[3] += res4[it].w; }
+                    if (ep.mask) {
+                        const __nv_bfloat16* mp = ep.mask + row * ep.ldmask + col;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (col + i < N && !(__bfloat162float(mp[i]) > 0.f)) v[i] = 0.f;
+                    }
+                    if (ksplit > 1) {
+                        float* cp = ep.c + row * ep.ldc + col;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) if (col + i < N) atomicAdd(cp + i, v[i]);
+                        continue;
+                    }
                     if (ep.c) {
                         float* cp = ep.c + row * ep.ldc + col;
                         if (vec_ok && (ep.ldc & 3) == 0) {
@@ -374,7 +398,7 @@ static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld
     return 0;
 }
 
-static int sm_count() {
+int sm_count() {
     static int n = 0;
     if (!n) {
         int dev = 0;
@@ -398,7 +422,7 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
         attr = true;
     }
-    const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (ep.ksplit > 1 ? ep.ksplit : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
     gemm_tc_kernel<P, BN, BK><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     return css_check_launch("gemm_tc");
@@ -416,7 +440,20 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     CSS_REQUIRE(K % KPAD == 0 && K > 0, "gemm_tc: K=%d must be a positive multiple of %d", K, KPAD);
     TcEpilogue ep = {e.bias, e.act, e.alpha, e.residual, e.ldr, e.clamp_max, C, ldc,
                      out ? reinterpret_cast<__nv_bfloat16*>(out->ptr) : nullptr, out ? out->plane_stride : 0,
-                     out ? out->ld : 0, out ? out->planes : 0};
+                     out ? out->ld : 0, out ? out->planes : 0, reinterpret_cast<const __nv_bfloat16*>(e.relu_mask), e.ldmask, 1};
+    if (e.accumulate) {
+        CSS_REQUIRE(C && !out && !e.bias && !e.act && !e.residual && !e.relu_mask, "gemm_tc: accumulate mode takes a plain fp32 output");
+        const int bn = N > 128 ? 256 : 128, bk = (N > 128 && g_tc_variant == 1) ? 32 : 64;
+        const long tiles = ((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+        const int kblocks = K / bk;
+        int want = (int)(sm_count() / tiles);
+        if (want < 1) want = 1;
+        if (want > kblocks) want = kblocks;
+        const int kper = (kblocks + want - 1) / want;
+        ep.ksplit = (kblocks + kper - 1) / kper;   // every split owns at least one k-block
+        if (ep.ksplit < 2) ep.ksplit = 2;           // force the atomic epilogue (second split may not be empty: kblocks >= 2 always holds for K >= 128)
+        CSS_REQUIRE(kblocks >= 2, "gemm_tc: accumulate mode needs K >= 128");
+    }
     const bool wide = N > 128;
     const int v = g_tc_variant;
     if (P == 1) {
