@@ -134,6 +134,46 @@ int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scrat
 int css_pit_mse(const float* est, const float* tgt, long B, int K, long n, double* pair_ws, float* loss_b, int* perm,
                 float* loss, float* grad, float gscale, css_stream_t stream);
 
+/* ---- training step: css/trainer/iteration_types.py:34-63 (train_one_epoch body), css/objectives/mse.py:22-37 ---- */
+/* All parameters live in ONE flat fp32 buffer and all gradients in a second buffer of the same layout (the torch
+ * Parameters of css_b200.models.Conformer are views into them); the structs below give element offsets.  Within a
+ * block, linear_q/k/v weights (and biases) must be adjacent in that order: wqkv/bqkv name the first of the three. */
+typedef struct { long ln_g, ln_b, w1, b1, w2, b2; } css_ffn_offsets;
+typedef struct {
+    css_ffn_offsets ff_in;
+    long att_ln_g, att_ln_b, wqkv, bqkv, wo, bo;
+    long conv_ln_g, conv_ln_b, pw1_w, pw1_b, dw_w, dw_b, bn_g, bn_b, pw2_w, pw2_b;
+    css_ffn_offsets ff_out;
+    long out_ln_g, out_ln_b;
+} css_conformer_block_offsets;
+typedef struct {
+    int idim, d_model, heads, d_ffn, num_blocks, num_bins, num_out, num_spk, pe_rows, ksize;
+    long embed_w, embed_b, embed_ln_g, embed_ln_b, pe /* -1: no relative positions */, head_w, head_b;
+} css_conformer_train_desc;
+/* params/grads: flat buffers; bn_running: [num_blocks][2][d_model] running mean / var (updated in place, momentum 0.1) */
+void* css_trainer_create(const css_conformer_train_desc* desc_host, const css_conformer_block_offsets* blocks_host,
+                         float* params, float* grads, float* bn_running);
+void css_trainer_destroy(void* trainer);
+size_t css_trainer_workspace_bytes(const void* trainer, long N, int T);
+/* Conformer.forward in train mode (css/models/conformer.py:83-104; dropout probability 0): feat (N,T,idim) raw features
+ * -> y_pred (N,num_spk,T,num_bins) and optionally the head activations masks_head (N*T, ld_head).  Activations needed by
+ * the backward stay in `workspace`, which must be passed unchanged to css_trainer_backward. */
+int css_trainer_forward(void* trainer, const float* feat, long N, int T, float* y_pred, float* masks_head, int ld_head,
+                        void* workspace, size_t workspace_bytes, css_stream_t stream);
+/* d loss / d y_pred (N,num_spk,T,num_bins) -> gradients ACCUMULATED into the flat gradient buffer. */
+int css_trainer_backward(void* trainer, const float* feat, const float* grad_y_pred, long N, int T, void* workspace,
+                         size_t workspace_bytes, css_stream_t stream);
+/* The same backward in pieces, so that the caller can start the gradient all-reduce of finished layers while earlier
+ * layers are still running: parts are num_blocks (mask head), l (encoder block l) and -1 (input embedding), processed
+ * from part_hi down to part_lo.  The whole range num_blocks..-1 must be covered in descending order. */
+int css_trainer_backward_part(void* trainer, const float* feat, const float* grad_y_pred, long N, int T, int part_hi,
+                              int part_lo, void* workspace, size_t workspace_bytes, css_stream_t stream);
+/* torch.nn.utils.clip_grad_norm_ + torch.optim.Adam(weight_decay) over flat buffers (scripts/python/train.py:209-211) */
+int css_grad_sqnorm(const float* g, long n, double* out, css_stream_t stream);
+int css_adam_step(float* p, const float* g, float* m, float* v, long n, float lr, float beta1, float beta2, float eps,
+                  float weight_decay, long step, float gscale, const double* sqnorm, float max_norm, float* norm_out,
+                  css_stream_t stream);
+
 /* tcgen05/TMEM GEMM from fp32 operands (same contract as css_gemm_f32): operands are split into `planes` bf16 planes
  * in `scratch` (1 = bf16, 2 = bf16x3, 3 = bf16x6 product terms), accumulation in fp32 */
 size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes);
