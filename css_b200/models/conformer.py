@@ -5,7 +5,8 @@ constructor, ``add_args``/``build_model`` and ``state_dict()`` key names (the ``
 contract), same default PyTorch initialisation order, so a given
 ``torch.manual_seed`` yields the reference's weights.  The torch modules below are parameter
 containers only: ``forward`` hands the weight pointers to ``css_conformer_forward`` in
-libcss_b200.so.  Inference only (dropout is the identity, BatchNorm uses running stats).
+libcss_b200.so.  In eval mode dropout is the identity and BatchNorm uses running stats; in train mode ``forward`` runs the native
+training step (css_b200/trainer), with batch-statistics BatchNorm and a native backward.
 """
 import ctypes
 
@@ -118,8 +119,17 @@ class Conformer(nn.Module):
         self.conf = dict(conformer_conf)
         self.linear = nn.Linear(conformer_conf["attention_dim"], num_bins * (num_spk + num_noise))
         self._engine = None
+        self._train_engine = None
 
     # ------------------------------------------------------------------ native engine
+    def train_engine(self):
+        """Flat-buffer training engine (css_b200/trainer/engine.py), built on first use; re-homes the Parameters."""
+        if self._train_engine is None:
+            from ..trainer.engine import ConformerTrainEngine
+
+            self._train_engine = ConformerTrainEngine(self)
+        return self._train_engine
+
     def invalidate(self):
         """Drop the packed weights (call after loading a state_dict or moving devices)."""
         if self._engine is not None:
@@ -132,6 +142,7 @@ class Conformer(nn.Module):
 
     def _apply(self, fn, *a, **k):
         self.invalidate()
+        self._train_engine = None    # a device/dtype move re-allocates the parameters
         return super()._apply(fn, *a, **k)
 
     def __del__(self):
@@ -238,6 +249,12 @@ class Conformer(nn.Module):
         N, T, F = f.shape
         if F != self.in_features:
             raise RuntimeError(f"expected {self.in_features} input features, got {F}")
+        if self.training and torch.is_grad_enabled():
+            if self.conf["dropout_rate"] != 0.0:
+                raise nv.NativeError("the native training step implements dropout_rate 0 (set conformer_dropout_rate=0.0)")
+            from ..trainer.autograd import train_forward
+
+            return train_forward(self, f)
         eng = self.engine()
         x = torch.zeros(N * T, eng["ldin"], dtype=torch.float32, device=f.device)
         x[:, :F] = f.reshape(N * T, F)

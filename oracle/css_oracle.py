@@ -145,10 +145,11 @@ def _conformer_conv(x, sd, p, training_stats=False):
     return y * sd[p + ".pw_conv_2.weight"].view(()) + sd[p + ".pw_conv_2.bias"].view(())
 
 
-def conformer_masks(f, sd, heads=4, num_out=3):
+def conformer_masks(f, sd, heads=4, num_out=3, training=False):
     """Reference Conformer forward up to the masks.  css/models/conformer.py:83-101,152-165.
 
-    f: (N, T, F) -> list of num_out tensors (N, T, num_bins).
+    f: (N, T, F) -> list of num_out tensors (N, T, num_bins).  ``training``: BatchNorm uses batch statistics
+    (model.train() with dropout probability 0).
     """
     if f.ndim == 4:
         f = f.squeeze(0)
@@ -167,7 +168,7 @@ def conformer_masks(f, sd, heads=4, num_out=3):
         p = "conformer.encoders.%d" % i
         x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_in")
         x = x + _conformer_mhsa(x, pos_k, sd, p + ".self_attn", heads)
-        x = x + _conformer_conv(x, sd, p + ".conv")
+        x = x + _conformer_conv(x, sd, p + ".conv", training)
         x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_out")
         x = _layer_norm(x, sd, p + ".layer_norm")
     m = torch.relu(_linear(x, sd, "linear"))
@@ -216,21 +217,21 @@ def _bilstm(x, sd, p):
     return torch.cat([fw, bw], dim=-1)
 
 
-def model_masks(f, sd, heads=4):
+def model_masks(f, sd, heads=4, training=False):
     """Dispatch on the state_dict's own key names (the reference's .mdl interchange contract)."""
     if any(k.startswith("conformer.") for k in sd):
-        return conformer_masks(f, sd, heads)
+        return conformer_masks(f, sd, heads, training=training)
     return blstm_masks(f, sd)
 
 
-def model_forward(f, sd, num_bins=257, heads=4):
+def model_forward(f, sd, num_bins=257, heads=4, training=False):
     """(y_pred, masks) with the documented patch D3 (``f_orig[..., :num_bins]``).
 
     css/models/conformer.py:103-104, css/models/blstm.py:87-88; SURVEY.md A.9 D3.
     """
     if f.ndim == 4:
         f = f.squeeze(0)
-    masks = model_masks(f, sd, heads)
+    masks = model_masks(f, sd, heads, training)
     y_pred = torch.stack([m * f[..., :num_bins] for m in masks[:-1]], dim=1)
     return y_pred, masks
 
@@ -530,11 +531,39 @@ def pit_mse(y_pred, y_true, return_permutation=False):
     return (loss, perms) if return_permutation else loss
 
 
-def mse_objective(sd, sample, heads=4):
+def mse_objective(sd, sample, heads=4, training=False):
     """MeanSquaredError.forward with patches D3/D4.  css/objectives/mse.py:22-37."""
-    y_pred, _ = model_forward(sample["mix"], sd, heads=heads)
+    y_pred, _ = model_forward(sample["mix"], sd, heads=heads, training=training)
     y_true = torch.stack((sample["source1"], sample["source2"]), dim=1)
     return pit_mse(y_pred, y_true)
+
+
+def train_steps(sd, samples, lr=1e-4, weight_decay=1e-2, grad_thresh=5.0, heads=4):
+    """The body of train_one_epoch (css/trainer/iteration_types.py:34-63) with the optimiser of
+    scripts/python/train.py:209-211 (torch.optim.Adam(lr, weight_decay)) and train.sh:16 (clip 5.0), dropout 0.
+
+    sd: state_dict (modified in place: parameters updated, BatchNorm running stats are NOT tracked here).
+    Returns per step: loss, gradient norm (before clipping), and the gradients of the first step.
+    """
+    names = [k for k, v in sd.items() if v.dtype.is_floating_point and "running_" not in k]
+    params = [sd[k].detach().clone().requires_grad_(True) for k in names]
+    opt = torch.optim.Adam(params, lr=lr, weight_decay=weight_decay)
+    out = {"loss": [], "norm": [], "grads": None}
+    for step, sample in enumerate(samples):
+        live = dict(sd)
+        live.update(zip(names, params))
+        loss = mse_objective(live, sample, heads=heads, training=True)
+        opt.zero_grad()
+        loss.backward()
+        if step == 0:
+            out["grads"] = {k: (p.grad.detach().clone() if p.grad is not None else torch.zeros_like(p)) for k, p in zip(names, params)}
+        norm = torch.nn.utils.clip_grad_norm_(params, grad_thresh)
+        opt.step()
+        out["loss"].append(float(loss.detach()))
+        out["norm"].append(float(norm.detach()))
+    for k, p in zip(names, params):
+        sd[k] = p.detach()
+    return out
 
 
 # --------------------------------------------------------------------------------------

@@ -54,3 +54,27 @@ def rel_inf(a, b):
 def rel_l2(a, b):
     a, b = torch.as_tensor(a).double().cpu(), torch.as_tensor(b).double().cpu()
     return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def train_samples(steps, n, t, seed=21, idim=1799):
+    """Seeded synthetic training batches shaped like the reference's (mix feats, 2 source magnitudes)."""
+    g = torch.Generator().manual_seed(seed)
+    out = []
+    for _ in range(steps):
+        s1 = torch.rand(n, t, 257, generator=g) ** 2
+        s2 = torch.rand(n, t, 257, generator=g) ** 2
+        mix = torch.empty(n, t, idim)
+        mix[..., :257] = s1 + s2 + 0.05 * torch.rand(n, t, 257, generator=g)
+        if idim > 257:
+            mix[..., 257:] = (torch.rand(n, t, idim - 257, generator=g) * 2 - 1) * 3.14159
+        out.append({"mix": mix, "source1": s1, "source2": s2, "ovl": 0.5})
+    return out
+
+
+def train_conformer(num_blocks=2, idim=1799, seed=3):
+    """Case-E model: reference init under `seed`, dropout 0 (the native step's supported setting), train mode."""
+    import css_b200.models as M
+
+    conf = dict(CONF_C7, conformer_num_blocks=num_blocks, idim=idim, conformer_dropout_rate=0.0)
+    torch.manual_seed(seed)
+    return M.build_model("Conformer", conf).train()
