@@ -55,7 +55,7 @@ def test_train_step_matches_reference_golden(cuda, gtrain):
         norms.append(float(opt.clip_grad_norm_(5.0)))
         opt.step()
         opt.zero_grad()
-        losses.append(float(loss))
+        losses.append(float(loss.detach()))
     assert np.allclose(losses, gtrain["E_loss"], rtol=2e-5), (losses, gtrain["E_loss"])
     assert np.allclose(norms, gtrain["E_norm"], rtol=1e-3), (norms, gtrain["E_norm"])
     for key in gtrain.files:
@@ -87,9 +87,12 @@ def test_all_gradients_vs_oracle_t250(cuda, mode, tol):
         ref = O.train_steps(sd, [b])
         assert abs(float(loss) - ref["loss"][0]) <= (1e-5 if mode == 1 else 2e-3) * ref["loss"][0]
         worst = 0.0
+        total = float(torch.sqrt(sum(g.double().pow(2).sum() for g in ref["grads"].values())))
         for name, p in model.named_parameters():
             r = ref["grads"][name]
-            err = float((p.grad.cpu() - r).norm() / r.norm().clamp_min(1e-30))
+            # linear_k.bias has an analytically ZERO gradient (softmax is invariant to a shift of all keys), so every
+            # tensor is measured against max(its own norm, 1e-3 of the global gradient norm)
+            err = float((p.grad.cpu() - r).norm() / max(float(r.norm()), 1e-3 * total))
             worst = max(worst, err)
             assert err < tol, f"{name}: rel-l2 {err:.2e}"
         print(f"mode {mode}: worst gradient rel-l2 {worst:.2e}")
