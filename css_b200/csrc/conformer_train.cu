@@ -32,7 +32,7 @@ inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 inline long pad64(long v) { return (v + 63) / 64 * 64; }
 
 struct SavedBlock {
-    float *x0, *x1, *x2, *x3, *x4, *qkv, *cpre, *bnsave;
+    float *x0, *x1, *x2, *x3, *x4, *qkv, *cpre, *bnsave, *probs;
     PlaneMat n1, h1, n2, att, n4, h4;
 };
 struct Ws {
@@ -44,7 +44,7 @@ struct Ws {
     // scratch
     double* bn_stats;
     float* bstats;
-    float *g, *dwide, *dn, *datt, *Pg, *dSg, *tmp;
+    float *g, *dwide, *dn, *datt, *att_scratch, *tmp;
     PlaneMat gP, gT, dwP, dwT, actT;
     size_t bytes;
 };
@@ -55,7 +55,6 @@ void carve(const Trainer* t, long N, int T, char* base, Ws* w) {
     const long M = N * T, Mp = pad64(M);
     const int d = c.d_model, f = c.d_ffn;
     const int wide = std::max(std::max(f, 3 * d), t->nhp);
-    const int TP = (T + 31) & ~31;
     size_t off = 0;
     auto take = [&](size_t bytes) { char* p = base ? base + off : nullptr; off += align256(bytes); return p; };
     auto planes = [&](long rows, int ld) { PlaneMat pm = {take((size_t)kP * rows * ld * 2), rows * (long)ld, ld, kP}; return pm; };
@@ -75,6 +74,7 @@ void carve(const Trainer* t, long N, int T, char* base, Ws* w) {
         s.qkv = f32((size_t)M * 3 * d);
         s.cpre = f32((size_t)M * d);
         s.bnsave = f32(2 * d);
+        s.probs = f32(attention_train_probs_floats(N, T, c.heads));
         s.n1 = planes(M, d); s.h1 = planes(M, f); s.n2 = planes(M, d); s.att = planes(M, d); s.n4 = planes(M, d); s.h4 = planes(M, f);
     }
     w->bn_stats = reinterpret_cast<double*>(take(2 * d * sizeof(double)));
@@ -84,8 +84,7 @@ void carve(const Trainer* t, long N, int T, char* base, Ws* w) {
     w->dn = f32((size_t)M * d);
     w->datt = f32((size_t)M * d);
     w->tmp = f32((size_t)M * d);
-    w->Pg = f32((size_t)N * c.heads * T * TP);
-    w->dSg = f32((size_t)N * c.heads * T * TP);
+    w->att_scratch = f32(attention_train_scratch_floats(N, T, c.heads));
     w->gP = planes(M, d);
     w->gT = planes(d, (int)Mp);
     w->dwP = planes(M, wide);
@@ -290,7 +289,7 @@ extern "C" int css_trainer_forward(void* trainer, const float* feat, long N, int
         if ((rc = layernorm_planes_launch(s.x1, p + o.att_ln_g, p + o.att_ln_b, nullptr, M, d, 1e-5f, 0, s.n2.ptr, s.n2.plane_stride, kP, st))) return rc;
         GemmEpilogue eq = {p + o.bqkv, 0, 1.f, nullptr, 0, 0.f};
         if ((rc = tc(s.n2, b.wqkv.w, P, M, 3 * d, d, eq, s.qkv, 3 * d, nullptr, st))) return rc;
-        if ((rc = attention_launch(s.qkv, pe, c.pe_rows, w.tmp, N, T, c.heads, d / c.heads, st))) return rc;
+        if ((rc = attention_train_fwd_launch(s.qkv, pe, c.pe_rows, w.tmp, s.probs, w.att_scratch, N, T, c.heads, d / c.heads, P == 2, st))) return rc;
         if ((rc = split_planes_launch(w.tmp, M, d, d, s.att, st))) return rc;
         GemmEpilogue eo = {p + o.bo, 0, 1.f, s.x1, d, 0.f};
         if ((rc = tc(s.att, b.wo.w, P, M, d, d, eo, s.x2, d, nullptr, st))) return rc;
@@ -363,8 +362,8 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             GemmEpilogue ed = {nullptr, 0, 1.f, nullptr, 0, 0.f};
             if ((rc = tc(w.gP, b.wo.wT, P, M, d, d, ed, w.datt, d, nullptr, st))) return rc;
             float* dqkv = w.dwide;   // (M, 3d)
-            if ((rc = attention_bwd_launch(s.qkv, pe, c.pe_rows, w.datt, dqkv, pe ? gr + c.pe : nullptr, w.Pg, w.dSg, N, T, c.heads,
-                                           d / c.heads, st))) return rc;
+            if ((rc = attention_train_bwd_launch(s.qkv, pe, c.pe_rows, s.probs, w.datt, dqkv, pe ? gr + c.pe : nullptr, w.att_scratch,
+                                                 N, T, c.heads, d / c.heads, P == 2, st))) return rc;
             PlaneMat dqP = view(w.dwP, M, 3 * d), dqT = view(w.dwT, 3 * d, (int)Mp);
             if ((rc = split_t_launch(dqkv, M, 3 * d, 3 * d, &dqP, &dqT, Mp, gr + o.bqkv, 1.f, st))) return rc;
             PlaneMat nT = view(w.actT, d, (int)Mp);

@@ -30,10 +30,16 @@ struct LnBwdArgs {
 };
 int ln_bwd_launch(const LnBwdArgs& a, long M, int d, float eps, bool glu, cudaStream_t st);
 
-// relative-position attention backward (css/models/conformer.py:229-250): qkv (N*T, 3*H*64), dO (N*T, H*64) ->
-// dqkv (N*T, 3*H*64), dpe (pe_rows, 64) accumulated.  P, dS: scratch (N*H*T*TP floats each, TP = T rounded up to 32).
-int attention_bwd_launch(const float* qkv, const float* pe, int pe_rows, const float* dO, float* dqkv, float* dpe, float* Pg,
-                         float* dSg, long N, int T, int H, int dk, cudaStream_t st);
+// relative-position attention of the training step on the warp-level tensor cores (attention_train.cu), T <= 256:
+// qkv (N*T, 3*H*64) -> out (N*T, H*64); `probs` keeps the attention probabilities for the backward.
+// split3: three-term TF32 split (fp32-class accuracy) instead of single TF32 products.
+size_t attention_train_scratch_floats(long N, int T, int H);
+size_t attention_train_probs_floats(long N, int T, int H);
+int attention_train_fwd_launch(const float* qkv, const float* pe, int pe_rows, float* out, float* probs, float* scratch, long N,
+                               int T, int H, int dk, bool split3, cudaStream_t st);
+// dO (N*T, H*64) -> dqkv (N*T, 3*H*64) overwritten, dpe (pe_rows, 64) accumulated
+int attention_train_bwd_launch(const float* qkv, const float* pe, int pe_rows, const float* probs, const float* dO, float* dqkv,
+                               float* dpe, float* scratch, long N, int T, int H, int dk, bool split3, cudaStream_t st);
 
 struct ConvTrainParams {
     const float *ln_g, *ln_b, *pw1_w, *pw1_b, *dw_w, *dw_b, *bn_g, *bn_b, *pw2_w, *pw2_b;

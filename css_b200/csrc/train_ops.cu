@@ -237,241 +237,6 @@ int ln_bwd_launch(const LnBwdArgs& a, long M, int d, float eps, bool glu, cudaSt
 }
 
 // ---------------------------------------------------------------------------------------------
-// Relative-position attention backward.  Kernel 1 (one CTA per (sequence, head), one warp per query row) recomputes
-// the probabilities exactly as the forward does, writes P and dS = P (dP - sum P dP) / sqrt(dk) to scratch and
-// produces dQ; kernel 2 (one warp per key row / relative offset) reduces dV = P^T dO, dK = dS^T Q and
-// dPE[r] = sum_i dS[i][i-r] Q[i] from the scratch matrices.
-// ---------------------------------------------------------------------------------------------
-#define AB_DK 64
-#define AB_WARPS 8
-
-__global__ void __launch_bounds__(AB_WARPS * 32)
-attn_bwd_ds_kernel(const float* __restrict__ qkv, const float* __restrict__ pe, int pe_rows, int use_pe,
-                   const float* __restrict__ dO, float* __restrict__ Pg, float* __restrict__ dSg, float* __restrict__ dqkv,
-                   int T, int H) {
-    extern __shared__ float sm[];
-    const int TP = (T + 31) & ~31;
-    const int RP = 2 * TP;
-    float* Kt = sm;                          // [64][TP]
-    float* Pt = Kt + AB_DK * TP;             // [64][RP]
-    float* Pb = Pt + AB_DK * RP;             // [warps][TP]
-    float* Qb = Pb + AB_WARPS * TP;          // [warps][64]
-    float* Db = Qb + AB_WARPS * AB_DK;       // [warps][64]
-    const int n = blockIdx.x / H, h = blockIdx.x % H;
-    const int ld = 3 * H * AB_DK;
-    const float* base = qkv + (long)n * T * ld;
-    const int maxlen = pe_rows / 2;
-    for (int i = threadIdx.x; i < T * AB_DK; i += blockDim.x) {
-        const int j = i >> 6, d = i & 63;
-        Kt[d * TP + j] = base[(long)j * ld + (H + h) * AB_DK + d];
-    }
-    for (int i = threadIdx.x; i < AB_DK * (TP - T); i += blockDim.x) {
-        const int d = i / (TP - T), j = T + i % (TP - T);
-        Kt[d * TP + j] = 0.f;
-    }
-    for (int i = threadIdx.x; i < RP * AB_DK; i += blockDim.x) {
-        const int r = i >> 6, d = i & 63;
-        float v = 0.f;
-        if (use_pe && r <= 2 * (T - 1)) {
-            int rel = r - (T - 1);
-            rel = max(-maxlen, min(maxlen - 1, rel)) + maxlen;
-            v = pe[(long)rel * AB_DK + d];
-        }
-        Pt[d * RP + r] = v;
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float* pb = Pb + warp * TP;
-    float* qb = Qb + warp * AB_DK;
-    float* dob = Db + warp * AB_DK;
-    const int NJ = TP / 32;
-    const long nh = (long)n * H + h;
-    for (int i = warp; i < T; i += AB_WARPS) {
-        const float* qrow = base + (long)i * ld + h * AB_DK;
-        const float* dorow = dO + ((long)n * T + i) * (H * AB_DK) + h * AB_DK;
-        qb[lane] = qrow[lane];
-        qb[lane + 32] = qrow[lane + 32];
-        dob[lane] = dorow[lane];
-        dob[lane + 32] = dorow[lane + 32];
-        __syncwarp();
-        float s[8];
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj) s[jj] = 0.f;
-        for (int d = 0; d < AB_DK; ++d) {
-            const float qd = qb[d];
-            const float* kr = Kt + d * TP + lane;
-            const float* pr = Pt + d * RP + (i + T - 1) - lane;
-#pragma unroll
-            for (int jj = 0; jj < 8; ++jj)
-                if (jj < NJ) {
-                    const int r = (i + T - 1) - lane - 32 * jj;
-                    const float pv = (r >= 0) ? pr[-32 * jj] : 0.f;
-                    s[jj] = fmaf(qd, kr[32 * jj] + pv, s[jj]);
-                }
-        }
-        float mx = -INFINITY;
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj)
-            if (jj < NJ) {
-                s[jj] = (lane + 32 * jj < T) ? s[jj] * 0.125f : -INFINITY;
-                mx = fmaxf(mx, s[jj]);
-            }
-        mx = warp_max(mx);
-        float sum = 0.f;
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj)
-            if (jj < NJ) {
-                s[jj] = (lane + 32 * jj < T) ? expf(s[jj] - mx) : 0.f;
-                sum += s[jj];
-            }
-        const float inv = 1.f / warp_sum(sum);
-        // dP[j] = dO_i . V_j  (lane = j, V rows straight from global/L2)
-        float dp[8];
-        float dsum = 0.f;
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj)
-            if (jj < NJ) {
-                s[jj] *= inv;
-                const int j = lane + 32 * jj;
-                float acc = 0.f;
-                if (j < T) {
-                    const float4* vr = reinterpret_cast<const float4*>(base + (long)j * ld + (2 * H + h) * AB_DK);
-#pragma unroll
-                    for (int d4 = 0; d4 < AB_DK / 4; ++d4) {
-                        const float4 vv = vr[d4];
-                        const float4 dd = reinterpret_cast<const float4*>(dob)[d4];
-                        acc += vv.x * dd.x + vv.y * dd.y + vv.z * dd.z + vv.w * dd.w;
-                    }
-                }
-                dp[jj] = acc;
-                dsum += s[jj] * acc;
-            }
-        dsum = warp_sum(dsum);
-        float* prow = Pg + (nh * T + i) * TP;
-        float* srow = dSg + (nh * T + i) * TP;
-#pragma unroll
-        for (int jj = 0; jj < 8; ++jj)
-            if (jj < NJ) {
-                const float ds = s[jj] * (dp[jj] - dsum) * 0.125f;
-                prow[lane + 32 * jj] = s[jj];
-                srow[lane + 32 * jj] = ds;
-                pb[lane + 32 * jj] = ds;
-            }
-        __syncwarp();
-        // dQ_i = sum_j dS_ij (K_j + PE[i-j])   (lane = d)
-        float q0 = 0.f, q1 = 0.f;
-        for (int j = 0; j < T; ++j) {
-            const float c = pb[j];
-            const float* kr = base + (long)j * ld + (H + h) * AB_DK;
-            float k0 = kr[lane], k1 = kr[lane + 32];
-            if (use_pe) {
-                const int rel = max(-maxlen, min(maxlen - 1, i - j)) + maxlen;
-                k0 += pe[(long)rel * AB_DK + lane];
-                k1 += pe[(long)rel * AB_DK + lane + 32];
-            }
-            q0 = fmaf(c, k0, q0);
-            q1 = fmaf(c, k1, q1);
-        }
-        float* dq = dqkv + ((long)n * T + i) * ld + h * AB_DK;
-        dq[lane] = q0;
-        dq[lane + 32] = q1;
-        __syncwarp();
-    }
-}
-
-__global__ void __launch_bounds__(AB_WARPS * 32)
-attn_bwd_kv_kernel(const float* __restrict__ qkv, const float* __restrict__ dO, const float* __restrict__ Pg,
-                   const float* __restrict__ dSg, float* __restrict__ dqkv, float* __restrict__ dpe, int pe_rows, int use_pe,
-                   int T, int H) {
-    extern __shared__ float sm[];
-    const int TP = (T + 31) & ~31;
-    float* Qs = sm;                  // [T][64]
-    float* Os = Qs + T * AB_DK;      // [T][64]
-    const int n = blockIdx.x / H, h = blockIdx.x % H;
-    const int ld = 3 * H * AB_DK;
-    const float* base = qkv + (long)n * T * ld;
-    const long nh = (long)n * H + h;
-    for (int i = threadIdx.x; i < T * AB_DK; i += blockDim.x) {
-        const int t = i >> 6, d = i & 63;
-        Qs[i] = base[(long)t * ld + h * AB_DK + d];
-        Os[i] = dO[((long)n * T + t) * (H * AB_DK) + h * AB_DK + d];
-    }
-    __syncthreads();
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const float* P = Pg + nh * T * TP;
-    const float* S = dSg + nh * T * TP;
-    for (int j = warp; j < T; j += AB_WARPS) {
-        float v0 = 0.f, v1 = 0.f, k0 = 0.f, k1 = 0.f;
-        for (int i0 = 0; i0 < T; i0 += 32) {
-            const int i = i0 + lane;
-            const float pl = i < T ? P[(long)i * TP + j] : 0.f;
-            const float sl = i < T ? S[(long)i * TP + j] : 0.f;
-            const int cnt = min(32, T - i0);
-            for (int ii = 0; ii < cnt; ++ii) {
-                const float p = __shfl_sync(0xffffffffu, pl, ii);
-                const float s = __shfl_sync(0xffffffffu, sl, ii);
-                const float* orow = Os + (i0 + ii) * AB_DK;
-                const float* qrow = Qs + (i0 + ii) * AB_DK;
-                v0 = fmaf(p, orow[lane], v0);
-                v1 = fmaf(p, orow[lane + 32], v1);
-                k0 = fmaf(s, qrow[lane], k0);
-                k1 = fmaf(s, qrow[lane + 32], k1);
-            }
-        }
-        float* dk = dqkv + ((long)n * T + j) * ld + (H + h) * AB_DK;
-        float* dv = dqkv + ((long)n * T + j) * ld + (2 * H + h) * AB_DK;
-        dk[lane] = k0; dk[lane + 32] = k1;
-        dv[lane] = v0; dv[lane + 32] = v1;
-    }
-    if (!use_pe) return;
-    const int maxlen = pe_rows / 2;
-    for (int r = warp; r < 2 * T - 1; r += AB_WARPS) {
-        const int rel = r - (T - 1);                 // i - j
-        const int ilo = max(0, rel), ihi = min(T - 1, T - 1 + rel);
-        float a0 = 0.f, a1 = 0.f;
-        for (int i0 = ilo; i0 <= ihi; i0 += 32) {
-            const int i = i0 + lane;
-            const float sl = i <= ihi ? S[(long)i * TP + (i - rel)] : 0.f;
-            const int cnt = min(32, ihi - i0 + 1);
-            for (int ii = 0; ii < cnt; ++ii) {
-                const float s = __shfl_sync(0xffffffffu, sl, ii);
-                const float* qrow = Qs + (i0 + ii) * AB_DK;
-                a0 = fmaf(s, qrow[lane], a0);
-                a1 = fmaf(s, qrow[lane + 32], a1);
-            }
-        }
-        const int row = max(-maxlen, min(maxlen - 1, rel)) + maxlen;
-        atomicAdd(dpe + (long)row * AB_DK + lane, a0);
-        atomicAdd(dpe + (long)row * AB_DK + lane + 32, a1);
-    }
-}
-
-int attention_bwd_launch(const float* qkv, const float* pe, int pe_rows, const float* dO, float* dqkv, float* dpe, float* Pg,
-                         float* dSg, long N, int T, int H, int dk, cudaStream_t st) {
-    CSS_REQUIRE(dk == AB_DK, "attention_bwd: head dim %d unsupported (kernel is built for 64)", dk);
-    CSS_REQUIRE(N > 0 && T > 0 && T <= 256, "attention_bwd: T=%d out of range (1..256)", T);
-    const int TP = (T + 31) & ~31;
-    const size_t smem1 = sizeof(float) * ((size_t)AB_DK * TP + (size_t)AB_DK * 2 * TP + AB_WARPS * TP + 2 * AB_WARPS * AB_DK);
-    const size_t smem2 = sizeof(float) * 2 * (size_t)T * AB_DK;
-    CSS_REQUIRE(smem1 <= 227 * 1024 && smem2 <= 227 * 1024, "attention_bwd: T=%d needs too much shared memory", T);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(attn_bwd_ds_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        cudaFuncSetAttribute(attn_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        attr_set = true;
-    }
-    css_prof_begin(1, 12.0 * (double)N * H * T * T * AB_DK, st);
-    attn_bwd_ds_kernel<<<(unsigned)(N * H), AB_WARPS * 32, smem1, st>>>(qkv, pe, pe_rows, pe != nullptr, dO, Pg, dSg, dqkv, T, H);
-    int rc = css_check_launch("attn_bwd_ds");
-    if (!rc) {
-        attn_bwd_kv_kernel<<<(unsigned)(N * H), AB_WARPS * 32, smem2, st>>>(qkv, dO, Pg, dSg, dqkv, dpe, pe_rows, pe != nullptr, T, H);
-        rc = css_check_launch("attn_bwd_kv");
-    }
-    css_prof_end(st);
-    return rc;
-}
-
-// ---------------------------------------------------------------------------------------------
 // Conv module in training mode (css/models/conformer.py:289-303 with BatchNorm1d batch statistics).
 // ---------------------------------------------------------------------------------------------
 #define CT_D 256
