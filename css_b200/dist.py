@@ -60,3 +60,140 @@ def gather_waveforms(local, lengths, rank, world, dst=0):
         for s, i in enumerate(shard_recordings(lengths, r, world)):
             res[i] = out[r][s, :, : lengths[i]]
     return res
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# One long recording sharded across the GPUs of a box (BASELINE.json configs[4]: 1-hour 7-ch meeting)
+# ---------------------------------------------------------------------------------------------------------------
+HALO = 2   # a stitched frame averages up to 3 consecutive chunks (stitcher.py:96-110): 2 neighbours on either side
+
+
+def chunk_ranges(n_chunks, world):
+    """Contiguous, near-equal chunk ranges [c0, c1) per rank (ranks beyond the chunk count get empty ranges)."""
+    base, rem = divmod(n_chunks, world)
+    out, c = [], 0
+    for r in range(world):
+        n = base + (1 if r < rem else 0)
+        out.append((c, c + n))
+        c += n
+    return out
+
+
+def extended_range(c0, c1, n_chunks, halo=HALO):
+    """Chunks a rank evaluates: its own plus `halo` recomputed neighbours on each side (no mask exchange needed)."""
+    return max(0, c0 - halo), min(n_chunks, c1 + halo)
+
+
+def owned_parity(state_local, c0, c1, e0):
+    """XOR of the swap bits of the pairs (k, k+1) with k+1 in [c0, c1), from the rank-local prefix states
+    (state_local[j] = XOR of the local swap bits before local chunk j).  Works on tensors or lists."""
+    lo = max(c0 - 1, 0) - e0
+    return state_local[c1 - 1 - e0] ^ state_local[lo]
+
+
+def first_state(prefix_parity, state_local, c0, e0):
+    """Global permutation state of the rank's first evaluated chunk e0, given the XOR of the owned parities of all
+    earlier ranks (= state of chunk c0-1)."""
+    if c0 == 0:
+        return prefix_parity * 0
+    return prefix_parity ^ state_local[c0 - 1 - e0]
+
+
+class ShardedCssPipeline:
+    """``CssPipeline`` for ONE recording split into contiguous chunk ranges, one per rank.
+
+    Every rank evaluates the masks of its own chunks plus a 2-chunk halo on each side (recomputed rather than exchanged:
+    4 extra chunks against hundreds), decides the chunk-pair permutations locally (the kernels are deterministic, so a
+    halo pair gets the same bit on both ranks), and the only data-path exchange is an all-gather of one parity bit per
+    rank that turns the rank-local permutation states into global ones (stitcher.py:55-60 is a prefix XOR).  MVDR and
+    the iSTFT placement run on the owned chunks with the GLOBAL placement plan (its 32-chunk batch seams are defined by
+    global chunk indices, beamformer.py:54-57); the per-rank partial waveforms are summed onto rank 0 (NCCL reduce over
+    NVLink), which applies the global peak normalisation (beamformer.py:122-123).  Results equal the single-GPU
+    pipeline's bit for bit.
+    """
+
+    def __init__(self, cfg, model, device, rank, world, group=None):
+        from .pipeline import CssPipeline
+
+        self.pipe = CssPipeline(cfg, model, device=device)
+        self.rank, self.world, self.group = rank, world, group
+        self.device = torch.device(device)
+
+    def _phase1(self, wav, c0, c1, B):
+        """Masks, local pair decisions and local prefix states of the chunk range [c0, c1) plus its halo."""
+        sep, st = self.pipe.separator, self.pipe.stitcher
+        dev = self.device
+        e0, e1 = extended_range(c0, c1, B)
+        lo, hi = e0 * sep.eval_hop, (e1 - 1) * sep.eval_hop + sep.chunk_len
+        local = wav[:, lo:hi].to(dev, torch.float32, non_blocking=True)
+        masks, mags = sep.separate(local)
+        swap = st.stitch_device(mags, masks)
+        state_local = torch.zeros(e1 - e0, dtype=torch.int32, device=dev)
+        if e1 - e0 > 1:
+            state_local[1:] = (torch.cumsum(swap, 0) & 1).to(torch.int32)
+        return {"c0": c0, "c1": c1, "e0": e0, "e1": e1, "local": local, "masks": masks, "swap": swap, "state_local": state_local,
+                "spec": sep.last["spec"], "parity": owned_parity(state_local, c0, c1, e0).reshape(1)}
+
+    def _phase2(self, ctx, prefix, B, T, out):
+        """Global states -> stitched masks -> MVDR of the range -> placement of the OWNED chunks into out (2, T)."""
+        st, bf = self.pipe.stitcher, self.pipe.beamformer
+        c0, c1, e0, e1 = ctx["c0"], ctx["c1"], ctx["e0"], ctx["e1"]
+        s0 = first_state(prefix, ctx["state_local"], c0, e0).reshape(1)
+        stitched = st.connect_device(ctx["swap"], ctx["masks"], state0=s0)
+        Y = bf.beamform_chunks(ctx["local"], stitched, e1 - e0, spec=ctx["spec"])
+        layers = []
+        for items in bf._plan(B, T, out.device):
+            keep = (items[:, 0] >= c0) & (items[:, 0] < c1)
+            sub = items[keep].clone()
+            sub[:, 0] -= e0
+            layers.append(sub.contiguous())
+        bf.place(Y, layers, out)
+        return st.last_state[c0 - e0 : c1 - e0]
+
+    def __call__(self, wav, return_intermediates=False):
+        """wav: (7, T) fp32 host (pinned) or device, the same on every rank -> (2, T) on rank 0, None elsewhere."""
+        sep, bf = self.pipe.separator, self.pipe.beamformer
+        D, T = wav.shape
+        B = sep.n_chunks(T)
+        if B < 1:
+            raise RuntimeError(f"waveform of {T} samples is shorter than one window of {sep.chunk_len}")
+        c0, c1 = chunk_ranges(B, self.world)[self.rank]
+        dev = self.device
+        out = torch.zeros(2, T, dtype=torch.float32, device=dev)
+        ctx = self._phase1(wav, c0, c1, B) if c1 > c0 else None
+        parity = ctx["parity"] if ctx else torch.zeros(1, dtype=torch.int32, device=dev)
+        if self.world > 1:
+            allp = torch.zeros(self.world, dtype=torch.int32, device=dev)
+            dist.all_gather_into_tensor(allp, parity.contiguous(), group=self.group)
+        else:
+            allp = parity
+        states = None
+        if ctx:
+            prefix = (allp[: self.rank].sum() & 1).to(torch.int32).reshape(1)
+            states = self._phase2(ctx, prefix, B, T, out)
+        if self.world > 1:
+            dist.reduce(out, dst=0, op=dist.ReduceOp.SUM, group=self.group)
+        if self.rank == 0:
+            bf.peak_normalize(out)
+        res = out if self.rank == 0 else None
+        return (res, {"state": states, "range": (c0, c1)}) if return_intermediates else res
+
+    def emulate(self, wav, world):
+        """Single-process emulation of a `world`-rank run (the ranks' work executed one after the other on this GPU,
+        the parity all-gather and the final sum done in place).  Used by the parity tests on one-GPU boxes."""
+        sep, bf = self.pipe.separator, self.pipe.beamformer
+        D, T = wav.shape
+        B = sep.n_chunks(T)
+        out = torch.zeros(2, T, dtype=torch.float32, device=self.device)
+        ranges = chunk_ranges(B, world)
+        ctxs = [self._phase1(wav, c0, c1, B) if c1 > c0 else None for c0, c1 in ranges]
+        zero = torch.zeros(1, dtype=torch.int32, device=self.device)
+        allp = torch.cat([c["parity"] if c else zero for c in ctxs])
+        states = []
+        for r, ctx in enumerate(ctxs):
+            if ctx:
+                part = torch.zeros_like(out)
+                states.append(self._phase2(ctx, (allp[:r].sum() & 1).to(torch.int32).reshape(1), B, T, part))
+                out += part
+        bf.peak_normalize(out)
+        return out, torch.cat(states)

@@ -134,6 +134,14 @@ class Beamformer:
         if B < 1:
             raise RuntimeError(f"waveform of {T} samples is shorter than one window of {chunk_len}")
         stitched = self.stitched_layout(masks, dev)
+        Y = self.beamform_chunks(X, stitched, B, spec)
+        out = torch.zeros(2, T, dtype=torch.float32, device=dev)
+        self.place(Y, self._plan(B, T, dev), out)
+        self.peak_normalize(out)
+        return out[0:1], out[1:2]
+
+    def beamform_chunks(self, X, stitched, B, spec=None):
+        """MVDR + rescale + dedup of chunks 0..B-1 of X (beamformer.py:60-80) -> Y (B, 2, mask_win, KP, 2)."""
         frames = self.mask_hop * (B - 1) + self.mask_win
         if stitched.shape[1] < frames:
             raise RuntimeError(f"masks cover {stitched.shape[1]} frames, need {frames}")
@@ -142,13 +150,20 @@ class Beamformer:
         edge = stft_edge(X, B, self.eval_hop)
         Y, energy = self._mvdr(spec, edge, stitched, B, spec.shape[1])
         self.last_scal = self._finalize(Y, energy, dedup=True)
-        out = torch.zeros(2, T, dtype=torch.float32, device=dev)
-        for items in self._plan(B, T, dev):
-            nv.call("css_istft_place", nv.ptr(Y), nv.c_int(self.mask_win), nv.ptr(items), nv.c_int(items.shape[0]),
-                    nv.ptr(out), nv.c_long(T))
-        scratch = torch.empty(2, dtype=torch.int32, device=dev)
-        nv.call("css_peak_normalize", nv.ptr(out), nv.c_int(2), nv.c_long(T), nv.c_float(0.9), nv.ptr(scratch))
-        return out[0:1], out[1:2]
+        return Y
+
+    def place(self, Y, layers, out):
+        """iSTFT + slice placement (beamformer.py:83-118) of the plan layers into out (2, T), accumulated."""
+        for items in layers:
+            if items.shape[0]:
+                nv.call("css_istft_place", nv.ptr(Y), nv.c_int(self.mask_win), nv.ptr(items), nv.c_int(items.shape[0]),
+                        nv.ptr(out), nv.c_long(out.shape[1]))
+
+    @staticmethod
+    def peak_normalize(out):
+        """beamformer.py:122-123: every output scaled to a peak of 0.9, in place."""
+        scratch = torch.empty(out.shape[0], dtype=torch.int32, device=out.device)
+        nv.call("css_peak_normalize", nv.ptr(out), nv.c_int(out.shape[0]), nv.c_long(out.shape[1]), nv.c_float(0.9), nv.ptr(scratch))
 
     def process_one_batch(self, x, speech_mask, noise_mask):
         """x: (B, D, N) windows, masks (B, F, T) -> beamformed (B, F, T) complex64 (beamformer.py:126-163)."""

@@ -37,8 +37,11 @@ class Stitcher:
         swap = self.stitch_device(x, masks)
         return [[1, 0] if v else [0, 1] for v in swap.tolist()]
 
-    def connect_device(self, swap, masks):
-        """-> stitched [3][L][KP] fp32 CUDA (bin fastest; the beamformer's native layout)."""
+    def connect_device(self, swap, masks, state0=None):
+        """-> stitched [3][L][KP] fp32 CUDA (bin fastest; the beamformer's native layout).
+
+        ``state0`` (1-element int32 CUDA tensor, optional) is the permutation state of the first chunk -- non-zero when
+        ``masks`` is a chunk range in the middle of a recording that is sharded across GPUs (css_b200/dist.py)."""
         masks = nv.require_cuda(masks, "masks").float().contiguous()
         B, F, T, C = masks.shape
         if F != nv.NBINS or C != 3:
@@ -49,6 +52,8 @@ class Stitcher:
         state = torch.empty(B, dtype=torch.int32, device=masks.device)
         swap = swap.to(masks.device, torch.int32).contiguous() if swap.numel() else torch.zeros(1, dtype=torch.int32, device=masks.device)
         nv.call("css_perm_states", nv.ptr(swap), nv.c_long(B), nv.ptr(state))
+        if state0 is not None:
+            state ^= state0.to(state.device, torch.int32).reshape(1)
         L = hop * (B - 1) + T
         out = torch.empty(3, L, nv.KP, dtype=torch.float32, device=masks.device)
         nv.call("css_stitch_connect", nv.ptr(masks), nv.ptr(state), nv.c_long(B), nv.c_int(T), nv.c_int(C), nv.c_int(hop), nv.ptr(out))

@@ -48,3 +48,43 @@ def test_gather_world2_gloo():
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=10) is True
+
+
+def test_long_recording_shard_plan():
+    """Host logic of the one-recording sharding: ranges partition the chunks, halos stay in bounds, and the parity
+    exchange reproduces the global prefix-XOR permutation states for random swap bits."""
+    import random
+
+    from css_b200.dist import chunk_ranges, extended_range, first_state, owned_parity
+
+    rng = random.Random(0)
+    for B in (1, 2, 3, 7, 72, 747, 4497):
+        swaps = [rng.randint(0, 1) for _ in range(B - 1)]
+        state = [0]
+        for s in swaps:
+            state.append(state[-1] ^ s)                      # stitcher.py:55-60
+        for world in (1, 2, 3, 8):
+            ranges = chunk_ranges(B, world)
+            assert ranges[0][0] == 0 and ranges[-1][1] == B and all(a[1] == b[0] for a, b in zip(ranges, ranges[1:]))
+            assert max(c1 - c0 for c0, c1 in ranges) - min(c1 - c0 for c0, c1 in ranges) <= 1
+            parities, locals_ = [], []
+            for c0, c1 in ranges:
+                if c1 == c0:
+                    parities.append(0); locals_.append(None)
+                    continue
+                e0, e1 = extended_range(c0, c1, B)
+                assert 0 <= e0 <= c0 and c1 <= e1 <= B
+                sl = [0]
+                for s in swaps[e0:e1 - 1]:
+                    sl.append(sl[-1] ^ s)
+                locals_.append((sl, e0, e1))
+                parities.append(owned_parity(sl, c0, c1, e0))
+            for r, (c0, c1) in enumerate(ranges):
+                if c1 == c0:
+                    continue
+                sl, e0, e1 = locals_[r]
+                prefix = 0
+                for p in parities[:r]:
+                    prefix ^= p
+                s0 = first_state(prefix, sl, c0, e0)
+                assert [s0 ^ v for v in sl] == state[e0:e1]
