@@ -125,7 +125,12 @@ class ShardedCssPipeline:
         dev = self.device
         e0, e1 = extended_range(c0, c1, B)
         lo, hi = e0 * sep.eval_hop, (e1 - 1) * sep.eval_hop + sep.chunk_len
-        local = wav[:, lo:hi].to(dev, torch.float32, non_blocking=True)
+        if wav.is_cuda:
+            local = wav[:, lo:hi].to(dev, torch.float32)
+        else:   # row-wise copies: a strided host slice would be staged through pageable memory
+            local = torch.empty(wav.shape[0], hi - lo, dtype=torch.float32, device=dev)
+            for d in range(wav.shape[0]):
+                local[d].copy_(wav[d, lo:hi], non_blocking=True)
         masks, mags = sep.separate(local)
         swap = st.stitch_device(mags, masks)
         state_local = torch.zeros(e1 - e0, dtype=torch.int32, device=dev)
