@@ -8,7 +8,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libcss_b200.so")
+LIB_PATH = os.environ.get("CSS_B200_LIB") or os.path.join(_HERE, "csrc", "libcss_b200.so")   # override: A/B of kernel builds
 KP = 264
 NBINS = 257
 

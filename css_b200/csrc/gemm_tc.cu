@@ -136,7 +136,9 @@ struct Cfg {
     static_assert(STAGES >= 2, "tile does not fit a 2-stage ring");
 };
 
-template <int P, int BN, int BK>
+// TRAIN = false is the inference instantiation: no split-K bookkeeping and no mask test in the epilogue (they cost the
+// K = 256 GEMMs, whose tile time is set by the epilogue, 27 % when they were run-time branches)
+template <int P, int BN, int BK, bool TRAIN>
 __global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
                TcEpilogue ep) {
@@ -153,7 +155,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int m_tiles = (int)((M + BM - 1) / BM), n_tiles = (N + BN - 1) / BN;
-    const int ksplit = ep.ksplit > 1 ? ep.ksplit : 1;
+    const int ksplit = TRAIN ? (ep.ksplit > 1 ? ep.ksplit : 1) : 1;
     const int tiles = m_tiles * n_tiles;
     const int total = tiles * ksplit;
     const int kblocks = K / BK;
@@ -182,9 +184,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             int stage = 0; uint32_t phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
-                const int tt = t % tiles, sp = t / tiles;
+                const int tt = TRAIN ? t % tiles : t, sp = TRAIN ? t / tiles : 0;
                 const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
-                const int kb0 = sp * kper, kb1 = min(kblocks, kb0 + kper);
+                const int kb0 = TRAIN ? sp * kper : 0, kb1 = TRAIN ? min(kblocks, kb0 + kper) : kblocks;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty[stage], phase ^ 1);
                     mbar_expect_tx(&full[stage], C::STAGE_BYTES);
@@ -210,8 +212,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 mbar_wait(&tempty[acc], acc_phase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
-                const int sp = t / tiles;
-                const int kb0 = sp * kper, kb1 = min(kblocks, kb0 + kper);
+                const int sp = TRAIN ? t / tiles : 0;
+                const int kb0 = TRAIN ? sp * kper : 0, kb1 = TRAIN ? min(kblocks, kb0 + kper) : kblocks;
                 for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&full[stage], phase);
                     tc_fence_after();
@@ -244,7 +246,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int cg = lane & 7, rsub = lane >> 3;
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
-            const int tt = t % tiles;
+            const int tt = TRAIN ? t % tiles : t;
             const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
@@ -291,11 +293,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         }
                     }
                 }
+                // all shared-memory reads of the chunk before the first global store: the compiler cannot prove that the
+                // (generic) staging pointer and the outputs do not alias, so a load inside the store loop would serialise it
+                float4 xs[8];
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int rr = it * 4 + rsub;
+                    xs[it] = stg[rr * 8 + (cg ^ (rr & 7))];
+                }
 #pragma unroll
                 for (int it = 0; it < 8; ++it) {
                     const int rr = it * 4 + rsub;
                     const long row = row_base + rr;
-                    const float4 x4 = stg[rr * 8 + (cg ^ (rr & 7))];
+                    const float4 x4 = xs[it];
                     if (row >= M) continue;
                     float v[4] = {x4.x + b4[0], x4.y + b4[1], x4.z + b4[2], x4.w + b4[3]};
 #pragma unroll
@@ -305,13 +315,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         v[i] *= ep.alpha;
                     }
                     if (ep.residual) { v[0] += res4[it].x; v[1] += res4[it].y; v[2] += res4[it].z; v[3] += res4[it].w; }
-                    if (ep.mask) {
+                    if (TRAIN && ep.mask) {
                         const __nv_bfloat16* mp = ep.mask + row * ep.ldmask + col;
 #pragma unroll
                         for (int i = 0; i < 4; ++i)
                             if (col + i < N && !(__bfloat162float(mp[i]) > 0.f)) v[i] = 0.f;
                     }
-                    if (ksplit > 1) {
+                    if (TRAIN && ksplit > 1) {
                         float* cp = ep.c + row * ep.ldc + col;
 #pragma unroll
                         for (int i = 0; i < 4; ++i) if (col + i < N) atomicAdd(cp + i, v[i]);
@@ -416,15 +426,18 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
     int rc;
     if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
     if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
+    const bool train = ep.mask != nullptr || ep.ksplit > 1;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
         attr = true;
     }
     const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (ep.ksplit > 1 ? ep.ksplit : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    gemm_tc_kernel<P, BN, BK><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    if (train) gemm_tc_kernel<P, BN, BK, true><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else gemm_tc_kernel<P, BN, BK, false><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     return css_check_launch("gemm_tc");
 }
 
