@@ -138,7 +138,10 @@ struct Cfg {
 
 // TRAIN = false is the inference instantiation: no split-K bookkeeping and no mask test in the epilogue (they cost the
 // K = 256 GEMMs, whose tile time is set by the epilogue, 27 % when they were run-time branches)
-template <int P, int BN, int BK, bool TRAIN>
+// EM selects the epilogue: 0 generic; 1 bias (+ReLU) -> NPL = P bf16 planes only (FFN-in, QKV); 2 (acc + bias) * alpha
+// + residual -> fp32 only (FFN-out, attention out-projection).  The lean forms need N % 32 == 0 and are chosen on the host;
+// the K = 256 GEMMs are bound by epilogue instruction issue, so every instruction removed there is tile time.
+template <int P, int BN, int BK, bool TRAIN, int EM>
 __global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
                TcEpilogue ep) {
@@ -266,6 +269,66 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 __syncwarp();
                 // phase B: 8 lanes cover one 128-byte row segment -> coalesced global traffic
                 const int col = col0 + cg * 4;
+                if constexpr (EM == 1 || EM == 2) {
+                    float4 xs[8];
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) {
+                        const int rr = it * 4 + rsub;
+                        xs[it] = stg[rr * 8 + (cg ^ (rr & 7))];
+                    }
+                    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (ep.bias) bb = make_float4(__ldg(ep.bias + col), __ldg(ep.bias + col + 1), __ldg(ep.bias + col + 2), __ldg(ep.bias + col + 3));
+                    const long row0 = row_base + rsub;
+                    if constexpr (EM == 1) {
+                        const float floor_v = ep.act == 1 ? 0.f : -INFINITY;
+                        __nv_bfloat16* pp = ep.planes + row0 * ep.ldp + col;
+#pragma unroll
+                        for (int it = 0; it < 8; ++it) {
+                            if (row0 + it * 4 >= M) continue;
+                            float v0 = fmaxf(xs[it].x + bb.x, floor_v), v1 = fmaxf(xs[it].y + bb.y, floor_v);
+                            float v2 = fmaxf(xs[it].z + bb.z, floor_v), v3 = fmaxf(xs[it].w + bb.w, floor_v);
+                            __nv_bfloat16* dst = pp + (long)(it * 4) * ep.ldp;
+#pragma unroll
+                            for (int p = 0; p < P; ++p) {
+                                const __nv_bfloat162 h01 = __floats2bfloat162_rn(v0, v1);
+                                const __nv_bfloat162 h23 = __floats2bfloat162_rn(v2, v3);
+                                uint2 w;
+                                w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                                w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                                *reinterpret_cast<uint2*>(dst + p * ep.plane_stride) = w;
+                                if (p + 1 < P) {
+                                    v0 -= __uint_as_float(w.x << 16); v1 -= __uint_as_float(w.x & 0xffff0000u);
+                                    v2 -= __uint_as_float(w.y << 16); v3 -= __uint_as_float(w.y & 0xffff0000u);
+                                }
+                            }
+                        }
+                    } else {
+                        float4 res4[8];
+                        if (ep.residual) {
+                            const float* rp = ep.residual + row0 * ep.ldr + col;
+#pragma unroll
+                            for (int it = 0; it < 8; ++it)
+                                res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr)
+                                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                        } else {
+#pragma unroll
+                            for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+                        float* cp = ep.c + row0 * ep.ldc + col;
+#pragma unroll
+                        for (int it = 0; it < 8; ++it) {
+                            if (row0 + it * 4 >= M) continue;
+                            float4 o;
+                            o.x = fmaf(xs[it].x + bb.x, ep.alpha, res4[it].x);
+                            o.y = fmaf(xs[it].y + bb.y, ep.alpha, res4[it].y);
+                            o.z = fmaf(xs[it].z + bb.z, ep.alpha, res4[it].z);
+                            o.w = fmaf(xs[it].w + bb.w, ep.alpha, res4[it].w);
+                            *reinterpret_cast<float4*>(cp + (long)(it * 4) * ep.ldc) = o;
+                        }
+                    }
+                    __syncwarp();
+                    continue;
+                }
                 float b4[4] = {0.f, 0.f, 0.f, 0.f};
                 if (ep.bias) {
 #pragma unroll
@@ -419,6 +482,9 @@ int sm_count() {
     return n;
 }
 
+static int g_lean_epilogue = 1;   // 0: always the generic epilogue (A/B switch)
+extern "C" void css_gemm_tc_lean_epilogue(int on) { g_lean_epilogue = on; }
+
 template <int P, int BN, int BK>
 static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
     using C = Cfg<P, BN, BK>;
@@ -427,17 +493,26 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
     if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
     if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
     const bool train = ep.mask != nullptr || ep.ksplit > 1;
+    const bool lean_ok = !train && g_lean_epilogue && N % 32 == 0 && ep.clamp_max <= 0.f;
+    int em = 0;
+    if (lean_ok && ep.planes && !ep.c && !ep.residual && ep.alpha == 1.f && ep.n_planes == P && ep.ldp == N) em = 1;
+    else if (lean_ok && ep.c && !ep.planes && ep.act == 0 && (ep.ldc & 3) == 0 && (!ep.residual || (ep.ldr & 3) == 0) &&
+             ((uintptr_t)ep.c & 15) == 0 && ((uintptr_t)ep.residual & 15) == 0) em = 2;
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
         attr = true;
     }
     const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (ep.ksplit > 1 ? ep.ksplit : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-    if (train) gemm_tc_kernel<P, BN, BK, true><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
-    else gemm_tc_kernel<P, BN, BK, false><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    if (train) gemm_tc_kernel<P, BN, BK, true, 0><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else if (em == 1) gemm_tc_kernel<P, BN, BK, false, 1><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else if (em == 2) gemm_tc_kernel<P, BN, BK, false, 2><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else gemm_tc_kernel<P, BN, BK, false, 0><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     return css_check_launch("gemm_tc");
 }
 
