@@ -18,18 +18,21 @@ __device__ __forceinline__ float2 unit_cross(float2 a, float2 b) {
         return make_float2(-1.f, na ? -8.742278e-8f : 8.742278e-8f);
     }
     float2 p = cmulc(a, b);
-    float n = sqrtf(p.x * p.x + p.y * p.y);
-    if (n == 0.f) {
-        // phase(a) - phase(b) with the zero operand's phase taken as 0
-        float na = sqrtf(a.x * a.x + a.y * a.y), nb = sqrtf(b.x * b.x + b.y * b.y);
+    const float n2 = p.x * p.x + p.y * p.y;
+    if (n2 < 1e-30f || n2 > 1e30f) {
+        // vanishing or huge product: normalise the operands first (phase(a) - phase(b), a zero operand's phase taken as 0)
+        const float na = sqrtf(a.x * a.x + a.y * a.y), nb = sqrtf(b.x * b.x + b.y * b.y);
         if (na == 0.f && nb == 0.f) return make_float2(1.f, 0.f);
         if (na == 0.f) return make_float2(b.x / nb, -b.y / nb);
         if (nb == 0.f) return make_float2(a.x / na, a.y / na);
-        // underflow of the product: normalise first
         a.x /= na; a.y /= na; b.x /= nb; b.y /= nb;
         return cmulc(a, b);
     }
-    return make_float2(p.x / n, p.y / n);
+    // one MUFU.RSQ + a Newton step (full fp32 accuracy) instead of sqrt and two IEEE divisions: this function runs
+    // 2 x 6 x 150 times per bin and the kernel is bound by instruction issue, not by HBM
+    float r = rsqrtf(n2);
+    r = r * (1.5f - 0.5f * n2 * r * r);
+    return make_float2(p.x * r, p.y * r);
 }
 
 // One block per chunk; thread k owns bin k.  spec element (d, chunk b, frame t, bin k) lives at
@@ -144,30 +147,45 @@ extern "C" int css_features(const void* spec, long stride_d, long stride_chunk, 
 }
 
 // Same normalisation, written as bf16 split planes (pitch ldp >= F, padding columns zeroed) for the tcgen05 embed GEMM;
-// x is left untouched.
-__global__ void mvn_time_planes_kernel(const float* __restrict__ x, int T, int F, int ld, __nv_bfloat16* __restrict__ planes,
-                                       long plane_stride, int ldp, int n_planes) {
+// x is left untouched.  One CTA per (sequence, 64 features): the (T x 64) tile is staged in shared memory with all its
+// loads in flight at once, then thread (feature, quarter of the frames) reduces and emits its share.
+#define MVN_F 64
+__global__ void __launch_bounds__(256)
+mvn_time_planes_kernel(const float* __restrict__ x, int T, int F, int ld, __nv_bfloat16* __restrict__ planes,
+                       long plane_stride, int ldp, int n_planes) {
+    extern __shared__ float mvn_tile[];          // [T][MVN_F]
+    __shared__ float red[4][MVN_F];
+    __shared__ float stat[2][MVN_F];
     const long n = blockIdx.x;
-    const int f = blockIdx.y * blockDim.x + threadIdx.x;
-    if (f >= ldp) return;
-    __nv_bfloat16* out = planes + n * (long)T * ldp + f;
-    if (f >= F) {
-        for (int p = 0; p < n_planes; ++p)
-            for (int t = 0; t < T; ++t) out[p * plane_stride + (long)t * ldp] = __float2bfloat16_rn(0.f);
-        return;
-    }
-    const float* col = x + n * (long)T * ld + f;
+    const int f0 = blockIdx.y * MVN_F;
+    const int f = threadIdx.x & (MVN_F - 1), part = threadIdx.x >> 6;
+    const float* src = x + n * (long)T * ld + f0 + f;
+    const bool live = f0 + f < F;
+    for (int t = part; t < T; t += 4) mvn_tile[t * MVN_F + f] = live ? src[(long)t * ld] : 0.f;
+    __syncthreads();
+    const int per = (T + 3) / 4;
+    const int t0 = part * per, t1 = min(T, t0 + per);
     float s = 0.f;
-    for (int t = 0; t < T; ++t) s += col[(long)t * ld];
-    const float mean = s / T;
+    for (int t = t0; t < t1; ++t) s += mvn_tile[t * MVN_F + f];
+    red[part][f] = s;
+    __syncthreads();
+    if (part == 0) stat[0][f] = (red[0][f] + red[1][f] + red[2][f] + red[3][f]) / T;
+    __syncthreads();
+    const float mean = stat[0][f];
     float v = 0.f;
-    for (int t = 0; t < T; ++t) {
-        float d = col[(long)t * ld] - mean;
+    for (int t = t0; t < t1; ++t) {
+        const float d = mvn_tile[t * MVN_F + f] - mean;
         v += d * d;
     }
-    const float inv = 1.f / (sqrtf(v / (T - 1)) + FEAT_EPS);
-    for (int t = 0; t < T; ++t) {
-        float r = (col[(long)t * ld] - mean) * inv;
+    red[part][f] = v;
+    __syncthreads();
+    if (part == 0) stat[1][f] = 1.f / (sqrtf((red[0][f] + red[1][f] + red[2][f] + red[3][f]) / (T - 1)) + FEAT_EPS);
+    __syncthreads();
+    if (f0 + f >= ldp) return;
+    const float inv = stat[1][f];
+    __nv_bfloat16* out = planes + n * (long)T * ldp + f0 + f;
+    for (int t = t0; t < t1; ++t) {
+        float r = live ? (mvn_tile[t * MVN_F + f] - mean) * inv : 0.f;
         for (int p = 0; p < n_planes; ++p) {
             const __nv_bfloat16 h = __float2bfloat16_rn(r);
             r -= __bfloat162float(h);
@@ -179,8 +197,15 @@ __global__ void mvn_time_planes_kernel(const float* __restrict__ x, int T, int F
 int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* planes, long plane_stride, int ldp, int n_planes,
                            cudaStream_t st) {
     CSS_REQUIRE(n > 0 && T > 1 && F > 0 && ld >= F && ldp >= F, "mvn_time_planes: bad shape");
-    dim3 grid((unsigned)n, (ldp + 127) / 128);
-    mvn_time_planes_kernel<<<grid, 128, 0, st>>>(x, T, F, ld, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, n_planes);
+    CSS_REQUIRE(T <= 512, "mvn_time_planes: T=%d exceeds the shared-memory tile (512 frames)", T);
+    const size_t smem = sizeof(float) * (size_t)T * MVN_F;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(mvn_time_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * MVN_F * 4);
+        attr_set = true;
+    }
+    dim3 grid((unsigned)n, (ldp + MVN_F - 1) / MVN_F);
+    mvn_time_planes_kernel<<<grid, 256, smem, st>>>(x, T, F, ld, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, n_planes);
     return css_check_launch("mvn_time_planes");
 }
 

@@ -62,7 +62,10 @@ def test_train_step_matches_reference_golden(cuda, gtrain):
         if key.startswith("E_param2/"):
             name = key[len("E_param2/"):]
             got, ref = _sub(named[name]), gtrain[key]
-            assert np.abs(got - ref).max() <= 2e-6 + 1e-4 * np.abs(ref).max(), name
+            # Adam moves every element by about lr = 1e-4 per step whatever the gradient's size, so an element whose
+            # gradient is at rounding-noise level may differ by a fraction of lr; all others must agree to ~1e-2 lr
+            diff = np.abs(got - ref)
+            assert diff.max() <= 2e-5 and np.quantile(diff, 0.99) <= 1e-6, (name, diff.max(), np.quantile(diff, 0.99))
     bn = model.conformer.encoders[1].conv.BN
     assert rel_inf(bn.running_var, gtrain["E_bn_running_var"]) < 1e-4
     assert np.abs(bn.running_mean.cpu().numpy() - gtrain["E_bn_running_mean"]).max() < 1e-5
