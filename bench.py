@@ -7,8 +7,8 @@
 One step = one synthetic 7-mic LibriCSS-shaped session (default 600 s, 747 chunks) through the whole hot path:
 global STFT -> IPD features -> 16-block Conformer masks -> DOA merge -> stitch -> MVDR -> iSTFT/placement ->
 peak normalisation.  `value` times the path with the waveform already resident in HBM; `e2e` times the
-public call (`CssPipeline.__call__`) from a pinned HOST waveform to the two separated waveforms back in
-pinned host memory.  N > 1 (torchrun, one rank per GPU): every rank separates its own session (weak scaling,
+public call (`CssPipeline.run_many`, one recording per step) from pinned HOST waveforms to the separated waveforms back in
+pinned host memory, every step's H2D and D2H inside the timed region (double-buffered around the compute).  N > 1 (torchrun, one rank per GPU): every rank separates its own session (weak scaling,
 no data-path collective -- sessions are independent, run.sh:21-36 of the reference); time = max over ranks.
 """
 import argparse
@@ -236,11 +236,13 @@ def run_b200(args):
     nv.check(lib.css_profile_collect(ms_c, work_c, cnt_c, ncat), "css_profile_collect")
     lib.css_profile_enable(0)
 
-    # ---- timed region 2: public call from pinned host memory, result back on the host (e2e) ----
+    # ---- timed region 2: public call from pinned host memory, results back on the host (e2e): one recording per step
+    # through CssPipeline.run_many, which double-buffers the H2D / D2H copies of consecutive recordings around the compute
+    outs_host = [out_host, torch.empty_like(out_host).pin_memory()]
+    pipe.run_many([wav_host] * 2, outs_host)
     barrier()
     e0.record()
-    for _ in range(args.steps):
-        step_e2e()
+    pipe.run_many([wav_host] * args.steps, [outs_host[i % 2] for i in range(args.steps)])
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))

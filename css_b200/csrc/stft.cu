@@ -9,7 +9,7 @@
 
 // frame g of signal s covers samples [256 g, 256 g + 512).
 __global__ void __launch_bounds__(STFT_WARPS * 32)
-stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_frames, float2* __restrict__ spec) {
+stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_frames, float2* __restrict__ spec, long spec_stride) {
     __shared__ FftTables tab;
     __shared__ float2 buf[STFT_WARPS][2][256];
     fft_tables_init(&tab);
@@ -27,7 +27,7 @@ stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_fra
         }
         __syncwarp();
         const float2* Z = warp_fft256(a, buf[warp][1], tab.tw, lane);
-        float2* dst = spec + (s * n_frames + g) * CSS_KP;
+        float2* dst = spec + (s * spec_stride + g) * CSS_KP;
         for (int k = lane; k < CSS_KP; k += 32)
             dst[k] = (k < CSS_NBINS) ? rfft_bin(Z, tab.tw, k) : make_float2(0.f, 0.f);
         __syncwarp();
@@ -73,8 +73,20 @@ extern "C" int css_stft(const float* x, long n_sig, long sig_stride, long n_fram
     long warps = n_sig * n_frames;
     int grid = (int)((warps + STFT_WARPS - 1) / STFT_WARPS);
     if (grid > 148 * 8) grid = 148 * 8;
-    stft_kernel<<<grid, STFT_WARPS * 32, 0, st>>>(x, n_sig, sig_stride, n_frames, (float2*)spec);
+    stft_kernel<<<grid, STFT_WARPS * 32, 0, st>>>(x, n_sig, sig_stride, n_frames, (float2*)spec, n_frames);
     return css_check_launch("css_stft");
+}
+
+// Frames [0, n_frames) of signals whose first sample is x + s * sig_stride, written to spec + s * spec_stride frames: lets a
+// caller fill a frame range of a larger [sig][frames][KP] buffer (recordings streamed to the device in segments).
+extern "C" int css_stft_range(const float* x, long n_sig, long sig_stride, long n_frames, void* spec, long spec_stride,
+                              cudaStream_t st) {
+    CSS_REQUIRE(n_sig > 0 && n_frames > 0 && spec_stride >= n_frames, "css_stft_range: bad shape (n_sig=%ld n_frames=%ld)", n_sig, n_frames);
+    long warps = n_sig * n_frames;
+    int grid = (int)((warps + STFT_WARPS - 1) / STFT_WARPS);
+    if (grid > 148 * 8) grid = 148 * 8;
+    stft_kernel<<<grid, STFT_WARPS * 32, 0, st>>>(x, n_sig, sig_stride, n_frames, (float2*)spec, spec_stride);
+    return css_check_launch("css_stft_range");
 }
 
 extern "C" int css_stft_edge(const float* x, long n_sig, long sig_stride, long n_chunks, long chunk_hop, void* edge,

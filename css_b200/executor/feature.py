@@ -5,6 +5,8 @@
 MVN/IPD kernel (``css_features``).  The executor's fast path uses ``stft``/``features`` directly
 and stays in the bin-fastest device layout.
 """
+import ctypes
+
 import torch
 
 from .. import _native as nv
@@ -30,6 +32,13 @@ def stft(x, n_frames=None):
     spec = torch.empty(n_sig, n_frames, nv.KP, 2, dtype=torch.float32, device=x.device)
     nv.call("css_stft", nv.ptr(x), nv.c_long(n_sig), nv.c_long(x.stride(0)), nv.c_long(n_frames), nv.ptr(spec))
     return spec
+
+
+def stft_range(x, spec, f0, f1):
+    """Frames [f0, f1) of x (n_sig, N) into the matching rows of spec (n_sig, L, KP, 2), in place."""
+    n_sig, L = spec.shape[0], spec.shape[1]
+    nv.call("css_stft_range", ctypes.c_void_p(x.data_ptr() + 4 * 256 * f0), nv.c_long(n_sig), nv.c_long(x.stride(0)), nv.c_long(f1 - f0),
+            ctypes.c_void_p(spec.data_ptr() + 8 * nv.KP * f0), nv.c_long(L))
 
 
 def stft_edge(x, n_chunks, chunk_hop):

@@ -15,7 +15,7 @@ import torch
 
 from .. import _native as nv
 from ..utils.model_util import B200Session, get_b200_model
-from .feature import FeatureExtractor, features, stft
+from .feature import FeatureExtractor, features, stft, stft_range
 
 CHUNK_EXTRA = 256   # separator.py:67
 
@@ -33,7 +33,7 @@ def steervec_7ch(nfreqs=257, nvecs=30, radius=0.0425, sndvelocity=340, samplerat
 
 class Separator:
     def __init__(self, separation_config, sr=16000, sess_options=None, device="cuda", backend="b200",
-                 lowcut=80, highcut=2000, model=None, max_chunks_per_launch=2048):
+                 lowcut=80, highcut=2000, model=None, max_chunks_per_launch=2048, stream_first_fraction=0.125):
         if backend not in ("b200", "native"):
             raise ValueError(f"Unknown backend: {backend}")
         self.device = torch.device(device)
@@ -59,6 +59,10 @@ class Separator:
         self.chunk_frames = (self.chunk_len - self.frame_length) // self.frame_shift + 1
         self.hop_frames = self.eval_hop // self.frame_shift
         self.max_chunks = max_chunks_per_launch
+        # a pinned host recording is copied in pieces: a small first one, whose chunks keep the GPU busy while the rest
+        # arrives (the mask network of 1/8 of the chunks takes about as long as the copy of the other 7/8)
+        self.stream_first_fraction = float(stream_first_fraction)
+        self._copy_stream = None
         # DOA merge; the 1-ch config has no `merge` keys (defect D1) -> default off
         self.merge = separation_config.get("merge", False)
         self.merge_threshold = separation_config.get("merge_threshold", 16)
@@ -77,13 +81,26 @@ class Separator:
     def n_chunks(self, T):
         return 0 if T < self.chunk_len else (T - self.chunk_len) // self.eval_hop + 1
 
-    def _masks(self, spec, stride_d, stride_chunk, B, D):
+    def _batches(self, B, first=0):
+        """[(b0, nb)]: an optional short first batch, then launches of at most max_chunks_per_launch chunks."""
+        out, b0 = [], 0
+        if 0 < first < B:
+            out.append((0, first))
+            b0 = first
+        while b0 < B:
+            nb = min(self.max_chunks, B - b0)
+            out.append((b0, nb))
+            b0 += nb
+        return out
+
+    def _masks(self, spec, stride_d, stride_chunk, B, D, batches=None, before_batch=None):
         il, ir = self.feature.ipd_tensors(spec.device)
         ldin = self.model.engine()["ldin"]
         T = self.chunk_frames
         mags, masks = [], []
-        for b0 in range(0, B, self.max_chunks):
-            nb = min(self.max_chunks, B - b0)
+        for i, (b0, nb) in enumerate(batches or self._batches(B)):
+            if before_batch is not None:
+                before_batch(i, b0, nb)
             sub = spec.reshape(-1)[b0 * stride_chunk * nv.KP * 2:]
             mag, feat = features(sub, stride_d, stride_chunk, nb, T, il, ir, ldin)
             m = self.model.masks_layout(feat, nb, T, clamp_max=1.0)
@@ -104,15 +121,55 @@ class Separator:
         """s: (D, T) waveform (CPU or CUDA) -> masks (B,257,150,3), mags (B,257,150) on the GPU."""
         if s.dim() != 2:
             raise RuntimeError(f"separate expects a (D, T) waveform, got {tuple(s.shape)}")
-        s = s.to(self.device, torch.float32, non_blocking=True)
         D, T = s.shape
         B = self.n_chunks(T)
         if B < 1:
             raise RuntimeError(f"waveform of {T} samples is shorter than one window of {self.chunk_len}")
         L = self.hop_frames * (B - 1) + self.chunk_frames
+        if not s.is_cuda and s.is_pinned() and s.dtype == torch.float32 and self.stream_first_fraction > 0 and B >= 64:
+            return self._separate_streamed(s, B, L)
+        s = s.to(self.device, torch.float32, non_blocking=True)
         spec = stft(s, n_frames=L)
         self.last = {"spec": spec, "wav": s, "n_chunks": B, "frames": L}
         return self._masks(spec, L, self.hop_frames, B, D)
+
+    def _separate_streamed(self, s, B, L):
+        """Pinned host recording: the H2D copy runs in pieces (one per batch of chunks) on a copy stream while the STFT, the
+        features and the mask network of the chunks already on the device run on the compute stream (each batch of
+        chunks waits only for the piece that holds its last sample).  Same arithmetic as the resident path: the
+        STFT frames of a batch are written into the one global spec buffer (frames shared with the previous batch
+        are recomputed to the same values)."""
+        D, T = s.shape
+        dev = self.device
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        main = torch.cuda.current_stream(dev)
+        wav = torch.empty(D, T, dtype=torch.float32, device=dev)
+        spec = torch.empty(D, L, nv.KP, 2, dtype=torch.float32, device=dev)
+        batches = self._batches(B, first=max(1, int(B * self.stream_first_fraction)))
+        events = []
+        self._copy_stream.wait_stream(main)            # wav/spec allocations are ordered before the copies
+        with torch.cuda.stream(self._copy_stream):
+            lo = 0
+            for b0, nb in batches:
+                last = b0 + nb - 1
+                hi = T if last == B - 1 else last * self.eval_hop + self.chunk_len
+                for d in range(D):
+                    wav[d, lo:hi].copy_(s[d, lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._copy_stream)
+                events.append(ev)
+                lo = hi
+        wav.record_stream(self._copy_stream)
+
+        def before_batch(i, b0, nb):
+            main.wait_event(events[i])
+            f0 = b0 * self.hop_frames
+            f1 = (b0 + nb - 1) * self.hop_frames + self.chunk_frames
+            stft_range(wav, spec, f0, f1)
+
+        self.last = {"spec": spec, "wav": wav, "n_chunks": B, "frames": L}
+        return self._masks(spec, L, self.hop_frames, B, D, batches=batches, before_batch=before_batch)
 
     def separate_one_batch(self, s):
         """s: (B, D, T) batch of windows -> masks (B,257,T',3), mags (B,257,T')."""

@@ -54,8 +54,8 @@ class CssPipeline:
         With a single channel (no MVDR possible, as in the reference's 1-ch flow) the stitched masks
         [3][L][KP] are returned instead.
         """
-        wav = wav.to(self.device, torch.float32, non_blocking=True)
-        masks, mags = self.separator.separate(wav)
+        masks, mags = self.separator.separate(wav)     # a pinned host recording is streamed to the device in pieces
+        wav = self.separator.last["wav"]
         swap = self.stitcher.stitch_device(mags, masks)
         stitched = self.stitcher.connect_device(swap, masks)
         if beamform is None:
@@ -71,3 +71,54 @@ class CssPipeline:
             return {"masks": masks, "mags": mags, "swap": swap, "stitched": stitched, "wavs": out,
                     "sims": self.stitcher.last_sims, "doa": self.separator.angle_merge_debug()}
         return out if beamform else stitched
+
+    def run_many(self, recordings, outputs=None):
+        """Separate a list of pinned host recordings (D, T_i) back to back, as the session loop of
+        scripts/python/separate_libricss.py:65-82 does, with the transfers double-buffered around the compute: the H2D
+        copy of recording i+1 and the D2H copy of result i-1 run on their own streams while recording i is separated.
+
+        outputs: optional list of pinned host tensors (2, T_i) to receive the results; returned (allocated if None).
+        The call returns when every result has landed on the host.
+        """
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_h2d", None) is None:
+            self._h2d, self._d2h = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        n = len(recordings)
+        if outputs is None:
+            outputs = [torch.empty(2, r.shape[1], dtype=torch.float32).pin_memory() for r in recordings]
+        bufs, staged, freed = [None, None], [None] * n, [None, None]
+
+        def stage(i):
+            r = recordings[i]
+            slot = i % 2
+            with torch.cuda.stream(self._h2d):
+                if freed[slot] is not None:
+                    self._h2d.wait_event(freed[slot])          # the previous user of this buffer has been separated
+                if bufs[slot] is None or bufs[slot].shape != r.shape:
+                    bufs[slot] = torch.empty(r.shape, dtype=torch.float32, device=dev)
+                bufs[slot].copy_(r, non_blocking=True)
+                staged[i] = torch.cuda.Event()
+                staged[i].record(self._h2d)
+
+        if n:
+            stage(0)
+        done = []
+        for i in range(n):
+            if i + 1 < n:
+                stage(i + 1)
+            main.wait_event(staged[i])
+            out = self(bufs[i % 2])
+            ev = torch.cuda.Event()
+            ev.record(main)
+            freed[i % 2] = ev
+            with torch.cuda.stream(self._d2h):
+                self._d2h.wait_event(ev)
+                outputs[i].copy_(out, non_blocking=True)
+                out.record_stream(self._d2h)
+                fin = torch.cuda.Event()
+                fin.record(self._d2h)
+                done.append(fin)
+        for fin in done:
+            fin.synchronize()
+        return outputs

@@ -28,6 +28,8 @@ int css_profile_collect(double* ms_host, double* work_host, long* count_host, in
 /* ---- STFT / features: css/executor/feature.py:45-82 (STFT.forward), :105-134, :156-175 ---- */
 /* spec[sig][frame][KP] complex64; frame g covers samples [256 g, 256 g + 512), Hann(512). */
 int css_stft(const float* x, long n_sig, long sig_stride, long n_frames, void* spec, css_stream_t stream);
+/* same, into a frame range of a larger buffer: signal s is read at x + s*sig_stride and written at spec + s*spec_stride frames */
+int css_stft_range(const float* x, long n_sig, long sig_stride, long n_frames, void* spec, long spec_stride, css_stream_t stream);
 /* centred-STFT frame 0 (reflect pad) of every chunk: css/executor/beamformer.py:137-145 */
 int css_stft_edge(const float* x, long n_sig, long sig_stride, long n_chunks, long chunk_hop, void* edge,
                   css_stream_t stream);

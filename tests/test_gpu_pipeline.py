@@ -208,3 +208,32 @@ def test_sixty_seconds_properties(cuda):
     # deterministic: a second run is bit-identical
     again = pipe(wav)
     assert torch.equal(again, got["wavs"])
+
+
+def test_streamed_host_recording_equals_resident(cuda):
+    """A pinned host recording is copied in overlapped pieces (Separator._separate_streamed): same bits as the resident path."""
+    from css_b200.pipeline import CssPipeline
+    from css_b200.synth import make_recording
+    from tests.helpers import cfg7, golden_conformer
+
+    wav = make_recording(60, channels=7, seed=5)               # 72 chunks -> a 9-chunk first piece, then the rest
+    pipe = CssPipeline(cfg7(), golden_conformer(num_blocks=1).to(cuda), device=cuda)
+    a = pipe(wav.to(cuda), return_intermediates=True)
+    b = pipe(wav.pin_memory(), return_intermediates=True)
+    torch.cuda.synchronize()
+    assert torch.equal(a["masks"], b["masks"]) and torch.equal(a["swap"], b["swap"]) and torch.equal(a["wavs"], b["wavs"])
+
+
+def test_run_many_equals_single_calls(cuda):
+    """Double-buffered session loop: every result equals the one-recording call, also with different lengths."""
+    from css_b200.pipeline import CssPipeline
+    from css_b200.synth import make_recording
+    from tests.helpers import cfg7, golden_conformer
+
+    pipe = CssPipeline(cfg7(), golden_conformer(num_blocks=1).to(cuda), device=cuda)
+    recs = [make_recording(sec, channels=7, seed=40 + i).pin_memory() for i, sec in enumerate((8, 12, 8, 5))]
+    outs = pipe.run_many(recs)
+    for r, o in zip(recs, outs):
+        ref = pipe(r.to(cuda))
+        torch.cuda.synchronize()
+        assert torch.equal(o, ref.cpu())
