@@ -231,7 +231,7 @@ def run_b200(args):
     launches = nv.launch_count()
     clocks = sampler.stop() if rank == 0 else None
     import ctypes
-    ncat = 5
+    ncat = 11
     ms_c, work_c, cnt_c = (ctypes.c_double * ncat)(), (ctypes.c_double * ncat)(), (ctypes.c_long * ncat)()
     nv.check(lib.css_profile_collect(ms_c, work_c, cnt_c, ncat), "css_profile_collect")
     lib.css_profile_enable(0)
@@ -258,12 +258,23 @@ def run_b200(args):
     # dominant kernel: the dense Linear GEMMs of the Conformer (category 0)
     g_ms, g_flop, g_n = ms_c[0], work_c[0], cnt_c[0]
     achieved = g_flop / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
-    names = ("gemm", "attention", "conv_module", "layernorm", "lstm_step")
+    names = ("gemm", "attention", "conv_module", "layernorm", "lstm_step", "stft", "features_mvn", "doa_merge", "stitch", "mvdr",
+             "istft_peak")
     shares = {names[i]: round(ms_c[i] / ms_total, 4) for i in range(ncat) if cnt_c[i]}
+    # HBM-bound kernels (north_star: STFT, mask, MVDR, stitch): algorithmic bytes / CUDA-event time vs measured copy peak
+    hbm = {names[i]: {"achieved_GBps": round(work_c[i] / (ms_c[i] * 1e-3) / 1e9, 1), "frac": round(work_c[i] / (ms_c[i] * 1e-3) / 1e9 / pk["hbm"], 4),
+                      "ms_per_step": round(ms_c[i] / args.steps, 4), "algorithmic_MB_per_step": round(work_c[i] / args.steps / 1e6, 1)}
+           for i in (2, 3, 5, 6, 7, 8, 9, 10) if cnt_c[i] and ms_c[i] > 0}
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    if os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("gemm_tc", {}).get("bytes_per_launch")
     roof = {"kernel": {0: "gemm_simt_f32", 1: "gemm_tc_bf16x3 (tcgen05)", 2: "gemm_tc_bf16 (tcgen05)"}[gemm_mode],
             "bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
             "frac": achieved / pk["tensor"], "peak_source": f"{pk['src']} bf16 sustained (kernel timed inside a long step)",
-            "traffic": None, "launches": int(g_n), "avg_launch_ms": g_ms / max(1, g_n),
+            "traffic": traffic, "traffic_note": "ncu dram bytes per launch, mean over the six GEMMs of one block (profiles/r1_traffic.json)",
+            "launches": int(g_n), "avg_launch_ms": g_ms / max(1, g_n),
             "algorithmic_flop_per_step": g_flop / args.steps, "share_of_step": shares}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -273,7 +284,7 @@ def run_b200(args):
                        "session_seconds": audio_s, "chunks_per_session": B, "blocks": args.blocks, "sessions_per_step": world,
                        "l2": f"inputs larger than L2 (waveform {wav_dev.numel() * 4 / 1e6:.0f} MB, features {B * 150 * 1856 * 4 / 1e6:.0f} MB vs 126 MB L2)",
                        "parallelism": f"dp{world} (independent sessions, no data-path collective)", "gemm_mode": gemm_mode},
-            "clocks": clocks, "roofline": roof,
+            "clocks": clocks, "roofline": roof, "hbm_kernels": {"peak_GBps": pk["hbm"], "kernels": hbm},
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps,
                     "h2d_bytes_per_step": wav_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
             "gpu_launches": int(launches)}

@@ -17,6 +17,14 @@ int css_check_launch(const char* what);
 void css_prof_begin(int cat, double work, cudaStream_t st);
 void css_prof_end(cudaStream_t st);
 
+// categories 5.. are the HBM-bound DSP kernels, work = algorithmic bytes: 5 stft, 6 features + input MVN,
+// 7 DOA merge, 8 stitch (pair decisions + connect), 9 MVDR (covariances, solve, apply, rescale), 10 iSTFT placement + peak
+struct CssProfScope {
+    cudaStream_t st;
+    CssProfScope(int cat, double work, cudaStream_t s) : st(s) { css_prof_begin(cat, work, s); }
+    ~CssProfScope() { css_prof_end(st); }
+};
+
 #define CSS_REQUIRE(cond, ...)            \
     do {                                  \
         if (!(cond)) {                    \

@@ -37,7 +37,7 @@ __device__ __forceinline__ float2 unit_cross(float2 a, float2 b) {
 
 // One block per chunk; thread k owns bin k.  spec element (d, chunk b, frame t, bin k) lives at
 // spec[(d*stride_d + b*stride_chunk + t) * CSS_KP + k].
-__global__ void __launch_bounds__(FEAT_THREADS)
+__global__ void __launch_bounds__(FEAT_THREADS, 3)
 features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T,
                 const int* __restrict__ ipd_l, const int* __restrict__ ipd_r, int n_pairs,
                 float* __restrict__ mag, float* __restrict__ feat, int ldf) {
@@ -47,6 +47,19 @@ features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chun
     const bool act = k < CSS_NBINS;
     const float2* base = spec + (b * stride_chunk) * CSS_KP + k;
 
+    // per-pair channel pointers in registers (the index tables are read once, not once per frame), and the common case of
+    // one shared reference channel ("1,0;2,0;...") loads that channel once per frame
+    const float2* pl[8];
+    const float2* pr[8];
+    bool same_r = true;
+#pragma unroll
+    for (int p = 0; p < 8; ++p) {
+        const int l = p < n_pairs ? ipd_l[p] : 0, r = p < n_pairs ? ipd_r[p] : 0;
+        pl[p] = base + (long)l * stride_d * CSS_KP;
+        pr[p] = base + (long)r * stride_d * CSS_KP;
+        if (p < n_pairs && r != ipd_r[0]) same_r = false;
+    }
+
     // ---- pass 1: statistics over time ----
     float m_sum = 0.f;
     float cs[8], sn[8];
@@ -54,14 +67,18 @@ features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chun
     for (int p = 0; p < 8; ++p) cs[p] = sn[p] = 0.f;
     if (act) {
         for (int t = 0; t < T; ++t) {
-            float2 x0 = base[(long)t * CSS_KP];
+            const long o = (long)t * CSS_KP;
+            const float2 x0 = base[o];
             m_sum += fmaxf(sqrtf(x0.x * x0.x + x0.y * x0.y), FEAT_EPS);
+            float2 xl[8], xr0 = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int p = 0; p < 8; ++p)
+                if (p < n_pairs) xl[p] = pl[p][o];
+            if (same_r && n_pairs > 0) xr0 = pr[0][o];
 #pragma unroll
             for (int p = 0; p < 8; ++p)
                 if (p < n_pairs) {
-                    float2 xl = base[((long)ipd_l[p] * stride_d + t) * CSS_KP];
-                    float2 xr = base[((long)ipd_r[p] * stride_d + t) * CSS_KP];
-                    float2 u = unit_cross(xl, xr);
+                    const float2 u = unit_cross(xl[p], same_r ? xr0 : pr[p][o]);
                     cs[p] += u.x;
                     sn[p] += u.y;
                 }
@@ -87,18 +104,22 @@ features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chun
         if (act)
             for (int tt = 0; tt < tn; ++tt) {
                 const int t = t0 + tt;
-                float2 x0 = base[(long)t * CSS_KP];
+                const long o = (long)t * CSS_KP;
+                const float2 x0 = base[o];
+                float2 xl[8], xr0 = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int p = 0; p < 8; ++p)
+                    if (p < n_pairs) xl[p] = pl[p][o];
+                if (same_r && n_pairs > 0) xr0 = pr[0][o];
                 float m = sqrtf(x0.x * x0.x + x0.y * x0.y);
                 tile[tt][k] = m;
-                float* fr = frow + (long)t * ldf;
-                fr[k] = (fmaxf(m, FEAT_EPS) - m_mean) * inv;
+                float* fr = frow + (long)t * ldf + k;
+                fr[0] = (fmaxf(m, FEAT_EPS) - m_mean) * inv;
 #pragma unroll
                 for (int p = 0; p < 8; ++p)
                     if (p < n_pairs) {
-                        float2 xl = base[((long)ipd_l[p] * stride_d + t) * CSS_KP];
-                        float2 xr = base[((long)ipd_r[p] * stride_d + t) * CSS_KP];
-                        float2 u = unit_cross(xl, xr);
-                        fr[(p + 1) * CSS_NBINS + k] = atan2f(u.y - sn[p], u.x - cs[p]);
+                        const float2 u = unit_cross(xl[p], same_r ? xr0 : pr[p][o]);
+                        fr[(p + 1) * CSS_NBINS] = atan2f(u.y - sn[p], u.x - cs[p]);
                     }
             }
         __syncthreads();
@@ -141,6 +162,7 @@ extern "C" int css_features(const void* spec, long stride_d, long stride_chunk, 
     CSS_REQUIRE(n_chunks > 0 && T > 1, "css_features: empty input (chunks=%ld T=%d)", n_chunks, T);
     CSS_REQUIRE(n_pairs >= 0 && n_pairs <= 8, "css_features: at most 8 IPD pairs supported, got %d", n_pairs);
     CSS_REQUIRE(ldf >= CSS_NBINS * (n_pairs + 1), "css_features: feature pitch %d too small", ldf);
+    CssProfScope prof(6, (double)n_chunks * T * CSS_NBINS * ((n_pairs ? 7 : 1) * 8.0 + (n_pairs + 1) * 4.0 + 4.0), st);
     features_kernel<<<(unsigned)n_chunks, FEAT_THREADS, 0, st>>>((const float2*)spec, stride_d, stride_chunk, T, ipd_l,
                                                                  ipd_r, n_pairs, mag, feat, ldf);
     return css_check_launch("css_features");
@@ -205,6 +227,7 @@ int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* p
         attr_set = true;
     }
     dim3 grid((unsigned)n, (ldp + MVN_F - 1) / MVN_F);
+    CssProfScope prof(6, (double)n * T * (F * 4.0 + (double)ldp * 2.0 * n_planes), st);
     mvn_time_planes_kernel<<<grid, 256, smem, st>>>(x, T, F, ld, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, n_planes);
     return css_check_launch("mvn_time_planes");
 }

@@ -64,6 +64,7 @@ extern "C" int css_istft_place(const void* Y, int T, const int* plan, int n_item
     CSS_REQUIRE(T >= 2 && out_len > 0, "css_istft_place: bad shape");
     if (n_items == 0) return 0;
     dim3 grid((unsigned)n_items, 2);
+    CssProfScope prof(10, (double)n_items * 8.0 * (CSS_NBINS * 8.0 + CSS_HOP * 4.0), st);   // <= 8 frames in, 8 x 256 samples out per item
     istft_place_kernel<<<grid, IS_WARPS * 32, 0, st>>>((const float2*)Y, T, (const int4*)plan, out, out_len);
     return css_check_launch("css_istft_place");
 }
@@ -101,6 +102,7 @@ extern "C" int css_peak_normalize(float* x, int rows, long n, float target, unsi
     cudaMemsetAsync(scratch, 0, sizeof(unsigned) * rows, st);
     dim3 grid((unsigned)((n + 256 * 8 - 1) / (256 * 8)), rows);
     if (grid.x > 148 * 8) grid.x = 148 * 8;
+    CssProfScope prof(10, (double)rows * n * 12.0, st);
     absmax_kernel<<<grid, 256, 0, st>>>(x, n, scratch);
     int rc = css_check_launch("absmax");
     if (rc) return rc;

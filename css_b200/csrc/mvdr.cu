@@ -212,6 +212,7 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
     float* scm = static_cast<float*>(scratch);
     float2* wv = reinterpret_cast<float2*>(static_cast<char*>(scratch) + scm_bytes);
     const unsigned nblk = (CSS_NBINS + MV_BINS - 1) / MV_BINS;
+    CssProfScope prof(9, (double)n_chunks * T * CSS_NBINS * (7 * 8.0 + 3 * 4.0 + 2 * 8.0), st);
     mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 3), 0, st>>>(
         (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
     int rc = css_check_launch("css_mvdr(scm)");
@@ -287,6 +288,7 @@ extern "C" int css_mvdr_finalize(void* Y, const float* energy, long n_chunks, in
                                  float* scal, cudaStream_t st) {
     CSS_REQUIRE(n_chunks > 0 && n_chunks <= 65535, "css_mvdr_finalize: chunk count out of range");
     const int nblk = (CSS_NBINS + MV_BINS - 1) / MV_BINS;
+    CssProfScope prof(9, 0.0, st);   // second pass over Y: time counted with the MVDR, bytes already counted there
     chunk_scalars_kernel<<<(unsigned)((n_chunks + 127) / 128), 128, 0, st>>>(energy, n_chunks, nblk, T, rescale, scal);
     int rc = css_check_launch("chunk_scalars");
     if (rc) return rc;

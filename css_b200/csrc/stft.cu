@@ -73,6 +73,7 @@ extern "C" int css_stft(const float* x, long n_sig, long sig_stride, long n_fram
     long warps = n_sig * n_frames;
     int grid = (int)((warps + STFT_WARPS - 1) / STFT_WARPS);
     if (grid > 148 * 8) grid = 148 * 8;
+    CssProfScope prof(5, (double)warps * (CSS_HOP * 4 + CSS_NBINS * 8), st);
     stft_kernel<<<grid, STFT_WARPS * 32, 0, st>>>(x, n_sig, sig_stride, n_frames, (float2*)spec, n_frames);
     return css_check_launch("css_stft");
 }
@@ -85,6 +86,7 @@ extern "C" int css_stft_range(const float* x, long n_sig, long sig_stride, long 
     long warps = n_sig * n_frames;
     int grid = (int)((warps + STFT_WARPS - 1) / STFT_WARPS);
     if (grid > 148 * 8) grid = 148 * 8;
+    CssProfScope prof(5, (double)warps * (CSS_HOP * 4 + CSS_NBINS * 8), st);
     stft_kernel<<<grid, STFT_WARPS * 32, 0, st>>>(x, n_sig, sig_stride, n_frames, (float2*)spec, spec_stride);
     return css_check_launch("css_stft_range");
 }

@@ -129,6 +129,7 @@ extern "C" int css_doa_merge(const void* spec, long stride_d, long stride_chunk,
         cudaFuncSetAttribute(doa_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
+    CssProfScope prof(7, (double)n_chunks * T * (CSS_NBINS * C * 4.0 + 7.0 * (hi - lo) * 8.0), st);
     doa_merge_kernel<<<(unsigned)n_chunks, 256, smem, st>>>((const float2*)spec, stride_d, stride_chunk, T,
                                                             (const float2*)svT, angles, lo, nf, thresh, 0.5f, masks, C,
                                                             like, idx);
@@ -175,6 +176,7 @@ extern "C" int css_stitch_perm(const float* mags, const float* masks, long n_chu
     CSS_REQUIRE(n_chunks >= 1 && T > 0 && C >= 2, "css_stitch_perm: bad shape");
     CSS_REQUIRE(margin > 0 && margin <= T, "css_stitch_perm: margin %d out of range", margin);
     if (n_chunks == 1) return 0;   // no pairs: empty permutation list
+    CssProfScope prof(8, (double)(n_chunks - 1) * 2.0 * 3.0 * CSS_NBINS * margin * 4.0, st);
     stitch_perm_kernel<<<(unsigned)(n_chunks - 1), 256, 0, st>>>(mags, masks, T, C, margin, swap, sims);
     return css_check_launch("css_stitch_perm");
 }
@@ -264,6 +266,7 @@ extern "C" int css_stitch_connect(const float* masks, const int* state, long n_c
     CSS_REQUIRE(n_chunks >= 1 && T > 0 && C == 3 && hop > 0, "css_stitch_connect: bad shape (C must be 3)");
     const long L = (long)hop * (n_chunks - 1) + T;
     dim3 grid((unsigned)((L + 31) / 32), (CSS_KP + 31) / 32);
+    CssProfScope prof(8, (double)n_chunks * CSS_NBINS * 3.0 * 4.0 * (T + hop), st);
     stitch_connect_kernel<<<grid, 256, 0, st>>>(masks, state, n_chunks, T, C, hop, L, out);
     return css_check_launch("css_stitch_connect");
 }
