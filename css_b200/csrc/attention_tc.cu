@@ -26,8 +26,9 @@ constexpr int ROWB = 144;                   // bytes per smem row: 64 bf16 + 16 
 constexpr int PE_ROWS = 2 * TMAX;           // >= 2T-1
 constexpr int PLANE_KV = TMAX * ROWB;       // one bf16 plane of K or V
 constexpr int PLANE_PE = PE_ROWS * ROWB;
-constexpr int RING_BYTES = 4 * 16 * 8 * 4;  // 4 slots of a 16 x 8 fp32 tile per warp
-constexpr int SMEM_BYTES = 2 * PLANE_PE + 4 * PLANE_KV + NWARP * RING_BYTES;
+constexpr int SLOT_BYTES = 16 * 8 * 4;      // one 16 x 8 fp32 tile of the relative term
+constexpr int RING_BYTES = 8 * SLOT_BYTES;  // 8 slots per warp, 4096-aligned so the read pointers wrap with one AND
+constexpr int SMEM_BYTES = 2 * PLANE_PE + 4 * PLANE_KV + NWARP * RING_BYTES + 4096;
 
 __device__ __forceinline__ void mma16816(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
     asm(
@@ -53,7 +54,22 @@ __device__ __forceinline__ void split2(float x, float y, uint32_t& hi, uint32_t&
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_f32x2(uint32_t addr, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(addr), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ float ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 struct AttnArgs {
     const __nv_bfloat16* qkv;   // [planes][M][3*H*64]
@@ -69,9 +85,10 @@ struct AttnArgs {
     int T, H;
 };
 
-// one 16 x 8 tile, 64-deep contraction: acc[0] += Al*Bh, acc[1] += Ah*Bl (SPLIT only), acc[2] += Ah*Bh
+// one 16 x 8 tile, 64-deep contraction: lo[] += Al*Bh + Ah*Bl (SPLIT only), hi[] += Ah*Bh.  The two correction
+// terms are ~2^-8 of the main one, so they share an accumulator; the caller adds lo into hi once per tile.
 template <bool SPLIT>
-__device__ __forceinline__ void tile_k64(float (*acc)[4], const uint32_t (*ah)[4], const uint32_t (*al)[4], uint32_t hi_s,
+__device__ __forceinline__ void tile_k64(float* lo, float* hi, const uint32_t (*ah)[4], const uint32_t (*al)[4], uint32_t hi_s,
                                          uint32_t lo_s, uint32_t off) {
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
@@ -82,15 +99,17 @@ __device__ __forceinline__ void tile_k64(float (*acc)[4], const uint32_t (*ah)[4
         for (int kk = 0; kk < 2; ++kk) {
             const int ks = 2 * half + kk;
             if (SPLIT) {
-                mma16816(acc[0], al[ks], bh[2 * kk], bh[2 * kk + 1]);
-                mma16816(acc[1], ah[ks], bl[2 * kk], bl[2 * kk + 1]);
+                mma16816(lo, al[ks], bh[2 * kk], bh[2 * kk + 1]);
+                mma16816(lo, ah[ks], bl[2 * kk], bl[2 * kk + 1]);
             }
-            mma16816(acc[2], ah[ks], bh[2 * kk], bh[2 * kk + 1]);
+            mma16816(hi, ah[ks], bh[2 * kk], bh[2 * kk + 1]);
         }
     }
 }
 
-template <bool SPLIT>
+// NT: score tiles of 8 keys computed per query tile (T <= 8 NT).  The tile loops have compile-time trip counts and no
+// run-time branches, so ldmatrix / mma of neighbouring tiles overlap; keys in [T, 8 NT) read zeroed rows and are masked.
+template <bool SPLIT, bool PE, int NT>
 __global__ void __launch_bounds__(NWARP * 32, 1)
 attention_tc_kernel(const AttnArgs a) {
     extern __shared__ __align__(16) uint8_t sm[];
@@ -100,17 +119,33 @@ attention_tc_kernel(const AttnArgs a) {
     const uint32_t pe_hi_s = sm_s, pe_lo_s = pe_hi_s + PLANE_PE;
     const uint32_t k_hi_s = pe_lo_s + PLANE_PE, k_lo_s = k_hi_s + PLANE_KV;
     const uint32_t v_hi_s = k_lo_s + PLANE_KV, v_lo_s = v_hi_s + PLANE_KV;
-    float* ring = reinterpret_cast<float*>(sm + 2 * PLANE_PE + 4 * PLANE_KV) + warp * (RING_BYTES / 4);
+    const uint32_t ring_s = ((v_lo_s + PLANE_KV + 4095u) & ~4095u) + warp * RING_BYTES;
     const int g = lane >> 2, q = lane & 3;
     const int ld = 3 * H * DK;
-    const int maxlen = a.pe_rows / 2;
-    const bool use_pe = a.pe != nullptr;
-    const int TK = (T + 15) & ~15;                 // keys padded to the PV k-step
-    const int n_stiles = (T + 7) >> 3;             // score n-tiles (8 keys each)
     constexpr int NPL = SPLIT ? 2 : 1;
+    constexpr int NKT = (NT + 1) / 2;              // PV k-steps of 16 keys
 
-    // ---- one-off: relative-position rows (smem row rho <-> r = rho - (T-1)), zero rows of the K/V padding ----
-    if (use_pe) {
+    // K (kv = 0) or V (kv = 1) planes of one (sequence, head) item -> shared memory; 40 rows per pass of the CTA
+    auto load_kv = [&](long item, int kv) {
+        const long n = item / H;
+        const int h = (int)(item - n * H);
+        const int j0 = threadIdx.x >> 3, c8 = threadIdx.x & 7;
+#pragma unroll
+        for (int p = 0; p < NPL; ++p) {
+            const __nv_bfloat16* src = a.qkv + p * a.qkv_plane_stride + (n * T + j0) * (long)ld + ((kv ? 2 : 1) * H + h) * DK + c8 * 8;
+            uint32_t dst = (kv ? (p ? v_lo_s : v_hi_s) : (p ? k_lo_s : k_hi_s)) + j0 * ROWB + c8 * 16;
+            for (int j = j0; j < T; j += NWARP * 4) {
+                cp_async16(dst, src);
+                src += (long)(NWARP * 4) * ld;
+                dst += NWARP * 4 * ROWB;
+            }
+        }
+        cp_async_commit();
+    };
+
+    // ---- one-off: relative-position rows (smem row rho <-> r = rho - (T-1)), zero rows [T, TMAX) of K and V ----
+    if (PE) {
+        const int maxlen = a.pe_rows / 2;
         const int nrel = 2 * T - 1;
         for (int i = threadIdx.x; i < nrel * 8 * NPL; i += blockDim.x) {
             const int p = i / (nrel * 8), rem = i - p * (nrel * 8);
@@ -120,30 +155,36 @@ attention_tc_kernel(const AttnArgs a) {
             cp_async16((p ? pe_lo_s : pe_hi_s) + rho * ROWB + c8 * 16, a.pe + p * a.pe_plane_stride + (long)r * DK + c8 * 8);
         }
     }
-    for (int i = threadIdx.x; i < (TK - T) * 8 * 4; i += blockDim.x) {
-        const int pl = i / ((TK - T) * 8), rem = i - pl * ((TK - T) * 8);
+    for (int i = threadIdx.x; i < (TMAX - T) * 8 * 4; i += blockDim.x) {
+        const int pl = i / ((TMAX - T) * 8), rem = i - pl * ((TMAX - T) * 8);
         *reinterpret_cast<uint4*>(sm + 2 * PLANE_PE + pl * PLANE_KV + (T + (rem >> 3)) * ROWB + (rem & 7) * 16) = make_uint4(0, 0, 0, 0);
     }
+    if (blockIdx.x < a.n_items) {
+        load_kv(blockIdx.x, 0);                    // group: PE rows + K of the first item
+        load_kv(blockIdx.x, 1);
+    }
     const int i0 = warp * 16;
+    const bool active = i0 < T;                    // warp-uniform; idle warps still reach every barrier
     const float kscale = 0.125f * 1.4426950408889634f;        // 1/sqrt(64) * log2(e)
+    // lane constants of the relative term.  R tile v holds columns u = 8v .. 8v+7 with u = j + (15 - l), i.e. relative
+    // position r = i0 + 15 - u; element (l, j) of score tile t sits at u = 8t + (j - 8t) + 15 - l.
+    const int rho0 = i0 + 15 - (lane & 7) + (T - 1);
+    const uint32_t rel_lane = (uint32_t)((lane >> 3) * 16);
+    const uint32_t st_s = ring_s + (uint32_t)(g * 8 + 2 * q) * 4;
+    uint32_t rd0[4];                               // ring read pointers of the lane's 4 elements at tile 0
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        const int c = 2 * q + 15 - g - ((e >> 1) ? 8 : 0) + (e & 1);
+        rd0[e] = ring_s + (uint32_t)((c >> 3) * SLOT_BYTES + ((g + ((e >> 1) ? 8 : 0)) * 8 + (c & 7)) * 4);
+    }
 
     for (long item = blockIdx.x; item < a.n_items; item += gridDim.x) {
         const long n = item / H;
         const int h = (int)(item - n * H);
+        const long next = item + gridDim.x;
         const __nv_bfloat16* base = a.qkv + n * (long)T * ld;
-        __syncthreads();                           // previous item's K/V fully consumed
-        for (int i = threadIdx.x; i < T * 8 * 2 * NPL; i += blockDim.x) {
-            const int sel = i / (T * 8), rem = i - sel * (T * 8);      // sel: K hi, V hi, (K lo, V lo)
-            const int j = rem >> 3, c8 = rem & 7;
-            const int p = sel >> 1, kv = sel & 1;
-            const uint32_t dst = (kv ? (p ? v_lo_s : v_hi_s) : (p ? k_lo_s : k_hi_s)) + j * ROWB + c8 * 16;
-            cp_async16(dst, base + p * a.qkv_plane_stride + (long)j * ld + ((kv ? 2 : 1) * H + h) * DK + c8 * 8);
-        }
-        cp_async_wait_all();
-        __syncthreads();
-        if (i0 >= T) continue;                     // warp-uniform; the barriers above are still reached next round
 
-        // ---- Q fragments (hi/lo) of rows i0+g and i0+g+8: plain 32-bit loads from the planes ----
+        // ---- Q fragments (hi/lo) of rows i0+g and i0+g+8: plain 32-bit loads, in flight while K lands ----
         uint32_t qh[4][4], ql[4][4];
         {
             const int r0 = i0 + g, r1 = i0 + g + 8;
@@ -159,92 +200,98 @@ attention_tc_kernel(const AttnArgs a) {
                 }
             }
         }
-        // R tile v: columns u = 8v .. 8v+7, u = j + (15 - l)  <->  relative position r = i0 + 15 - u
-        auto rel_off = [&](int v) {
-            int rho = (i0 + 15 - (8 * v + (lane & 7))) + (T - 1);
-            rho = max(0, min(2 * T - 2, rho));
-            return (uint32_t)(rho * ROWB + (lane >> 3) * 16);
-        };
-        auto rel_store = [&](int v, float (*r)[4]) {
-            float* slot = ring + (v & 3) * 128;
-            *reinterpret_cast<float2*>(slot + g * 8 + 2 * q) = make_float2(r[0][0] + r[1][0] + r[2][0], r[0][1] + r[1][1] + r[2][1]);
-            *reinterpret_cast<float2*>(slot + (g + 8) * 8 + 2 * q) = make_float2(r[0][2] + r[1][2] + r[2][2], r[0][3] + r[1][3] + r[2][3]);
-        };
-        if (use_pe) {
-#pragma unroll
-            for (int v = 0; v < 2; ++v) {
-                float r[3][4] = {};
-                tile_k64<SPLIT>(r, qh, ql, pe_hi_s, pe_lo_s, rel_off(v));
-                rel_store(v, r);
+        cp_async_wait<1>();                        // K of this item (and the PE rows) landed; V may still be in flight
+        __syncthreads();
+
+        float s[2 * NKT][4];
+        if (active) {
+            auto rel_tile = [&](int v) {           // R tile v -> ring slot v & 7
+                float lo[4] = {}, hi[4] = {};
+                const int rho = max(0, min(2 * T - 2, rho0 - 8 * v));
+                tile_k64<SPLIT>(lo, hi, qh, ql, pe_hi_s, pe_lo_s, (uint32_t)(rho * ROWB) + rel_lane);
+                const uint32_t dst = st_s + (v & 7) * SLOT_BYTES;
+                sts_f32x2(dst, hi[0] + lo[0], hi[1] + lo[1]);
+                sts_f32x2(dst + 8 * 8 * 4, hi[2] + lo[2], hi[3] + lo[3]);
+            };
+            uint32_t rd[4] = {rd0[0], rd0[1], rd0[2], rd0[3]};
+            if (PE) {
+                rel_tile(0);
+                rel_tile(1);
             }
-        }
-        // skewed read-back: element (l, j) of score tile t needs u = 8t + k0 with k0 = 2q + 15 - l (static per lane)
-        const int k0 = 2 * q + 15 - g;             // row g ; row g+8 uses k0 - 8
-        float s[TMAX / 8][4];
+            const uint32_t k_lane = (uint32_t)((lane & 7) * ROWB) + rel_lane;
 #pragma unroll
-        for (int t = 0; t < TMAX / 8; ++t) {
-            if (t < n_stiles) {
-                float sa[3][4] = {}, ra[3][4] = {};
-                tile_k64<SPLIT>(sa, qh, ql, k_hi_s, k_lo_s, (uint32_t)((8 * t + (lane & 7)) * ROWB + (lane >> 3) * 16));
-                if (use_pe) {
-                    tile_k64<SPLIT>(ra, qh, ql, pe_hi_s, pe_lo_s, rel_off(t + 2));
-                    rel_store(t + 2, ra);
+            for (int t2 = 0; t2 < NKT; ++t2) {
+                float lo[2][4] = {}, hi[2][4] = {};
+#pragma unroll
+                for (int b = 0; b < 2; ++b) {
+                    const int t = 2 * t2 + b;
+                    if (t < NT) tile_k64<SPLIT>(lo[b], hi[b], qh, ql, k_hi_s, k_lo_s, k_lane + (uint32_t)(8 * t * ROWB));
+                    if (PE && t + 2 <= NT + 1) rel_tile(t + 2);
                 }
-                __syncwarp();
+                if (PE) __syncwarp();
 #pragma unroll
-                for (int e = 0; e < 4; ++e) s[t][e] = sa[0][e] + sa[1][e] + sa[2][e];
-                if (use_pe) {
+                for (int b = 0; b < 2; ++b) {
+                    const int t = 2 * t2 + b;
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
-                        const int u = 8 * t + ((e >> 1) ? k0 - 8 : k0) + (e & 1);
-                        s[t][e] += ring[((u >> 3) & 3) * 128 + (g + ((e >> 1) ? 8 : 0)) * 8 + (u & 7)];
+                        s[t][e] = hi[b][e] + lo[b][e];
+                        if (PE && t < NT) s[t][e] += lds_f32(rd[e]);
+                        if (PE) rd[e] = ((rd[e] + SLOT_BYTES) & (RING_BYTES - 1)) | ring_s;
                     }
                 }
             }
         }
-        // ---- softmax over keys (rows g and g+8 live in the 4 lanes of a quad); exp2 with pre-scaled logits ----
-        float mx0 = -INFINITY, mx1 = -INFINITY;
+        __syncthreads();                           // every warp is done with K
+        if (next < a.n_items) load_kv(next, 0);    // next item's K lands during softmax and PV
+        else cp_async_commit();
+
+        // ---- softmax over keys (rows g and g+8 live in the 4 lanes of a quad): exp2 of (s - max) * scale ----
+        float inv0 = 0.f, inv1 = 0.f;
+        if (active) {
+            float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
-        for (int t = 0; t < TMAX / 8; ++t) {
-            if (t < n_stiles) {
-                const int j = 8 * t + 2 * q;
+            for (int t = 0; t < NT; ++t) {
+                if (8 * t + 8 > T) {               // uniform: only the last tile(s) hold keys >= T
+                    const int j = 8 * t + 2 * q;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) s[t][e] = (j + (e & 1) < T) ? s[t][e] * kscale : -INFINITY;
+                    for (int e = 0; e < 4; ++e) s[t][e] = (j + (e & 1) < T) ? s[t][e] : -INFINITY;
+                }
                 mx0 = fmaxf(mx0, fmaxf(s[t][0], s[t][1]));
                 mx1 = fmaxf(mx1, fmaxf(s[t][2], s[t][3]));
             }
-        }
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        float sum0 = 0.f, sum1 = 0.f;
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            const float m0 = mx0 * kscale, m1 = mx1 * kscale;
+            float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
-        for (int t = 0; t < TMAX / 8; ++t) {
-            if (t < n_stiles) {
-                s[t][0] = exp2f(s[t][0] - mx0); s[t][1] = exp2f(s[t][1] - mx0);
-                s[t][2] = exp2f(s[t][2] - mx1); s[t][3] = exp2f(s[t][3] - mx1);
+            for (int t = 0; t < NT; ++t) {
+                s[t][0] = ex2(fmaf(s[t][0], kscale, -m0)); s[t][1] = ex2(fmaf(s[t][1], kscale, -m0));
+                s[t][2] = ex2(fmaf(s[t][2], kscale, -m1)); s[t][3] = ex2(fmaf(s[t][3], kscale, -m1));
                 sum0 += s[t][0] + s[t][1];
                 sum1 += s[t][2] + s[t][3];
-            } else {
-                s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f;
             }
+            sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+            sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+            inv0 = 1.f / sum0;
+            inv1 = 1.f / sum1;
         }
-        sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
-        sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-        const float inv0 = 1.f / sum0, inv1 = 1.f / sum1;
+        cp_async_wait<1>();                        // V of this item landed (the newest group is the next item's K)
+        __syncthreads();
 
-        // ---- O = P V : probabilities become A fragments straight from the score registers ----
+        // ---- O = P V : the exponentials become A fragments straight from the score registers; 1/sum is applied to O ----
         float o[8][4];
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
+        if (active) {
+            const uint32_t v_lane = (uint32_t)(((lane & 7) + 8 * ((lane >> 3) & 1)) * ROWB + (lane >> 4) * 16);
 #pragma unroll
-        for (int kt = 0; kt < TMAX / 16; ++kt) {
-            if (16 * kt < T) {
+            for (int kt = 0; kt < NKT; ++kt) {
                 uint32_t ph[4], pl[4];
-                split2(s[2 * kt][0] * inv0, s[2 * kt][1] * inv0, ph[0], pl[0]);
-                split2(s[2 * kt][2] * inv1, s[2 * kt][3] * inv1, ph[1], pl[1]);
-                split2(s[2 * kt + 1][0] * inv0, s[2 * kt + 1][1] * inv0, ph[2], pl[2]);
-                split2(s[2 * kt + 1][2] * inv1, s[2 * kt + 1][3] * inv1, ph[3], pl[3]);
-                const uint32_t off = (16 * kt + (lane & 7) + 8 * ((lane >> 3) & 1)) * ROWB + (lane >> 4) * 16;
+                split2(s[2 * kt][0], s[2 * kt][1], ph[0], pl[0]);
+                split2(s[2 * kt][2], s[2 * kt][3], ph[1], pl[1]);
+                split2(s[2 * kt + 1][0], s[2 * kt + 1][1], ph[2], pl[2]);
+                split2(s[2 * kt + 1][2], s[2 * kt + 1][3], ph[3], pl[3]);
+                const uint32_t off = v_lane + (uint32_t)(16 * kt * ROWB);
                 uint32_t vh[4][4], vl[4][4];               // [pair of 8-wide output tiles][b0,b1 | b0,b1]
 #pragma unroll
                 for (int np = 0; np < 4; ++np) {
@@ -262,28 +309,41 @@ attention_tc_kernel(const AttnArgs a) {
                 for (int nt = 0; nt < 8; ++nt) mma16816(o[nt], ph, vh[nt >> 1][2 * (nt & 1)], vh[nt >> 1][2 * (nt & 1) + 1]);
             }
         }
+        __syncthreads();                           // every warp is done with V
+        if (next < a.n_items) load_kv(next, 1);    // next item's V lands during its score phase
+        else cp_async_commit();
+
         // ---- store rows i0+g, i0+g+8: fp32 and/or bf16 split planes (the out-projection GEMM's A operand) ----
         const int dm = H * DK;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
             const int r = i0 + g + 8 * half;
             if (r >= T) continue;
-            const long row = n * T + r;
+            const long eoff = (n * T + r) * dm + h * DK + 2 * q;
+            const float inv = half ? inv1 : inv0;
 #pragma unroll
             for (int nt = 0; nt < 8; ++nt) {
-                const int col = h * DK + 8 * nt + 2 * q;
-                float x = o[nt][2 * half], y = o[nt][2 * half + 1];
-                if (a.out) *reinterpret_cast<float2*>(a.out + row * dm + col) = make_float2(x, y);
-                for (int p = 0; p < a.n_planes; ++p) {
-                    const __nv_bfloat162 hb = __floats2bfloat162_rn(x, y);
-                    x -= __bfloat162float(hb.x);
-                    y -= __bfloat162float(hb.y);
-                    *reinterpret_cast<__nv_bfloat162*>(a.planes + p * a.plane_stride + row * dm + col) = hb;
+                o[nt][2 * half] *= inv;
+                o[nt][2 * half + 1] *= inv;
+            }
+            if (a.out) {
+                float* dst = a.out + eoff;
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) *reinterpret_cast<float2*>(dst + 8 * nt) = make_float2(o[nt][2 * half], o[nt][2 * half + 1]);
+            }
+            for (int p = 0; p < a.n_planes; ++p) {         // plane p takes the bf16 rounding of what planes < p left over
+                __nv_bfloat16* dst = a.planes + p * a.plane_stride + eoff;
+#pragma unroll
+                for (int nt = 0; nt < 8; ++nt) {
+                    const __nv_bfloat162 hb = __floats2bfloat162_rn(o[nt][2 * half], o[nt][2 * half + 1]);
+                    o[nt][2 * half] -= __bfloat162float(hb.x);
+                    o[nt][2 * half + 1] -= __bfloat162float(hb.y);
+                    *reinterpret_cast<__nv_bfloat162*>(dst + 8 * nt) = hb;
                 }
             }
         }
     }
-    cp_async_wait_all();
+    cp_async_wait<0>();
 }
 
 }  // namespace
@@ -297,11 +357,19 @@ int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_pl
     CSS_REQUIRE(attention_tc_supported(T, dk), "attention_tc: T=%d / dk=%d unsupported", T, dk);
     CSS_REQUIRE(in_planes == 1 || in_planes == 2, "attention_tc: %d input planes unsupported", in_planes);
     CSS_REQUIRE(N > 0 && H > 0 && qkv_planes && (out || (planes && n_planes > 0)), "attention_tc: bad arguments");
+    typedef void (*Kern)(const AttnArgs);
+    // score tiles per query tile: 19 covers the executor's 150-frame chunks (and anything up to 152), 20 the rest
+    const bool split = in_planes == 2, use_pe = pe_planes != nullptr, nt19 = T <= 152;
+    static const Kern kerns[8] = {attention_tc_kernel<false, false, 20>, attention_tc_kernel<false, false, 19>,
+                                  attention_tc_kernel<false, true, 20>,  attention_tc_kernel<false, true, 19>,
+                                  attention_tc_kernel<true, false, 20>,  attention_tc_kernel<true, false, 19>,
+                                  attention_tc_kernel<true, true, 20>,   attention_tc_kernel<true, true, 19>};
     static bool attr = false;
     if (!attr) {
-        cudaError_t e = cudaFuncSetAttribute(attention_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        if (e == cudaSuccess) e = cudaFuncSetAttribute(attention_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        CSS_REQUIRE(e == cudaSuccess, "attention_tc: cannot reserve %d B of shared memory: %s", SMEM_BYTES, cudaGetErrorString(e));
+        for (int i = 0; i < 8; ++i) {
+            cudaError_t e = cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+            CSS_REQUIRE(e == cudaSuccess, "attention_tc: cannot reserve %d B of shared memory: %s", SMEM_BYTES, cudaGetErrorString(e));
+        }
         attr = true;
     }
     int dev = 0, sms = 148;
@@ -312,8 +380,7 @@ int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_pl
     AttnArgs a = {static_cast<const __nv_bfloat16*>(qkv_planes), qkv_plane_stride, static_cast<const __nv_bfloat16*>(pe_planes),
                   pe_plane_stride, pe_rows, out, static_cast<__nv_bfloat16*>(planes), plane_stride, planes ? n_planes : 0, items, T, H};
     css_prof_begin(1, 6.0 * (double)N * H * T * T * DK, st);   // QK^T + Q.PE^T + PV (algorithmic)
-    if (in_planes == 2) attention_tc_kernel<true><<<grid, NWARP * 32, SMEM_BYTES, st>>>(a);
-    else attention_tc_kernel<false><<<grid, NWARP * 32, SMEM_BYTES, st>>>(a);
+    kerns[4 * split + 2 * use_pe + nt19]<<<grid, NWARP * 32, SMEM_BYTES, st>>>(a);
     css_prof_end(st);
     return css_check_launch("attention_tc");
 }
