@@ -178,28 +178,33 @@ attention_tc_kernel(const AttnArgs a) {
         rd0[e] = ring_s + (uint32_t)((c >> 3) * SLOT_BYTES + ((g + ((e >> 1) ? 8 : 0)) * 8 + (c & 7)) * 4);
     }
 
+    // Q fragments (hi/lo) of rows i0+g and i0+g+8 of one item: plain 32-bit loads from the planes.  The next item's are
+    // requested right after PV, so they land under the output stores.
+    uint32_t qh[4][4], ql[4][4];
+    auto load_q = [&](long item) {
+        const long n = item / H;
+        const int h = (int)(item - n * H);
+        const __nv_bfloat16* base = a.qkv + n * (long)T * ld;
+        const int r0 = i0 + g, r1 = i0 + g + 8;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+            const int c = h * DK + 16 * ks + 2 * q;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int r = (e & 1) ? r1 : r0;
+                const long off = (long)r * ld + c + ((e >> 1) ? 8 : 0);
+                qh[ks][e] = (r < T) ? *reinterpret_cast<const uint32_t*>(base + off) : 0u;
+                ql[ks][e] = (SPLIT && r < T) ? *reinterpret_cast<const uint32_t*>(base + a.qkv_plane_stride + off) : 0u;
+            }
+        }
+    };
+    if (blockIdx.x < a.n_items) load_q(blockIdx.x);
+
     for (long item = blockIdx.x; item < a.n_items; item += gridDim.x) {
         const long n = item / H;
         const int h = (int)(item - n * H);
         const long next = item + gridDim.x;
-        const __nv_bfloat16* base = a.qkv + n * (long)T * ld;
 
-        // ---- Q fragments (hi/lo) of rows i0+g and i0+g+8: plain 32-bit loads, in flight while K lands ----
-        uint32_t qh[4][4], ql[4][4];
-        {
-            const int r0 = i0 + g, r1 = i0 + g + 8;
-#pragma unroll
-            for (int ks = 0; ks < 4; ++ks) {
-                const int c = h * DK + 16 * ks + 2 * q;
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const int r = (e & 1) ? r1 : r0;
-                    const long off = (long)r * ld + c + ((e >> 1) ? 8 : 0);
-                    qh[ks][e] = (r < T) ? *reinterpret_cast<const uint32_t*>(base + off) : 0u;
-                    ql[ks][e] = (SPLIT && r < T) ? *reinterpret_cast<const uint32_t*>(base + a.qkv_plane_stride + off) : 0u;
-                }
-            }
-        }
         cp_async_wait<1>();                        // K of this item (and the PE rows) landed; V may still be in flight
         __syncthreads();
 
@@ -245,8 +250,8 @@ attention_tc_kernel(const AttnArgs a) {
         if (next < a.n_items) load_kv(next, 0);    // next item's K lands during softmax and PV
         else cp_async_commit();
 
-        // ---- softmax over keys (rows g and g+8 live in the 4 lanes of a quad): exp2 of (s - max) * scale ----
-        float inv0 = 0.f, inv1 = 0.f;
+        // ---- row maxima (rows g and g+8 live in the 4 lanes of a quad); the exponentials are taken inside the PV loop ----
+        float inv0 = 0.f, inv1 = 0.f, m0 = 0.f, m1 = 0.f;
         if (active) {
             float mx0 = -INFINITY, mx1 = -INFINITY;
 #pragma unroll
@@ -261,31 +266,31 @@ attention_tc_kernel(const AttnArgs a) {
             }
             mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
             mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-            const float m0 = mx0 * kscale, m1 = mx1 * kscale;
-            float sum0 = 0.f, sum1 = 0.f;
-#pragma unroll
-            for (int t = 0; t < NT; ++t) {
-                s[t][0] = ex2(fmaf(s[t][0], kscale, -m0)); s[t][1] = ex2(fmaf(s[t][1], kscale, -m0));
-                s[t][2] = ex2(fmaf(s[t][2], kscale, -m1)); s[t][3] = ex2(fmaf(s[t][3], kscale, -m1));
-                sum0 += s[t][0] + s[t][1];
-                sum1 += s[t][2] + s[t][3];
-            }
-            sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
-            sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
-            inv0 = 1.f / sum0;
-            inv1 = 1.f / sum1;
+            m0 = mx0 * kscale;
+            m1 = mx1 * kscale;
         }
         cp_async_wait<1>();                        // V of this item landed (the newest group is the next item's K)
         __syncthreads();
 
-        // ---- O = P V : the exponentials become A fragments straight from the score registers; 1/sum is applied to O ----
+        // ---- O = P V : exp2((s - max) * scale) becomes the A fragments straight from the score registers, tile by tile under
+        //      the mma of the previous step; 1/sum is applied to O ----
         float o[8][4];
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) o[nt][0] = o[nt][1] = o[nt][2] = o[nt][3] = 0.f;
         if (active) {
             const uint32_t v_lane = (uint32_t)(((lane & 7) + 8 * ((lane >> 3) & 1)) * ROWB + (lane >> 4) * 16);
+            float sum0 = 0.f, sum1 = 0.f;
 #pragma unroll
             for (int kt = 0; kt < NKT; ++kt) {
+#pragma unroll
+                for (int t = 2 * kt; t < 2 * kt + 2; ++t) {
+                    if (t < NT) {
+                        s[t][0] = ex2(fmaf(s[t][0], kscale, -m0)); s[t][1] = ex2(fmaf(s[t][1], kscale, -m0));
+                        s[t][2] = ex2(fmaf(s[t][2], kscale, -m1)); s[t][3] = ex2(fmaf(s[t][3], kscale, -m1));
+                        sum0 += s[t][0] + s[t][1];
+                        sum1 += s[t][2] + s[t][3];
+                    }
+                }
                 uint32_t ph[4], pl[4];
                 split2(s[2 * kt][0], s[2 * kt][1], ph[0], pl[0]);
                 split2(s[2 * kt][2], s[2 * kt][3], ph[1], pl[1]);
@@ -308,10 +313,18 @@ attention_tc_kernel(const AttnArgs a) {
 #pragma unroll
                 for (int nt = 0; nt < 8; ++nt) mma16816(o[nt], ph, vh[nt >> 1][2 * (nt & 1)], vh[nt >> 1][2 * (nt & 1) + 1]);
             }
+            sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1); sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+            sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1); sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+            inv0 = 1.f / sum0;
+            inv1 = 1.f / sum1;
         }
         __syncthreads();                           // every warp is done with V
-        if (next < a.n_items) load_kv(next, 1);    // next item's V lands during its score phase
-        else cp_async_commit();
+        if (next < a.n_items) {
+            load_kv(next, 1);                      // next item's V lands during its score phase
+            load_q(next);
+        } else {
+            cp_async_commit();
+        }
 
         // ---- store rows i0+g, i0+g+8: fp32 and/or bf16 split planes (the out-projection GEMM's A operand) ----
         const int dm = H * DK;
