@@ -21,48 +21,113 @@ __device__ __forceinline__ float2 load_x(const float2* __restrict__ spec, const 
                     : spec[((long)d * frames + b * hop_frames + t - 1) * CSS_KP + k];
 }
 
-// ---- kernel 1: masked covariances.  grid (9 bin tiles, B); block (32 bins, 3 masks); 56 accumulators per thread.
+// ---- kernel 1: masked covariances.  grid (9 bin tiles, B); block (32 bins, 4 pair groups).
+// The outer product x_i conj(x_j) does not depend on the mask, so one thread forms it once and feeds the three masks'
+// accumulators (42 per thread); the 28 pairs (i, j >= i) are dealt to the four warps by rows {0}, {1,6}, {2,5}, {3,4}
+// -- 7 pairs each.  The next frame's 7 channels and 3 mask values are requested before the current frame is consumed.
 // scm[b][mask][e][KP] fp32 (normalised by the mask sum, compute_scm(normalize=True)); energy slot 1 = sum |mask x0|^2.
-__global__ void __launch_bounds__(96)
-mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
-                const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
-                float* __restrict__ energy) {
+template <int G>
+__device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
+                                          long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
+                                          float* __restrict__ scm, float* __restrict__ energy) {
+    constexpr int R0 = G, R1 = (G == 0) ? -1 : MV_M - G;
     const long b = blockIdx.y;
-    const int lane = threadIdx.x, mk = threadIdx.y;
+    const int lane = threadIdx.x;
     const int k = blockIdx.x * MV_BINS + lane;
-    const bool act = k < CSS_NBINS;
-    float acc[MV_E];
+    float acc[3][14];
 #pragma unroll
-    for (int i = 0; i < MV_E; ++i) acc[i] = 0.f;
-    float msum = 0.f, e_mask = 0.f;
-    if (act) {
-        const float* mrow = stitched + ((long)mk * L + b * hop_frames) * CSS_KP + k;
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+        for (int i = 0; i < 14; ++i) acc[m][i] = 0.f;
+    float msum[3] = {0.f, 0.f, 0.f}, e_mask[2] = {0.f, 0.f};
+    if (k < CSS_NBINS) {
+        const float* mrow = stitched + (b * hop_frames) * (long)CSS_KP + k;
+        const float2* sp = spec + (b * hop_frames - 1) * (long)CSS_KP + k;      // frame t >= 1 of the chunk at sp + t * KP
+        const long mstride = L * CSS_KP, cstride = frames * CSS_KP;
+        float2 xn[MV_M];
+        float wn[3];
+#pragma unroll
+        for (int d = 0; d < MV_M; ++d) xn[d] = edge[((long)d * n_chunks + b) * CSS_KP + k];
+#pragma unroll
+        for (int m = 0; m < 3; ++m) wn[m] = mrow[m * mstride];
+#pragma unroll 2
         for (int t = 0; t < T; ++t) {
-            const float w = mrow[(long)t * CSS_KP];
             float2 x[MV_M];
+            float w[3];
 #pragma unroll
-            for (int d = 0; d < MV_M; ++d) x[d] = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k);
-            msum += w;
-            const float ar = w * x[0].x, ai = w * x[0].y;
-            e_mask += ar * ar + ai * ai;
+            for (int d = 0; d < MV_M; ++d) x[d] = xn[d];
+#pragma unroll
+            for (int m = 0; m < 3; ++m) w[m] = wn[m];
+            if (t + 1 < T) {
+#pragma unroll
+                for (int d = 0; d < MV_M; ++d) xn[d] = sp[d * cstride + (long)(t + 1) * CSS_KP];
+#pragma unroll
+                for (int m = 0; m < 3; ++m) wn[m] = mrow[m * mstride + (long)(t + 1) * CSS_KP];
+            }
+#pragma unroll
+            for (int m = 0; m < 3; ++m) msum[m] += w[m];
+            if (G == 0) {
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    const float ar = w[m] * x[0].x, ai = w[m] * x[0].y;
+                    e_mask[m] += ar * ar + ai * ai;
+                }
+            }
             int q = 0;
 #pragma unroll
-            for (int i = 0; i < MV_M; ++i) {
-                const float wr = w * x[i].x, wi = w * x[i].y;
+            for (int rr = 0; rr < 2; ++rr) {
+                const int i = rr == 0 ? R0 : R1;
+                if (i < 0) continue;
 #pragma unroll
                 for (int j = i; j < MV_M; ++j) {
-                    acc[q++] += wr * x[j].x + wi * x[j].y;      // (w x_i) * conj(x_j)
-                    acc[q++] += wi * x[j].x - wr * x[j].y;
+                    const float pr = x[i].x * x[j].x + x[i].y * x[j].y;      // x_i * conj(x_j)
+                    const float pi = x[i].y * x[j].x - x[i].x * x[j].y;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) {
+                        acc[m][q] += w[m] * pr;
+                        acc[m][q + 1] += w[m] * pi;
+                    }
+                    q += 2;
                 }
             }
         }
-        float* dst = scm + ((b * 3 + mk) * (long)MV_E) * CSS_KP + k;
 #pragma unroll
-        for (int i = 0; i < MV_E; ++i) dst[(long)i * CSS_KP] = acc[i] / msum;
+        for (int m = 0; m < 3; ++m) {
+            float* dst = scm + ((b * 3 + m) * (long)MV_E) * CSS_KP + k;
+            const float inv = 1.f / msum[m];
+            int q = 0;
+#pragma unroll
+            for (int rr = 0; rr < 2; ++rr) {
+                const int i = rr == 0 ? R0 : R1;
+                if (i < 0) continue;
+                const int e0 = 2 * (i * MV_M - (i * (i - 1)) / 2);        // packed slot of pair (i, i)
+#pragma unroll
+                for (int j = i; j < MV_M; ++j) {
+                    dst[(long)(e0 + 2 * (j - i)) * CSS_KP] = acc[m][q] * inv;
+                    dst[(long)(e0 + 2 * (j - i) + 1) * CSS_KP] = acc[m][q + 1] * inv;
+                    q += 2;
+                }
+            }
+        }
     }
-    if (mk < 2) {   // warp-uniform
-        e_mask = warp_sum(e_mask);
-        if (lane == 0) energy[((b * 2 + mk) * gridDim.x + blockIdx.x) * 2 + 1] = e_mask;
+    if (G == 0) {
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+            const float e = warp_sum(e_mask[m]);
+            if (lane == 0) energy[((b * 2 + m) * gridDim.x + blockIdx.x) * 2 + 1] = e;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128)
+mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
+                const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
+                float* __restrict__ energy) {
+    switch (threadIdx.y) {      // warp-uniform
+        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
+        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
+        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
+        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
     }
 }
 
@@ -213,7 +278,7 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
     float2* wv = reinterpret_cast<float2*>(static_cast<char*>(scratch) + scm_bytes);
     const unsigned nblk = (CSS_NBINS + MV_BINS - 1) / MV_BINS;
     CssProfScope prof(9, (double)n_chunks * T * CSS_NBINS * (7 * 8.0 + 3 * 4.0 + 2 * 8.0), st);
-    mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 3), 0, st>>>(
+    mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 4), 0, st>>>(
         (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
     int rc = css_check_launch("css_mvdr(scm)");
     if (!rc) {
