@@ -2,6 +2,7 @@
 // and the mask-head layout transform.  (css/models/conformer.py:188-303, css/executor/separator.py:100-104)
 #include "common.cuh"
 #include "conformer.h"
+#include "gemm.h"
 #include <cuda_bf16.h>
 
 // split 4 fp32 values into bf16 planes: plane p receives the bf16 rounding of what planes < p left over
@@ -236,20 +237,37 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 #define CM_D 256
 #define CM_HALO 16
 #define CM_TAPS (2 * CM_HALO + 1)
-#define CM_THREADS 1024
+#define CM_THREADS 512
 #define CM_MAX_ROWS 220          // (tile + 2*halo) rows of 1 KB each must fit in shared memory
 #define CM_OUT 8                 // outputs per register pass of the depthwise filter
 
-// One CTA per (sequence, time tile); the whole 150-frame chunk is one tile, so nothing is recomputed.
-// Phase 1: 32 warps, one row each: LayerNorm + scalar GLU into shared memory (zero rows outside [0, T)).
-// Phase 2: thread = (channel, quarter of the tile); 8 outputs are produced per pass from 40 shared-memory
-// reads (5 per output instead of 33), taps and accumulators in registers.
+// One CTA per (sequence, time tile); a 150-frame chunk is one tile, so nothing is recomputed.
+// Phase 1: 16 warps, one row each: LayerNorm + scalar GLU into shared memory (zero rows outside [0, T)).
+// Phase 2: thread = (channel pair, quarter of the tile); 8 outputs per pass from 40 shared-memory reads (5 per output
+// instead of 33), taps and accumulators in registers as channel pairs so that every filter step is one packed
+// fp32 FMA (FFMA2) -- the kernel is bound by the FMA pipe, not by memory.
+// Tiling (ConvPlan): the first n_full sequences get `full_tiles` tiles each; what is left -- less than one wave of CTAs,
+// which would otherwise cost a whole extra wave -- is cut into `tail_tiles` short tiles spread over the idle SMs.
+struct ConvPlan { int n_full, full_tiles, full_len, tail_tiles, tail_len; };
+
 __global__ void __launch_bounds__(CM_THREADS, 1)
-conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, int tile_len, ConvModuleParams p) {
+conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, ConvPlan pl, ConvModuleParams p) {
     extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D]
-    const long n = blockIdx.x;
-    const int t0 = blockIdx.y * tile_len;
-    const int tile = min(tile_len, T - t0);
+    long n;
+    int t0, tile;
+    {
+        const int bid = blockIdx.x, nf = pl.n_full * pl.full_tiles;
+        if (bid < nf) {
+            n = bid / pl.full_tiles;
+            t0 = (bid - (int)n * pl.full_tiles) * pl.full_len;
+            tile = min(pl.full_len, T - t0);
+        } else {
+            const int r = bid - nf, q = r / pl.tail_tiles;
+            n = pl.n_full + q;
+            t0 = (r - q * pl.tail_tiles) * pl.tail_len;
+            tile = min(pl.tail_len, T - t0);
+        }
+    }
     const int rows = tile + 2 * CM_HALO;
     const float* xs = x + n * (long)T * CM_D;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -282,38 +300,42 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
             for (int e = 0; e < 4; ++e) {
                 const float a = y[e] * p.pw1_w0 + p.pw1_b0;
                 const float gt = y[e] * p.pw1_w1 + p.pw1_b1;
-                y[e] = a / (1.f + expf(-gt));
+                y[e] = __fdividef(a, 1.f + __expf(-gt));         // a * sigmoid(gt)
             }
             urow[lane + 32 * i] = make_float4(y[0], y[1], y[2], y[3]);
         }
     }
     __syncthreads();
-    const int c = threadIdx.x & (CM_D - 1), part = threadIdx.x >> 8;
-    float w[CM_TAPS];
+    const int c = 2 * (threadIdx.x & (CM_D / 2 - 1)), part = threadIdx.x >> 7;     // channels c, c+1
+    float2 w[CM_TAPS];
 #pragma unroll
-    for (int k = 0; k < CM_TAPS; ++k) w[k] = p.dw_w[c * CM_TAPS + k];
-    const float bias = p.dw_b[c], sc = p.bn_scale[c], sh = p.bn_shift[c];
+    for (int k = 0; k < CM_TAPS; ++k) w[k] = make_float2(p.dw_w[c * CM_TAPS + k], p.dw_w[(c + 1) * CM_TAPS + k]);
+    const float2 bias = *reinterpret_cast<const float2*>(p.dw_b + c);
+    const float2 sc = *reinterpret_cast<const float2*>(p.bn_scale + c), sh = *reinterpret_cast<const float2*>(p.bn_shift + c);
     float* os = out + n * (long)T * CM_D;
     const int per = ((tile + 4 * CM_OUT - 1) / (4 * CM_OUT)) * CM_OUT;       // multiple of CM_OUT
     const int t_end = min(tile, (part + 1) * per);
     for (int tt = part * per; tt < t_end; tt += CM_OUT) {
-        float acc[CM_OUT];
+        float2 acc[CM_OUT];
 #pragma unroll
         for (int j = 0; j < CM_OUT; ++j) acc[j] = bias;
 #pragma unroll
         for (int kk = 0; kk < CM_TAPS + CM_OUT - 1; ++kk) {
             const int r = tt + kk;
-            const float u = (r < rows) ? U[r * CM_D + c] : 0.f;
+            const float2 u = (r < rows) ? *reinterpret_cast<const float2*>(U + r * CM_D + c) : make_float2(0.f, 0.f);
 #pragma unroll
             for (int j = 0; j < CM_OUT; ++j)
-                if (kk - j >= 0 && kk - j < CM_TAPS) acc[j] = fmaf(w[kk - j], u, acc[j]);
+                if (kk - j >= 0 && kk - j < CM_TAPS) acc[j] = __ffma2_rn(w[kk - j], u, acc[j]);
         }
 #pragma unroll
         for (int j = 0; j < CM_OUT; ++j) {
             if (tt + j < t_end) {
-                const float v = fmaxf(acc[j] * sc + sh, 0.f) * p.pw2_w + p.pw2_b;
                 const long idx = (long)(t0 + tt + j) * CM_D + c;
-                os[idx] = xs[idx] + v;
+                const float2 xv = *reinterpret_cast<const float2*>(xs + idx);
+                float2 o;
+                o.x = xv.x + (fmaxf(acc[j].x * sc.x + sh.x, 0.f) * p.pw2_w + p.pw2_b);
+                o.y = xv.y + (fmaxf(acc[j].y * sc.y + sh.y, 0.f) * p.pw2_w + p.pw2_b);
+                *reinterpret_cast<float2*>(os + idx) = o;
             }
         }
     }
@@ -324,17 +346,34 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
     CSS_REQUIRE(p.ksize == CM_TAPS, "conv_module: taps must be centre-padded to %d (got %d)", CM_TAPS, p.ksize);
     CSS_REQUIRE(N > 0 && T > 0 && x != out, "conv_module: bad arguments");
     const int max_tile = CM_MAX_ROWS - 2 * CM_HALO;
-    const int n_tiles = (T + max_tile - 1) / max_tile;
-    const int tile_len = (T + n_tiles - 1) / n_tiles;
-    const size_t smem = sizeof(float) * (size_t)(tile_len + 2 * CM_HALO) * CM_D;
+    ConvPlan pl;
+    pl.full_tiles = (T + max_tile - 1) / max_tile;
+    pl.full_len = (T + pl.full_tiles - 1) / pl.full_tiles;
+    pl.n_full = (int)N;
+    pl.tail_tiles = 1;
+    pl.tail_len = pl.full_len;
+    const int sms = sm_count();
+    const int rem = (int)(N % sms);
+    if (pl.full_tiles == 1 && N > sms && rem > 0 && T >= 16) {
+        // cut the sequences of the last, partial wave into short tiles (at least 8 frames) that fill the idle SMs
+        int tiles = sms / rem;
+        if (tiles > T / 8) tiles = T / 8;
+        if (tiles > 1) {
+            pl.tail_len = (T + tiles - 1) / tiles;
+            pl.tail_tiles = (T + pl.tail_len - 1) / pl.tail_len;
+            pl.n_full = (int)N - rem;
+        }
+    }
+    const long ctas = (long)pl.n_full * pl.full_tiles + (N - pl.n_full) * pl.tail_tiles;
+    CSS_REQUIRE(ctas < (1L << 31), "conv_module: too many sequences (%ld)", N);
+    const size_t smem = sizeof(float) * (size_t)(pl.full_len + 2 * CM_HALO) * CM_D;
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_MAX_ROWS * CM_D * 4);
         attr_set = true;
     }
-    dim3 grid((unsigned)N, n_tiles);
     css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
-    conv_module_kernel<<<grid, CM_THREADS, smem, st>>>(x, out, T, tile_len, p);
+    conv_module_kernel<<<(unsigned)ctas, CM_THREADS, smem, st>>>(x, out, T, pl, p);
     css_prof_end(st);
     return css_check_launch("conv_module");
 }

@@ -26,6 +26,20 @@ __device__ __forceinline__ float2 load_x(const float2* __restrict__ spec, const 
 // accumulators (42 per thread); the 28 pairs (i, j >= i) are dealt to the four warps by rows {0}, {1,6}, {2,5}, {3,4}
 // -- 7 pairs each.  The next frame's 7 channels and 3 mask values are requested before the current frame is consumed.
 // scm[b][mask][e][KP] fp32 (normalised by the mask sum, compute_scm(normalize=True)); energy slot 1 = sum |mask x0|^2.
+// row I of the upper triangle: pairs (I, j >= I) into acc[.][Q0 ...]
+template <int I, int Q0>
+__device__ __forceinline__ void scm_row(const float2 (&x)[MV_M], const float (&w)[3], float2 (&acc)[3][7]) {
+    const float2 xi = x[I];
+    const float2 xs = make_float2(xi.y, -xi.x);
+#pragma unroll
+    for (int j = I; j < MV_M; ++j) {
+        // x_i * conj(x_j) = (xr_i xr_j + xi_i xi_j, xi_i xr_j - xr_i xi_j)
+        const float2 pr = __ffma2_rn(xi, make_float2(x[j].x, x[j].x), __fmul2_rn(xs, make_float2(x[j].y, x[j].y)));
+#pragma unroll
+        for (int m = 0; m < 3; ++m) acc[m][Q0 + j - I] = __ffma2_rn(make_float2(w[m], w[m]), pr, acc[m][Q0 + j - I]);
+    }
+}
+
 template <int G>
 __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
                                           long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
@@ -34,11 +48,11 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
     const long b = blockIdx.y;
     const int lane = threadIdx.x;
     const int k = blockIdx.x * MV_BINS + lane;
-    float acc[3][14];
+    float2 acc[3][7];                        // (re, im) of the thread's 7 pairs, per mask: one packed FMA (FFMA2) each
 #pragma unroll
     for (int m = 0; m < 3; ++m)
 #pragma unroll
-        for (int i = 0; i < 14; ++i) acc[m][i] = 0.f;
+        for (int i = 0; i < 7; ++i) acc[m][i] = make_float2(0.f, 0.f);
     float msum[3] = {0.f, 0.f, 0.f}, e_mask[2] = {0.f, 0.f};
     if (k < CSS_NBINS) {
         const float* mrow = stitched + (b * hop_frames) * (long)CSS_KP + k;
@@ -73,23 +87,8 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
                     e_mask[m] += ar * ar + ai * ai;
                 }
             }
-            int q = 0;
-#pragma unroll
-            for (int rr = 0; rr < 2; ++rr) {
-                const int i = rr == 0 ? R0 : R1;
-                if (i < 0) continue;
-#pragma unroll
-                for (int j = i; j < MV_M; ++j) {
-                    const float pr = x[i].x * x[j].x + x[i].y * x[j].y;      // x_i * conj(x_j)
-                    const float pi = x[i].y * x[j].x - x[i].x * x[j].y;
-#pragma unroll
-                    for (int m = 0; m < 3; ++m) {
-                        acc[m][q] += w[m] * pr;
-                        acc[m][q + 1] += w[m] * pi;
-                    }
-                    q += 2;
-                }
-            }
+            scm_row<R0, 0>(x, w, acc);
+            if (R1 >= 0) scm_row<(R1 >= 0 ? R1 : 0), MV_M - R0>(x, w, acc);
         }
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
@@ -103,9 +102,9 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
                 const int e0 = 2 * (i * MV_M - (i * (i - 1)) / 2);        // packed slot of pair (i, i)
 #pragma unroll
                 for (int j = i; j < MV_M; ++j) {
-                    dst[(long)(e0 + 2 * (j - i)) * CSS_KP] = acc[m][q] * inv;
-                    dst[(long)(e0 + 2 * (j - i) + 1) * CSS_KP] = acc[m][q + 1] * inv;
-                    q += 2;
+                    dst[(long)(e0 + 2 * (j - i)) * CSS_KP] = acc[m][q].x * inv;
+                    dst[(long)(e0 + 2 * (j - i) + 1) * CSS_KP] = acc[m][q].y * inv;
+                    ++q;
                 }
             }
         }
