@@ -7,6 +7,9 @@ int layernorm_launch(const float* x, const float* g, const float* b, float* y, l
                      cudaStream_t st);
 int layernorm_planes_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
                             void* planes, long plane_stride, int n_planes, cudaStream_t st);
+// y = LN(x; g, b); planes = split planes of LN(y; g2, b2) (g2 == null: of y)
+int layernorm2_planes_launch(const float* x, const float* g, const float* b, float* y, const float* g2, const float* b2, long M,
+                             int d, float eps, int relu, void* planes, long plane_stride, int n_planes, cudaStream_t st);
 int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out, long N, int T, int H, int dk,
                      cudaStream_t st);
 

@@ -129,9 +129,10 @@ static int tc_gemm(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     return rc;
 }
 
+// ln_done: yP already holds the planes of LN(x) (written by the previous block's output norm)
 static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& w2, float* x, const PlaneMat& yP, const PlaneMat& hP,
-                  int P, long M, int d, int dffn, cudaStream_t st) {
-    int rc = layernorm_planes_launch(x, w.ln_g, w.ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st);
+                  int P, long M, int d, int dffn, bool ln_done, cudaStream_t st) {
+    int rc = ln_done ? 0 : layernorm_planes_launch(x, w.ln_g, w.ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st);
     if (rc) return rc;
     GemmEpilogue e1 = {w.b1, 1, 1.f, nullptr, 0, 0.f};
     if ((rc = tc_gemm(yP, w1, P, M, dffn, d, e1, nullptr, 0, &hP, st))) return rc;
@@ -165,7 +166,7 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
     for (int l = 0; l < c.num_blocks; ++l) {
         const css_conformer_block& b = m->blk[l];
         const BlockPlanes& q = m->bp[l];
-        if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, st))) return rc;
+        if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, l > 0, st))) return rc;
         if ((rc = layernorm_planes_launch(x, b.att_ln_g, b.att_ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st))) return rc;
         GemmEpilogue eq = {b.bqkv, 0, 1.f, nullptr, 0, 0.f};
         if (attention_tc_supported(T, d / c.heads)) {
@@ -185,11 +186,13 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
                                b.bn_scale, b.bn_shift, b.pw2_w, b.pw2_b, 33};
         if ((rc = conv_module_launch(x, a, N, T, d, cp, st))) return rc;
         { float* t = x; x = a; a = t; }
-        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, st))) return rc;
-        // block output LN: fp32 for the residual stream; the last block also feeds the head GEMM
+        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, false, st))) return rc;
+        // block output LN: fp32 for the residual stream, and in the same pass the planes the next GEMM reads -- the next
+        // block's FFN-in norm of that output, or the output itself for the head GEMM after the last block
         const bool last = l == c.num_blocks - 1;
-        if ((rc = layernorm_planes_launch(x, b.out_ln_g, b.out_ln_b, x, M, d, 1e-5f, 0, last ? yP.ptr : nullptr, yP.plane_stride,
-                                          last ? P : 0, st))) return rc;
+        const css_ffn_weights* nf = last ? nullptr : &m->blk[l + 1].ff_in;
+        if ((rc = layernorm2_planes_launch(x, b.out_ln_g, b.out_ln_b, x, nf ? nf->ln_g : nullptr, nf ? nf->ln_b : nullptr, M, d, 1e-5f,
+                                           0, yP.ptr, yP.plane_stride, P, st))) return rc;
     }
     if (c.num_blocks == 0 && (rc = split_planes_launch(x, M, d, d, yP, st))) return rc;
     if (head) {

@@ -27,7 +27,8 @@ __device__ __forceinline__ void store_split4(float4 o, __nv_bfloat16* base, long
 template <int VPL>   // float4 vectors per lane: d = 128 * VPL
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* x, const float* __restrict__ g, const float* __restrict__ b, float* y,
-                 long M, float eps, int relu, __nv_bfloat16* planes, long plane_stride, int n_planes) {
+                 long M, float eps, int relu, __nv_bfloat16* planes, long plane_stride, int n_planes,
+                 const float* __restrict__ g2, const float* __restrict__ b2) {
     const long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (row >= M) return;
@@ -60,7 +61,33 @@ layernorm_kernel(const float* x, const float* __restrict__ g, const float* __res
         o.w = (v[i].w - mean) * rstd * gg.w + bb.w;
         if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
         if (y) yr[lane + 32 * i] = o;
-        if (planes) store_split4(o, planes + row * d + 4 * (lane + 32 * i), plane_stride, n_planes);
+        if (planes && !g2) store_split4(o, planes + row * d + 4 * (lane + 32 * i), plane_stride, n_planes);
+        v[i] = o;
+    }
+    if (!g2) return;
+    // second LayerNorm of the row just produced (a block's output norm followed by the next block's FFN-in norm): the
+    // planes hold LN2(LN1(x)), y holds LN1(x) -- the same values two launches would give, without re-reading y
+    s = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) s += v[i].x + v[i].y + v[i].z + v[i].w;
+    const float mean2 = warp_sum(s) / d;
+    q = 0.f;
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        float a = v[i].x - mean2, bb = v[i].y - mean2, c = v[i].z - mean2, dd = v[i].w - mean2;
+        q += a * a + bb * bb + c * c + dd * dd;
+    }
+    const float rstd2 = rsqrtf(warp_sum(q) / d + eps);
+#pragma unroll
+    for (int i = 0; i < VPL; ++i) {
+        const float4 gg = reinterpret_cast<const float4*>(g2)[lane + 32 * i];
+        const float4 bb = reinterpret_cast<const float4*>(b2)[lane + 32 * i];
+        float4 o;
+        o.x = (v[i].x - mean2) * rstd2 * gg.x + bb.x;
+        o.y = (v[i].y - mean2) * rstd2 * gg.y + bb.y;
+        o.z = (v[i].z - mean2) * rstd2 * gg.z + bb.z;
+        o.w = (v[i].w - mean2) * rstd2 * gg.w + bb.w;
+        store_split4(o, planes + row * d + 4 * (lane + 32 * i), plane_stride, n_planes);
     }
 }
 
@@ -72,16 +99,23 @@ int layernorm_launch(const float* x, const float* g, const float* b, float* y, l
 // y (fp32, optional) and/or bf16 split planes (pitch d) of LayerNorm(x)
 int layernorm_planes_launch(const float* x, const float* g, const float* b, float* y, long M, int d, float eps, int relu,
                             void* planes_v, long plane_stride, int n_planes, cudaStream_t st) {
+    return layernorm2_planes_launch(x, g, b, y, nullptr, nullptr, M, d, eps, relu, planes_v, plane_stride, n_planes, st);
+}
+
+// y = LN(x; g, b) (fp32, optional); planes = split planes of LN(y; g2, b2) when g2 is given, of y otherwise
+int layernorm2_planes_launch(const float* x, const float* g, const float* b, float* y, const float* g2, const float* b2, long M,
+                             int d, float eps, int relu, void* planes_v, long plane_stride, int n_planes, cudaStream_t st) {
     __nv_bfloat16* planes = static_cast<__nv_bfloat16*>(planes_v);
     CSS_REQUIRE(M > 0 && (y || planes), "layernorm: empty input or no output");
+    CSS_REQUIRE(!g2 || (b2 && planes), "layernorm: the second norm needs its bias and a plane output");
     CSS_REQUIRE(d % 128 == 0 && d <= 1024, "layernorm: d=%d must be a multiple of 128 and <= 1024", d);
     const unsigned grid = (unsigned)((M + 7) / 8);
     css_prof_begin(3, (double)M * d * (4.0 + (y ? 4.0 : 0.0) + 2.0 * (planes ? n_planes : 0)), st);
     switch (d / 128) {
-        case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
-        case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
-        case 4: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
-        case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes); break;
+        case 1: layernorm_kernel<1><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes, g2, b2); break;
+        case 2: layernorm_kernel<2><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes, g2, b2); break;
+        case 4: layernorm_kernel<4><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes, g2, b2); break;
+        case 8: layernorm_kernel<8><<<grid, 256, 0, st>>>(x, g, b, y, M, eps, relu, planes, plane_stride, n_planes, g2, b2); break;
         default: CSS_REQUIRE(false, "layernorm: unsupported d=%d", d);
     }
     css_prof_end(st);
@@ -271,38 +305,57 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
     const int rows = tile + 2 * CM_HALO;
     const float* xs = x + n * (long)T * CM_D;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    for (int r = warp; r < rows; r += CM_THREADS / 32) {
-        const int t = t0 - CM_HALO + r;
-        float4* urow = reinterpret_cast<float4*>(U + r * CM_D);
-        if (t < 0 || t >= T) {
-            urow[lane] = make_float4(0, 0, 0, 0);
-            urow[lane + 32] = make_float4(0, 0, 0, 0);
-            continue;
-        }
-        const float4* xr = reinterpret_cast<const float4*>(xs + (long)t * CM_D);
-        float4 v[2] = {xr[lane], xr[lane + 32]};
-        float s = v[0].x + v[0].y + v[0].z + v[0].w + v[1].x + v[1].y + v[1].z + v[1].w;
-        const float mean = warp_sum(s) / CM_D;
-        float q = 0.f;
+    // four rows per pass: their eight loads are in flight together (the phase is latency-bound otherwise)
+    constexpr int NW = CM_THREADS / 32, RB = 4;
+    for (int rb = warp; rb < rows; rb += NW * RB) {
+        float4 v[RB][2];
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
-            q += a * a + b * b + c * c + d * d;
-        }
-        const float rstd = rsqrtf(warp_sum(q) / CM_D + 1e-5f);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const float4 g = reinterpret_cast<const float4*>(p.ln_g)[lane + 32 * i];
-            const float4 b = reinterpret_cast<const float4*>(p.ln_b)[lane + 32 * i];
-            float y[4] = {(v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y,
-                          (v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w};
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-                const float a = y[e] * p.pw1_w0 + p.pw1_b0;
-                const float gt = y[e] * p.pw1_w1 + p.pw1_b1;
-                y[e] = __fdividef(a, 1.f + __expf(-gt));         // a * sigmoid(gt)
+        for (int i = 0; i < RB; ++i) {
+            const int r = rb + i * NW, t = t0 - CM_HALO + r;
+            if (r < rows && t >= 0 && t < T) {
+                const float4* xr = reinterpret_cast<const float4*>(xs + (long)t * CM_D);
+                v[i][0] = xr[lane];
+                v[i][1] = xr[lane + 32];
+            } else {
+                v[i][0] = v[i][1] = make_float4(0, 0, 0, 0);
             }
-            urow[lane + 32 * i] = make_float4(y[0], y[1], y[2], y[3]);
+        }
+        const float4 g0 = reinterpret_cast<const float4*>(p.ln_g)[lane], g1 = reinterpret_cast<const float4*>(p.ln_g)[lane + 32];
+        const float4 b0 = reinterpret_cast<const float4*>(p.ln_b)[lane], b1 = reinterpret_cast<const float4*>(p.ln_b)[lane + 32];
+#pragma unroll
+        for (int i = 0; i < RB; ++i) {
+            const int r = rb + i * NW, t = t0 - CM_HALO + r;
+            if (r >= rows) break;                      // warp-uniform
+            float4* urow = reinterpret_cast<float4*>(U + r * CM_D);
+            if (t < 0 || t >= T) {
+                urow[lane] = make_float4(0, 0, 0, 0);
+                urow[lane + 32] = make_float4(0, 0, 0, 0);
+                continue;
+            }
+            const float4 v0 = v[i][0], v1 = v[i][1];
+            const float s = v0.x + v0.y + v0.z + v0.w + v1.x + v1.y + v1.z + v1.w;
+            const float mean = warp_sum(s) / CM_D;
+            float q = 0.f;
+            {
+                float a = v0.x - mean, b = v0.y - mean, c = v0.z - mean, d = v0.w - mean;
+                q += a * a + b * b + c * c + d * d;
+                a = v1.x - mean; b = v1.y - mean; c = v1.z - mean; d = v1.w - mean;
+                q += a * a + b * b + c * c + d * d;
+            }
+            const float rstd = rsqrtf(warp_sum(q) / CM_D + 1e-5f);
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh) {
+                const float4 vv = hh ? v1 : v0, g = hh ? g1 : g0, bb = hh ? b1 : b0;
+                float y[4] = {(vv.x - mean) * rstd * g.x + bb.x, (vv.y - mean) * rstd * g.y + bb.y,
+                              (vv.z - mean) * rstd * g.z + bb.z, (vv.w - mean) * rstd * g.w + bb.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float a = y[e] * p.pw1_w0 + p.pw1_b0;
+                    const float gt = y[e] * p.pw1_w1 + p.pw1_b1;
+                    y[e] = __fdividef(a, 1.f + __expf(-gt));         // a * sigmoid(gt)
+                }
+                urow[lane + 32 * hh] = make_float4(y[0], y[1], y[2], y[3]);
+            }
         }
     }
     __syncthreads();
