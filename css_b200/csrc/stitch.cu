@@ -36,7 +36,7 @@ __device__ __forceinline__ float pymod360(float x) {
     return (r < 0.f) ? r + 360.f : r;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)      // two CTAs per SM: the 104 KB steering table of the usual band fits twice
 doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T,
                  const float2* __restrict__ svT, const float* __restrict__ angles, int lo, int nf, float thresh,
                  float binarize, float* masks, int C, float* __restrict__ like_out, int* __restrict__ idx_out) {
@@ -54,24 +54,29 @@ doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chu
     const float2* sb = spec + (b * stride_chunk) * CSS_KP;
     for (int i = threadIdx.x; i < nf * T; i += blockDim.x) {
         const int t = i / nf, fi = i - t * nf, f = lo + fi;
-        float2 x[DOA_M];
+        float2 xx[DOA_M], xy[DOA_M];         // (re, re) and (im, im) of each channel: operands of the packed FMAs below
         float xpow = 0.f;
 #pragma unroll
         for (int m = 0; m < DOA_M; ++m) {
-            x[m] = sb[((long)m * stride_d + t) * CSS_KP + f];
-            xpow += x[m].x * x[m].x + x[m].y * x[m].y;
+            const float2 x = sb[((long)m * stride_d + t) * CSS_KP + f];
+            xpow += x.x * x.x + x.y * x.y;
+            xx[m] = make_float2(x.x, x.x);
+            xy[m] = make_float2(x.y, x.y);
         }
         const float* mk = mb + ((long)f * T + t) * C;
         const float b0 = mk[0] > binarize ? 1.f : 0.f, b1 = mk[1] > binarize ? 1.f : 0.f;
 #pragma unroll
         for (int a = 0; a < DOA_A; ++a) {
-            float re = 0.f, im = 0.f;
+            // conj(x) . s = (sum xr sr + sum xi si, sum xr si - sum xi sr): P = sum xr * (sr, si), Q = sum xi * (sr, si),
+            // two packed fp32 FMAs (FFMA2) per channel -- the kernel is bound by the FMA pipe
+            float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
 #pragma unroll
             for (int m = 0; m < DOA_M; ++m) {
-                const float2 s = sv[(a * DOA_M + m) * nf + fi];
-                re += x[m].x * s.x + x[m].y * s.y;      // conj(x) * s
-                im += x[m].x * s.y - x[m].y * s.x;
+                const float2 sm = sv[(a * DOA_M + m) * nf + fi];
+                P = __ffma2_rn(xx[m], sm, P);
+                Q = __ffma2_rn(xy[m], sm, Q);
             }
+            const float re = P.x + Q.y, im = P.y - Q.x;
             const float l = -sqrtf(xpow - (re * re + im * im));   // NaN when the radicand rounds < 0 (Q7)
             acc[0][a] += b0 * l;
             acc[1][a] += b1 * l;

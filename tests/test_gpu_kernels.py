@@ -230,6 +230,21 @@ def test_conformer_forward_vs_oracle(cuda, gemm_mode, N, T):
     assert rel_inf(y_pred, y_o) < 1e-4
 
 
+def test_conformer_many_sequences_match_small_batches(cuda):
+    """More sequences than SMs: the conv module cuts the last partial wave into short tiles and every block after the first
+    takes its FFN-in planes from the previous block's fused output norm.  The masks must equal, bit for bit, those of the
+    same sequences run in batches small enough to take neither path's tail branch."""
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    n = 2 * sms + 4
+    model = golden_conformer(num_blocks=3, idim=257).to(cuda)
+    g = torch.Generator().manual_seed(77)
+    f = (torch.randn(n, 150, 257, generator=g) * 2 + 0.3).to(cuda)
+    _, whole = model(f)
+    parts = [model(f[i:i + sms])[1] for i in range(0, n, sms)]
+    for c in range(3):
+        assert torch.equal(whole[c], torch.cat([p[c] for p in parts], 0))
+
+
 def test_conformer_bf16_mode_bound(cuda):
     """Plain bf16 tensor-core mode: stated looser bound (masks abs <= 5e-2 on a 2-block net)."""
     nv = _nv()
