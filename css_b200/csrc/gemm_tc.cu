@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "gemm.h"
 #include <cuda.h>
+#include <cstdlib>
 #include <cuda_bf16.h>
 
 namespace {
@@ -57,6 +58,16 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, u
         "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
         ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
         : "memory");
+}
+// the epilogue's staging tile is addressed in the shared window explicitly: through the (re-aligned) generic pointer the
+// compiler emitted generic LD.E/ST.E, whose long-scoreboard latency sat on the critical path of every chunk
+__device__ __forceinline__ void sts128(uint32_t addr, float a, float b, float c, float d) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -135,6 +146,177 @@ struct Cfg {
     static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_STAGING;
     static_assert(STAGES >= 2, "tile does not fit a 2-stage ring");
 };
+
+// Epilogue of one 128 x BN accumulator (TMEM columns tmem_acc ..) by one of the 8 epilogue warps: warp (q, chalf) drains
+// TMEM lanes 32q.. of the column half `chalf`.  row_base: global row of TMEM lane 32q; nb: n-tile index.
+template <int P, int BN, bool TRAIN, int EM>
+__device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tmem_acc, uint32_t stg, long row_base, int nb, long M,
+                                              int N, int q, int chalf, int lane, int ksplit) {
+    const int cg = lane & 7, rsub = lane >> 3;
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c0 = chalf * (BN / 2) + cc * 32;
+        const int col0 = nb * BN + c0;
+        if (col0 >= N && (!ep.planes || col0 >= ep.ldp)) break;          // warp-uniform
+        uint32_t r[32];
+        tc_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + c0, r);
+        // phase A: thread = row; 16-byte pieces XOR-swizzled by the row so both phases are conflict-free
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            sts128(stg + (lane * 8 + (j ^ (lane & 7))) * 16, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        // phase B: 8 lanes cover one 128-byte row segment -> coalesced global traffic
+        const int col = col0 + cg * 4;
+        if constexpr (EM == 1 || EM == 2) {
+            float4 xs[8];
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const int rr = it * 4 + rsub;
+                xs[it] = lds128(stg + (rr * 8 + (cg ^ (rr & 7))) * 16);
+            }
+            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ep.bias) bb = make_float4(__ldg(ep.bias + col), __ldg(ep.bias + col + 1), __ldg(ep.bias + col + 2), __ldg(ep.bias + col + 3));
+            const long row0 = row_base + rsub;
+            if constexpr (EM == 1) {
+                const float floor_v = ep.act == 1 ? 0.f : -INFINITY;
+                __nv_bfloat16* pp = ep.planes + row0 * ep.ldp + col;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    if (row0 + it * 4 >= M) continue;
+                    float v0 = fmaxf(xs[it].x + bb.x, floor_v), v1 = fmaxf(xs[it].y + bb.y, floor_v);
+                    float v2 = fmaxf(xs[it].z + bb.z, floor_v), v3 = fmaxf(xs[it].w + bb.w, floor_v);
+                    __nv_bfloat16* dst = pp + (long)(it * 4) * ep.ldp;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        const __nv_bfloat162 h01 = __floats2bfloat162_rn(v0, v1);
+                        const __nv_bfloat162 h23 = __floats2bfloat162_rn(v2, v3);
+                        uint2 w;
+                        w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                        w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                        *reinterpret_cast<uint2*>(dst + p * ep.plane_stride) = w;
+                        if (p + 1 < P) {
+                            v0 -= __uint_as_float(w.x << 16); v1 -= __uint_as_float(w.x & 0xffff0000u);
+                            v2 -= __uint_as_float(w.y << 16); v3 -= __uint_as_float(w.y & 0xffff0000u);
+                        }
+                    }
+                }
+            } else {
+                float4 res4[8];
+                if (ep.residual) {
+                    const float* rp = ep.residual + row0 * ep.ldr + col;
+#pragma unroll
+                    for (int it = 0; it < 8; ++it)
+                        res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr)
+                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
+                } else {
+#pragma unroll
+                    for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+                float* cp = ep.c + row0 * ep.ldc + col;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    if (row0 + it * 4 >= M) continue;
+                    float4 o;
+                    o.x = fmaf(xs[it].x + bb.x, ep.alpha, res4[it].x);
+                    o.y = fmaf(xs[it].y + bb.y, ep.alpha, res4[it].y);
+                    o.z = fmaf(xs[it].z + bb.z, ep.alpha, res4[it].z);
+                    o.w = fmaf(xs[it].w + bb.w, ep.alpha, res4[it].w);
+                    *reinterpret_cast<float4*>(cp + (long)(it * 4) * ep.ldc) = o;
+                }
+            }
+            __syncwarp();
+            continue;
+        }
+        float b4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (ep.bias) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) if (col + i < N) b4[i] = __ldg(ep.bias + col + i);
+        }
+        const bool vec_ok = col + 4 <= N;
+        // the residual may alias C (x <- x + ...): fetch all of this chunk's residual rows before any store,
+        // otherwise every load would have to wait for the previous store
+        float4 res4[8];
+        if (ep.residual) {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) {
+                const long row = row_base + it * 4 + rsub;
+                res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (row < M) {
+                    const float* rp = ep.residual + row * ep.ldr + col;
+                    if (vec_ok && (ep.ldr & 3) == 0) {
+                        res4[it] = *reinterpret_cast<const float4*>(rp);
+                    } else {
+                        if (col < N) res4[it].x = rp[0];
+                        if (col + 1 < N) res4[it].y = rp[1];
+                        if (col + 2 < N) res4[it].z = rp[2];
+                        if (col + 3 < N) res4[it].w = rp[3];
+                    }
+                }
+            }
+        }
+        // all shared-memory reads of the chunk before the first global store: the compiler cannot prove that the
+        // (generic) staging pointer and the outputs do not alias, so a load inside the store loop would serialise it
+        float4 xs[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            xs[it] = lds128(stg + (rr * 8 + (cg ^ (rr & 7))) * 16);
+        }
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            const long row = row_base + rr;
+            const float4 x4 = xs[it];
+            if (row >= M) continue;
+            float v[4] = {x4.x + b4[0], x4.y + b4[1], x4.z + b4[2], x4.w + b4[3]};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (ep.act == 1) v[i] = fmaxf(v[i], 0.f);
+                if (ep.clamp_max > 0.f) v[i] = fminf(v[i], ep.clamp_max);
+                v[i] *= ep.alpha;
+            }
+            if (ep.residual) { v[0] += res4[it].x; v[1] += res4[it].y; v[2] += res4[it].z; v[3] += res4[it].w; }
+            if (TRAIN && ep.mask) {
+                const __nv_bfloat16* mp = ep.mask + row * ep.ldmask + col;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (col + i < N && !(__bfloat162float(mp[i]) > 0.f)) v[i] = 0.f;
+            }
+            if (TRAIN && ksplit > 1) {
+                float* cp = ep.c + row * ep.ldc + col;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (col + i < N) atomicAdd(cp + i, v[i]);
+                continue;
+            }
+            if (ep.c) {
+                float* cp = ep.c + row * ep.ldc + col;
+                if (vec_ok && (ep.ldc & 3) == 0) {
+                    *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) if (col + i < N) cp[i] = v[i];
+                }
+            }
+            if (ep.planes && col + 4 <= ep.ldp) {
+                // split-float planes of the output (next GEMM's A operand); columns in [N, ldp) are zeroed
+#pragma unroll
+                for (int i = 0; i < 4; ++i) if (col + i >= N) v[i] = 0.f;
+                for (int p = 0; p < ep.n_planes; ++p) {
+                    const __nv_bfloat162 h01 = __floats2bfloat162_rn(v[0], v[1]);
+                    const __nv_bfloat162 h23 = __floats2bfloat162_rn(v[2], v[3]);
+                    v[0] -= __bfloat162float(h01.x); v[1] -= __bfloat162float(h01.y);
+                    v[2] -= __bfloat162float(h23.x); v[3] -= __bfloat162float(h23.y);
+                    uint2 w;
+                    w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                    w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                    *reinterpret_cast<uint2*>(ep.planes + p * ep.plane_stride + row * ep.ldp + col) = w;
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
 
 // TRAIN = false is the inference instantiation: no split-K bookkeeping and no mask test in the epilogue (they cost the
 // K = 256 GEMMs, whose tile time is set by the epilogue, 27 % when they were run-time branches)
@@ -245,178 +427,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int e = warp - 4;
         const int q = e & 3;                  // TMEM lane quadrant == warp % 4
         const int chalf = e >> 2;
-        float4* stg = reinterpret_cast<float4*>(smem + STAGES * C::STAGE_BYTES + 256) + e * 256;   // 4 KB per warp
-        const int cg = lane & 7, rsub = lane >> 3;
+        const uint32_t stg = smem_u32(smem + STAGES * C::STAGE_BYTES + 256) + e * 4096;              // 4 KB per warp
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int tt = TRAIN ? t % tiles : t;
             const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
-            const long row_base = (long)mb * BM + q * 32;
-#pragma unroll 1
-            for (int cc = 0; cc < BN / 64; ++cc) {
-                const int c0 = chalf * (BN / 2) + cc * 32;
-                const int col0 = nb * BN + c0;
-                if (col0 >= N && (!ep.planes || col0 >= ep.ldp)) break;          // warp-uniform
-                uint32_t r[32];
-                tc_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c0, r);
-                // phase A: thread = row; 16-byte pieces XOR-swizzled by the row so both phases are conflict-free
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    stg[lane * 8 + (j ^ (lane & 7))] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                                                    __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-                __syncwarp();
-                // phase B: 8 lanes cover one 128-byte row segment -> coalesced global traffic
-                const int col = col0 + cg * 4;
-                if constexpr (EM == 1 || EM == 2) {
-                    float4 xs[8];
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const int rr = it * 4 + rsub;
-                        xs[it] = stg[rr * 8 + (cg ^ (rr & 7))];
-                    }
-                    float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (ep.bias) bb = make_float4(__ldg(ep.bias + col), __ldg(ep.bias + col + 1), __ldg(ep.bias + col + 2), __ldg(ep.bias + col + 3));
-                    const long row0 = row_base + rsub;
-                    if constexpr (EM == 1) {
-                        const float floor_v = ep.act == 1 ? 0.f : -INFINITY;
-                        __nv_bfloat16* pp = ep.planes + row0 * ep.ldp + col;
-#pragma unroll
-                        for (int it = 0; it < 8; ++it) {
-                            if (row0 + it * 4 >= M) continue;
-                            float v0 = fmaxf(xs[it].x + bb.x, floor_v), v1 = fmaxf(xs[it].y + bb.y, floor_v);
-                            float v2 = fmaxf(xs[it].z + bb.z, floor_v), v3 = fmaxf(xs[it].w + bb.w, floor_v);
-                            __nv_bfloat16* dst = pp + (long)(it * 4) * ep.ldp;
-#pragma unroll
-                            for (int p = 0; p < P; ++p) {
-                                const __nv_bfloat162 h01 = __floats2bfloat162_rn(v0, v1);
-                                const __nv_bfloat162 h23 = __floats2bfloat162_rn(v2, v3);
-                                uint2 w;
-                                w.x = *reinterpret_cast<const uint32_t*>(&h01);
-                                w.y = *reinterpret_cast<const uint32_t*>(&h23);
-                                *reinterpret_cast<uint2*>(dst + p * ep.plane_stride) = w;
-                                if (p + 1 < P) {
-                                    v0 -= __uint_as_float(w.x << 16); v1 -= __uint_as_float(w.x & 0xffff0000u);
-                                    v2 -= __uint_as_float(w.y << 16); v3 -= __uint_as_float(w.y & 0xffff0000u);
-                                }
-                            }
-                        }
-                    } else {
-                        float4 res4[8];
-                        if (ep.residual) {
-                            const float* rp = ep.residual + row0 * ep.ldr + col;
-#pragma unroll
-                            for (int it = 0; it < 8; ++it)
-                                res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr)
-                                                               : make_float4(0.f, 0.f, 0.f, 0.f);
-                        } else {
-#pragma unroll
-                            for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        }
-                        float* cp = ep.c + row0 * ep.ldc + col;
-#pragma unroll
-                        for (int it = 0; it < 8; ++it) {
-                            if (row0 + it * 4 >= M) continue;
-                            float4 o;
-                            o.x = fmaf(xs[it].x + bb.x, ep.alpha, res4[it].x);
-                            o.y = fmaf(xs[it].y + bb.y, ep.alpha, res4[it].y);
-                            o.z = fmaf(xs[it].z + bb.z, ep.alpha, res4[it].z);
-                            o.w = fmaf(xs[it].w + bb.w, ep.alpha, res4[it].w);
-                            *reinterpret_cast<float4*>(cp + (long)(it * 4) * ep.ldc) = o;
-                        }
-                    }
-                    __syncwarp();
-                    continue;
-                }
-                float b4[4] = {0.f, 0.f, 0.f, 0.f};
-                if (ep.bias) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) if (col + i < N) b4[i] = __ldg(ep.bias + col + i);
-                }
-                const bool vec_ok = col + 4 <= N;
-                // the residual may alias C (x <- x + ...): fetch all of this chunk's residual rows before any store,
-                // otherwise every load would have to wait for the previous store
-                float4 res4[8];
-                if (ep.residual) {
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) {
-                        const long row = row_base + it * 4 + rsub;
-                        res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (row < M) {
-                            const float* rp = ep.residual + row * ep.ldr + col;
-                            if (vec_ok && (ep.ldr & 3) == 0) {
-                                res4[it] = *reinterpret_cast<const float4*>(rp);
-                            } else {
-                                if (col < N) res4[it].x = rp[0];
-                                if (col + 1 < N) res4[it].y = rp[1];
-                                if (col + 2 < N) res4[it].z = rp[2];
-                                if (col + 3 < N) res4[it].w = rp[3];
-                            }
-                        }
-                    }
-                }
-                // all shared-memory reads of the chunk before the first global store: the compiler cannot prove that the
-                // (generic) staging pointer and the outputs do not alias, so a load inside the store loop would serialise it
-                float4 xs[8];
-#pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int rr = it * 4 + rsub;
-                    xs[it] = stg[rr * 8 + (cg ^ (rr & 7))];
-                }
-#pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int rr = it * 4 + rsub;
-                    const long row = row_base + rr;
-                    const float4 x4 = xs[it];
-                    if (row >= M) continue;
-                    float v[4] = {x4.x + b4[0], x4.y + b4[1], x4.z + b4[2], x4.w + b4[3]};
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        if (ep.act == 1) v[i] = fmaxf(v[i], 0.f);
-                        if (ep.clamp_max > 0.f) v[i] = fminf(v[i], ep.clamp_max);
-                        v[i] *= ep.alpha;
-                    }
-                    if (ep.residual) { v[0] += res4[it].x; v[1] += res4[it].y; v[2] += res4[it].z; v[3] += res4[it].w; }
-                    if (TRAIN && ep.mask) {
-                        const __nv_bfloat16* mp = ep.mask + row * ep.ldmask + col;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (col + i < N && !(__bfloat162float(mp[i]) > 0.f)) v[i] = 0.f;
-                    }
-                    if (TRAIN && ksplit > 1) {
-                        float* cp = ep.c + row * ep.ldc + col;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) if (col + i < N) atomicAdd(cp + i, v[i]);
-                        continue;
-                    }
-                    if (ep.c) {
-                        float* cp = ep.c + row * ep.ldc + col;
-                        if (vec_ok && (ep.ldc & 3) == 0) {
-                            *reinterpret_cast<float4*>(cp) = make_float4(v[0], v[1], v[2], v[3]);
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) if (col + i < N) cp[i] = v[i];
-                        }
-                    }
-                    if (ep.planes && col + 4 <= ep.ldp) {
-                        // split-float planes of the output (next GEMM's A operand); columns in [N, ldp) are zeroed
-#pragma unroll
-                        for (int i = 0; i < 4; ++i) if (col + i >= N) v[i] = 0.f;
-                        for (int p = 0; p < ep.n_planes; ++p) {
-                            const __nv_bfloat162 h01 = __floats2bfloat162_rn(v[0], v[1]);
-                            const __nv_bfloat162 h23 = __floats2bfloat162_rn(v[2], v[3]);
-                            v[0] -= __bfloat162float(h01.x); v[1] -= __bfloat162float(h01.y);
-                            v[2] -= __bfloat162float(h23.x); v[3] -= __bfloat162float(h23.y);
-                            uint2 w;
-                            w.x = *reinterpret_cast<const uint32_t*>(&h01);
-                            w.y = *reinterpret_cast<const uint32_t*>(&h23);
-                            *reinterpret_cast<uint2*>(ep.planes + p * ep.plane_stride + row * ep.ldp + col) = w;
-                        }
-                    }
-                }
-                __syncwarp();
-            }
+            epilogue_tile<P, BN, TRAIN, EM>(ep, tmem_base + acc * BN, stg, (long)mb * BM + q * 32, nb, M, N, q, chalf, lane, ksplit);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[acc]);
@@ -429,6 +447,186 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 2) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
+    }
+}
+
+// ---- CTA-pair (cta_group::2) helpers ----
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// shared::cluster address of `local` (a shared::cta address of this CTA) in the CTA of rank `rank`
+__device__ __forceinline__ uint32_t mapa_rank(uint32_t local, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA load whose completion bytes are counted on a barrier that may live in the peer CTA of the pair
+__device__ __forceinline__ void tma_load_3d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1, int c2) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// commit of the pair's MMAs: arrives on the barrier at the same offset in both CTAs
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_pair(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+template <int P, int BK>
+struct Cfg2 {
+    static constexpr int BN = 256;
+    static constexpr int A_BYTES = BM * BK * 2;           // this CTA's 128 rows of A
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;     // this CTA's half of the 256 W rows
+    static constexpr int STAGE_BYTES = P * (A_BYTES + B_BYTES);
+    static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SMEM = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + EPI_STAGING;
+};
+
+// CTA-pair form of the kernel above for the inference GEMMs with N % 256 == 0: two CTAs on the SMs of one TPC work on a
+// 256 x 256 tile.  Each loads its own 128 rows of A and HALF of the W tile; the leader's tcgen05.mma.cta_group::2 (M = 256)
+// reads both halves, so the W traffic into and out of shared memory per SM is halved -- shared-memory bandwidth (TMA fill
+// + tensor-core operand reads + the epilogue's staging) is what bounds the one-CTA kernel, not the MMA rate.
+// Each CTA's TMEM holds its own 128 rows of the accumulator and its own epilogue warps drain it.
+template <int P, int BK, int EM>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
+                TcEpilogue ep) {
+    using C = Cfg2<P, BK>;
+    constexpr int BN = 256;
+    constexpr int STAGES = C::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+    uint64_t* full = bars;                    // [STAGES]  used in the leader only (bytes of both CTAs)
+    uint64_t* empty = bars + STAGES;          // [STAGES]  one per CTA, released by the pair's commit
+    uint64_t* tfull = bars + 2 * STAGES;      // [2]       one per CTA
+    uint64_t* tempty = bars + 2 * STAGES + 2; // [2]       used in the leader only: 16 epilogue warps of the pair
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int m_tiles = (int)((M + 2 * BM - 1) / (2 * BM)), n_tiles = N / BN;
+    const int total = m_tiles * n_tiles;
+    const int kblocks = K / BK;
+
+    if (warp == 0 && lane == 0) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    }
+    if (warp == 1 && lane == 0) {
+        for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 16); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(2 * BN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+    }
+    tc_fence_before();
+    cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs): own A rows, own half of W; bytes are counted on the leader's barrier =====
+        if (lane == 0) {
+            int stage = 0; uint32_t phase = 0;
+            for (int t = pair; t < total; t += n_pairs) {
+                const int mb = t / n_tiles, nb = t - mb * n_tiles;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&empty[stage], phase ^ 1);
+                    if (rank == 0) mbar_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+                    const uint32_t fb = mapa_rank(smem_u32(&full[stage]), 0);
+                    uint8_t* sa = smem + stage * C::STAGE_BYTES;
+                    uint8_t* sb = sa + P * C::A_BYTES;
+#pragma unroll
+                    for (int p = 0; p < P; ++p) {
+                        tma_load_3d_pair(sa + p * C::A_BYTES, &tmA, fb, kb * BK, mb * 2 * BM + (int)rank * BM, p);
+                        tma_load_3d_pair(sb + p * C::B_BYTES, &tmB, fb, kb * BK, nb * BN + (int)rank * (BN / 2), p);
+                    }
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (leader only) =====
+        if (lane == 0 && rank == 0) {
+            // instruction descriptor: D=f32, A=B=bf16, both K-major, N = 256, M = 256 over the pair
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+            int stage = 0; uint32_t phase = 0;
+            int acc = 0; uint32_t acc_phase = 0;
+            for (int t = pair; t < total; t += n_pairs) {
+                mbar_wait(&tempty[acc], acc_phase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    mbar_wait(&full[stage], phase);
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + stage * C::STAGE_BYTES);
+                    const uint32_t sb = sa + P * C::A_BYTES;
+#pragma unroll
+                    for (int ks = 0; ks < BK / UMMA_K; ++ks) {
+#pragma unroll
+                        for (int tm = 0; tm < Terms<P>::N; ++tm) {
+                            const int pa = term_a(tm), pb = term_b(tm);
+                            const uint64_t da = make_desc<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
+                            const uint64_t db = make_desc<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
+                            tc_mma_pair(d_tmem, da, db, idesc, (kb | ks | tm) != 0);
+                        }
+                    }
+                    tc_commit_pair(&empty[stage]);
+                    if (++stage == STAGES) { stage = 0; phase ^= 1; }
+                }
+                tc_commit_pair(&tfull[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===== epilogue (8 warps per CTA): this CTA's 128 rows of the pair's tile =====
+        const int e = warp - 4;
+        const int q = e & 3;
+        const int chalf = e >> 2;
+        const uint32_t stg = smem_u32(smem + STAGES * C::STAGE_BYTES + 256) + e * 4096;
+        int acc = 0; uint32_t acc_phase = 0;
+        for (int t = pair; t < total; t += n_pairs) {
+            const int mb = t / n_tiles, nb = t - mb * n_tiles;
+            mbar_wait(&tfull[acc], acc_phase);
+            tc_fence_after();
+            epilogue_tile<P, BN, false, EM>(ep, tmem_base + acc * BN, stg, (long)mb * 2 * BM + (long)rank * BM + q * 32, nb, M, N, q, chalf,
+                                            lane, 1);
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
+            acc ^= 1;
+            if (acc == 0) acc_phase ^= 1;
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();          // the peer's shared memory and barriers stay valid until both CTAs are done
+    if (warp == 2) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(2 * BN));
     }
 }
 
@@ -485,6 +683,49 @@ int sm_count() {
 static int g_lean_epilogue = 1;   // 0: always the generic epilogue (A/B switch)
 extern "C" void css_gemm_tc_lean_epilogue(int on) { g_lean_epilogue = on; }
 
+static int g_two_cta = -1;        // CTA-pair kernel for N % 256 == 0 inference GEMMs; -1: read CSS_B200_GEMM_2CTA (default on)
+extern "C" void css_gemm_tc_two_cta(int on) { g_two_cta = on ? 1 : 0; }
+static bool two_cta_enabled() {
+    if (g_two_cta < 0) {
+        const char* e = getenv("CSS_B200_GEMM_2CTA");
+        g_two_cta = (e && e[0] == '0') ? 0 : 1;
+    }
+    return g_two_cta != 0;
+}
+
+static int epilogue_mode(const TcEpilogue& ep, int P, int N, bool train) {
+    const bool lean_ok = !train && g_lean_epilogue && N % 32 == 0 && ep.clamp_max <= 0.f;
+    if (lean_ok && ep.planes && !ep.c && !ep.residual && ep.alpha == 1.f && ep.n_planes == P && ep.ldp == N) return 1;
+    if (lean_ok && ep.c && !ep.planes && ep.act == 0 && (ep.ldc & 3) == 0 && (!ep.residual || (ep.ldr & 3) == 0) &&
+        ((uintptr_t)ep.c & 15) == 0 && ((uintptr_t)ep.residual & 15) == 0) return 2;
+    return 0;
+}
+
+// CTA-pair launch: 256 x 256 tiles over pairs of SMs (N % 256 == 0, inference epilogues)
+template <int P, int BK>
+static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
+    using C = Cfg2<P, BK>;
+    CUtensorMap ta, tb;
+    int rc;
+    if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
+    if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, C::BN / 2, BK))) return rc;
+    const int em = epilogue_mode(ep, P, N, false);
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
+        attr = true;
+    }
+    const long tiles = ((M + 2 * BM - 1) / (2 * BM)) * (N / C::BN);
+    const int pairs = (int)(tiles < sm_count() / 2 ? tiles : sm_count() / 2);
+    if (em == 1) gemm_tc2_kernel<P, BK, 1><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else if (em == 2) gemm_tc2_kernel<P, BK, 2><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    else gemm_tc2_kernel<P, BK, 0><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    return css_check_launch("gemm_tc (CTA pair)");
+}
+
 template <int P, int BN, int BK>
 static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
     using C = Cfg<P, BN, BK>;
@@ -493,11 +734,7 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
     if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
     if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
     const bool train = ep.mask != nullptr || ep.ksplit > 1;
-    const bool lean_ok = !train && g_lean_epilogue && N % 32 == 0 && ep.clamp_max <= 0.f;
-    int em = 0;
-    if (lean_ok && ep.planes && !ep.c && !ep.residual && ep.alpha == 1.f && ep.n_planes == P && ep.ldp == N) em = 1;
-    else if (lean_ok && ep.c && !ep.planes && ep.act == 0 && (ep.ldc & 3) == 0 && (!ep.residual || (ep.ldr & 3) == 0) &&
-             ((uintptr_t)ep.c & 15) == 0 && ((uintptr_t)ep.residual & 15) == 0) em = 2;
+    const int em = epilogue_mode(ep, P, N, train);
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
@@ -544,6 +781,11 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     }
     const bool wide = N > 128;
     const int v = g_tc_variant;
+    const bool train = ep.mask != nullptr || ep.ksplit > 1;
+    if (!train && P <= 2 && N % 256 == 0 && M > 2 * BM && sm_count() >= 2 && two_cta_enabled()) {
+        if (P == 1) return v == 1 ? launch_cfg2<1, 32>(A, W, M, N, K, ep, st) : launch_cfg2<1, 64>(A, W, M, N, K, ep, st);
+        return v == 1 ? launch_cfg2<2, 32>(A, W, M, N, K, ep, st) : launch_cfg2<2, 64>(A, W, M, N, K, ep, st);
+    }
     if (P == 1) {
         if (!wide) return launch_cfg<1, 128, 64>(A, W, M, N, K, ep, st);
         return v == 1 ? launch_cfg<1, 256, 32>(A, W, M, N, K, ep, st) : launch_cfg<1, 256, 64>(A, W, M, N, K, ep, st);
