@@ -147,17 +147,45 @@ struct Cfg {
     static_assert(STAGES >= 2, "tile does not fit a 2-stage ring");
 };
 
+// The lane's four bias values of each 32-column chunk of a tile (lean epilogues), fetched by the caller BEFORE it waits for
+// the accumulator: a load issued inside the chunk loop put one global-memory latency on the critical path of every chunk.
+template <int BN, int EM>
+__device__ __forceinline__ void epilogue_bias(const TcEpilogue& ep, int nb, int N, int chalf, int lane, float4 (&bbv)[BN / 64]) {
+#pragma unroll
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int col = nb * BN + chalf * (BN / 2) + cc * 32 + (lane & 7) * 4;
+        bbv[cc] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (EM != 0 && ep.bias && col < N)
+            bbv[cc] = make_float4(__ldg(ep.bias + col), __ldg(ep.bias + col + 1), __ldg(ep.bias + col + 2), __ldg(ep.bias + col + 3));
+    }
+}
+
 // Epilogue of one 128 x BN accumulator (TMEM columns tmem_acc ..) by one of the 8 epilogue warps: warp (q, chalf) drains
 // TMEM lanes 32q.. of the column half `chalf`.  row_base: global row of TMEM lane 32q; nb: n-tile index.
 template <int P, int BN, bool TRAIN, int EM>
 __device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tmem_acc, uint32_t stg, long row_base, int nb, long M,
-                                              int N, int q, int chalf, int lane, int ksplit) {
+                                              int N, int q, int chalf, int lane, int ksplit, const float4 (&bbv)[BN / 64]) {
     const int cg = lane & 7, rsub = lane >> 3;
 #pragma unroll 1
     for (int cc = 0; cc < BN / 64; ++cc) {
         const int c0 = chalf * (BN / 2) + cc * 32;
         const int col0 = nb * BN + c0;
         if (col0 >= N && (!ep.planes || col0 >= ep.ldp)) break;          // warp-uniform
+        // EM 2: the residual rows of the chunk are requested before the accumulator is fetched and transposed, so their
+        // global-memory latency runs underneath that work (the residual may alias C: all loads precede the chunk's stores)
+        float4 res4[8];
+        if constexpr (EM == 2) {
+            if (ep.residual) {
+                const float* rp = ep.residual + (row_base + rsub) * ep.ldr + col0 + cg * 4;
+#pragma unroll
+                for (int it = 0; it < 8; ++it)
+                    res4[it] = (row_base + rsub + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr)
+                                                              : make_float4(0.f, 0.f, 0.f, 0.f);
+            } else {
+#pragma unroll
+                for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        }
         uint32_t r[32];
         tc_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + c0, r);
         // phase A: thread = row; 16-byte pieces XOR-swizzled by the row so both phases are conflict-free
@@ -175,8 +203,9 @@ __device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tme
                 const int rr = it * 4 + rsub;
                 xs[it] = lds128(stg + (rr * 8 + (cg ^ (rr & 7))) * 16);
             }
-            float4 bb = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ep.bias) bb = make_float4(__ldg(ep.bias + col), __ldg(ep.bias + col + 1), __ldg(ep.bias + col + 2), __ldg(ep.bias + col + 3));
+            float4 bb = bbv[0];
+#pragma unroll
+            for (int i = 1; i < BN / 64; ++i) if (cc == i) bb = bbv[i];      // static indices: bbv stays in registers
             const long row0 = row_base + rsub;
             if constexpr (EM == 1) {
                 const float floor_v = ep.act == 1 ? 0.f : -INFINITY;
@@ -202,17 +231,6 @@ __device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tme
                     }
                 }
             } else {
-                float4 res4[8];
-                if (ep.residual) {
-                    const float* rp = ep.residual + row0 * ep.ldr + col;
-#pragma unroll
-                    for (int it = 0; it < 8; ++it)
-                        res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr)
-                                                       : make_float4(0.f, 0.f, 0.f, 0.f);
-                } else {
-#pragma unroll
-                    for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-                }
                 float* cp = ep.c + row0 * ep.ldc + col;
 #pragma unroll
                 for (int it = 0; it < 8; ++it) {
@@ -236,7 +254,6 @@ __device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tme
         const bool vec_ok = col + 4 <= N;
         // the residual may alias C (x <- x + ...): fetch all of this chunk's residual rows before any store,
         // otherwise every load would have to wait for the previous store
-        float4 res4[8];
         if (ep.residual) {
 #pragma unroll
             for (int it = 0; it < 8; ++it) {
@@ -432,9 +449,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         for (int t = blockIdx.x; t < total; t += gridDim.x) {
             const int tt = TRAIN ? t % tiles : t;
             const int mb = tt / n_tiles, nb = tt - mb * n_tiles;
+            float4 bbv[BN / 64];
+            epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
-            epilogue_tile<P, BN, TRAIN, EM>(ep, tmem_base + acc * BN, stg, (long)mb * BM + q * 32, nb, M, N, q, chalf, lane, ksplit);
+            epilogue_tile<P, BN, TRAIN, EM>(ep, tmem_base + acc * BN, stg, (long)mb * BM + q * 32, nb, M, N, q, chalf, lane, ksplit, bbv);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tempty[acc]);
@@ -467,7 +486,7 @@ __device__ __forceinline__ uint32_t mapa_rank(uint32_t local, uint32_t rank) {
     return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA load whose completion bytes are counted on a barrier that may live in the peer CTA of the pair
 __device__ __forceinline__ void tma_load_3d_pair(void* dst, const CUtensorMap* map, uint32_t bar_cluster_addr, int c0, int c1, int c2) {
@@ -611,10 +630,12 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = pair; t < total; t += n_pairs) {
             const int mb = t / n_tiles, nb = t - mb * n_tiles;
+            float4 bbv[BN / 64];
+            epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
             mbar_wait(&tfull[acc], acc_phase);
             tc_fence_after();
             epilogue_tile<P, BN, false, EM>(ep, tmem_base + acc * BN, stg, (long)mb * 2 * BM + (long)rank * BM + q * 32, nb, M, N, q, chalf,
-                                            lane, 1);
+                                            lane, 1, bbv);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
