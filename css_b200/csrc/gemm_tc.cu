@@ -509,6 +509,74 @@ __device__ __forceinline__ void tc_mma_pair(uint32_t tmem_d, uint64_t da, uint64
         "}\n" ::"r"(tmem_d), "l"(da), "l"(db), "r"(idesc), "r"(accumulate) : "memory");
 }
 
+// ---- TMA-store epilogue (EM 3): bias (+ReLU) -> P bf16 planes, written by the bulk-copy engine ----
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* map, uint32_t src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(src), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void sts128u(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// One 128 x 256 accumulator -> planes.  The thread keeps the TMEM layout (lane = row, 32 consecutive columns): bias, ReLU and
+// the bf16 split happen in registers, the 64-byte row pieces of each plane go to a 32 x 32 shared tile in the 64-byte
+// swizzle of the output tensor map, and one lane hands the tile to the TMA store.  Compared with the transposing epilogue
+// this leaves 4 STS.128 per plane per chunk on the LSU instead of 8 STS + 8 LDS + 16 STG: the K = 256 GEMMs were bound
+// by the L1/LSU pipe (l1tex 72 % busy, stores backing up), not by the MMA.  Rows past M are clipped by the tensor map.
+template <int P>
+__device__ __forceinline__ void epilogue_tile_tma(const TcEpilogue& ep, const CUtensorMap* tmC, uint32_t tmem_acc, uint32_t stg,
+                                                  long row_base, int nb, int q, int chalf, int lane) {
+    constexpr int BN = 256;
+    const float floor_v = ep.act == 1 ? 0.f : -INFINITY;
+    const uint32_t sw = (uint32_t)((lane >> 1) & 3);           // SWIZZLE_64B: 16-byte piece j of row r sits at j ^ ((r >> 1) & 3)
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c0 = chalf * (BN / 2) + cc * 32;
+        const int col0 = nb * BN + c0;
+        // the chunk's 32 bias values, the same for every lane (L1-resident after the first tile)
+        float4 bb[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            bb[j] = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + col0) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        uint32_t r[32];
+        tc_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + c0, r);
+        // the previous chunk's stores must have read the staging tile before it is overwritten
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {                           // 16-byte piece j: columns 8j .. 8j+7
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float4 b4 = bb[2 * j + (i >> 2)];
+                const float bv = (i & 3) == 0 ? b4.x : ((i & 3) == 1 ? b4.y : ((i & 3) == 2 ? b4.z : b4.w));
+                v[i] = fmaxf(__uint_as_float(r[8 * j + i]) + bv, floor_v);
+            }
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                uint32_t w[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+                    w[i] = *reinterpret_cast<const uint32_t*>(&h);
+                    if (p + 1 < P) {
+                        v[2 * i] -= __uint_as_float(w[i] << 16);
+                        v[2 * i + 1] -= __uint_as_float(w[i] & 0xffff0000u);
+                    }
+                }
+                sts128u(stg + p * 2048 + lane * 64 + (((uint32_t)j ^ sw) << 4), w[0], w[1], w[2], w[3]);
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) tma_store_3d(tmC, stg + p * 2048, col0, (int)row_base, p);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+    }
+}
+
 template <int P, int BK>
 struct Cfg2 {
     static constexpr int BN = 256;
@@ -527,14 +595,15 @@ struct Cfg2 {
 // Each CTA's TMEM holds its own 128 rows of the accumulator and its own epilogue warps drain it.
 template <int P, int BK, int EM>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(384, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
-                TcEpilogue ep) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, long M, int N, int K, TcEpilogue ep) {
     using C = Cfg2<P, BK>;
     constexpr int BN = 256;
     constexpr int STAGES = C::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+    // the epilogue's staging tiles come first (1024-aligned: the TMA store of EM 3 reads them in the 64-byte swizzle)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES + EPI_STAGING);
     uint64_t* full = bars;                    // [STAGES]  used in the leader only (bytes of both CTAs)
     uint64_t* empty = bars + STAGES;          // [STAGES]  one per CTA, released by the pair's commit
     uint64_t* tfull = bars + 2 * STAGES;      // [2]       one per CTA
@@ -626,22 +695,30 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int e = warp - 4;
         const int q = e & 3;
         const int chalf = e >> 2;
-        const uint32_t stg = smem_u32(smem + STAGES * C::STAGE_BYTES + 256) + e * 4096;
+        const uint32_t stg = smem_u32(smem + STAGES * C::STAGE_BYTES) + e * 4096;
+        if (EM == 3 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmC)) : "memory");
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = pair; t < total; t += n_pairs) {
             const int mb = t / n_tiles, nb = t - mb * n_tiles;
-            float4 bbv[BN / 64];
-            epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
-            mbar_wait(&tfull[acc], acc_phase);
-            tc_fence_after();
-            epilogue_tile<P, BN, false, EM>(ep, tmem_base + acc * BN, stg, (long)mb * 2 * BM + (long)rank * BM + q * 32, nb, M, N, q, chalf,
-                                            lane, 1, bbv);
+            const long row_base = (long)mb * 2 * BM + (long)rank * BM + q * 32;
+            if constexpr (EM == 3) {
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                epilogue_tile_tma<P>(ep, &tmC, tmem_base + acc * BN, stg, row_base, nb, q, chalf, lane);
+            } else {
+                float4 bbv[BN / 64];
+                epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                epilogue_tile<P, BN, false, EM>(ep, tmem_base + acc * BN, stg, row_base, nb, M, N, q, chalf, lane, 1, bbv);
+            }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
             acc ^= 1;
             if (acc == 0) acc_phase ^= 1;
         }
+        if (EM == 3 && lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // stores done before exit
     }
     tc_fence_before();
     cluster_sync_all();          // the peer's shared memory and barriers stay valid until both CTAs are done
@@ -714,6 +791,9 @@ static bool two_cta_enabled() {
     return g_two_cta != 0;
 }
 
+static int g_tma_epilogue = 1;    // planes-only epilogue of the CTA-pair kernel through the TMA store (A/B switch)
+extern "C" void css_gemm_tc_tma_epilogue(int on) { g_tma_epilogue = on; }
+
 static int epilogue_mode(const TcEpilogue& ep, int P, int N, bool train) {
     const bool lean_ok = !train && g_lean_epilogue && N % 32 == 0 && ep.clamp_max <= 0.f;
     if (lean_ok && ep.planes && !ep.c && !ep.residual && ep.alpha == 1.f && ep.n_planes == P && ep.ldp == N) return 1;
@@ -730,10 +810,18 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
     int rc;
     if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
     if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, C::BN / 2, BK))) return rc;
-    const int em = epilogue_mode(ep, P, N, false);
+    int em = epilogue_mode(ep, P, N, false);
+    CUtensorMap tc = ta;
+    static const bool tma_env = !(getenv("CSS_B200_GEMM_TMA_EPI") && getenv("CSS_B200_GEMM_TMA_EPI")[0] == '0');
+    if (em == 1 && g_tma_epilogue && tma_env && ((uintptr_t)ep.bias & 15) == 0 && ((uintptr_t)ep.planes & 15) == 0) {
+        // planes-only output: 32 x 32 tiles of each plane leave through the TMA store (EM 3)
+        if ((rc = make_map(&tc, ep.planes, M, ep.ldp, ep.ldp, ep.plane_stride, P, 32, 32))) return rc;
+        em = 3;
+    }
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
@@ -741,9 +829,10 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
     }
     const long tiles = ((M + 2 * BM - 1) / (2 * BM)) * (N / C::BN);
     const int pairs = (int)(tiles < sm_count() / 2 ? tiles : sm_count() / 2);
-    if (em == 1) gemm_tc2_kernel<P, BK, 1><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
-    else if (em == 2) gemm_tc2_kernel<P, BK, 2><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
-    else gemm_tc2_kernel<P, BK, 0><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+    if (em == 3) gemm_tc2_kernel<P, BK, 3><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
+    else if (em == 1) gemm_tc2_kernel<P, BK, 1><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
+    else if (em == 2) gemm_tc2_kernel<P, BK, 2><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
+    else gemm_tc2_kernel<P, BK, 0><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
     return css_check_launch("gemm_tc (CTA pair)");
 }
 
