@@ -241,17 +241,34 @@ mvdr_apply_kernel(const float2* __restrict__ spec, const float2* __restrict__ ed
     float e_y = 0.f;
     float2* yrow = Y + ((b * 2 + mk) * (long)T) * CSS_KP + k;
     if (act) {
-        float2 w[MV_M];
+        // y = sum_d conj(w_d) x_d = (P.x + Q.y, P.y - Q.x) with P = sum_d wr_d * x_d, Q = sum_d wi_d * x_d: two packed fp32
+        // FMAs (FFMA2) per channel; the next frame's seven channels are requested before the current frame is consumed
+        float2 wx[MV_M], wy[MV_M];
 #pragma unroll
-        for (int i = 0; i < MV_M; ++i) w[i] = wv[((b * 2 + mk) * MV_M + i) * (long)CSS_KP + k];
+        for (int i = 0; i < MV_M; ++i) {
+            const float2 w = wv[((b * 2 + mk) * MV_M + i) * (long)CSS_KP + k];
+            wx[i] = make_float2(w.x, w.x);
+            wy[i] = make_float2(w.y, w.y);
+        }
+        float2 xn[MV_M];
+#pragma unroll
+        for (int d = 0; d < MV_M; ++d) xn[d] = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, 0, k);
+#pragma unroll 2
         for (int t = 0; t < T; ++t) {
-            float yr = 0.f, yi = 0.f;
+            float2 x[MV_M];
+#pragma unroll
+            for (int d = 0; d < MV_M; ++d) x[d] = xn[d];
+            if (t + 1 < T) {
+#pragma unroll
+                for (int d = 0; d < MV_M; ++d) xn[d] = spec[((long)d * frames + b * hop_frames + t) * CSS_KP + k];
+            }
+            float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
 #pragma unroll
             for (int d = 0; d < MV_M; ++d) {
-                const float2 x = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k);
-                yr += w[d].x * x.x + w[d].y * x.y;
-                yi += w[d].x * x.y - w[d].y * x.x;
+                P = __ffma2_rn(wx[d], x[d], P);
+                Q = __ffma2_rn(wy[d], x[d], Q);
             }
+            const float yr = P.x + Q.y, yi = P.y - Q.x;
             yrow[(long)t * CSS_KP] = make_float2(yr, yi);
             e_y += yr * yr + yi * yi;
         }
