@@ -129,14 +129,23 @@ static int tc_gemm(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     return rc;
 }
 
-// ln_done: yP already holds the planes of LN(x) (written by the previous block's output norm)
+// ln_done: yP already holds the planes of LN(x) (written by the previous block's output norm).
+// next_g/next_b: LayerNorm that follows this FFN (the attention-in norm after the first FFN of a block); when the GEMM can
+// take it in its epilogue, yP leaves holding the planes of LN(x_new) and *fused is set -- the caller then skips that launch.
 static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& w2, float* x, const PlaneMat& yP, const PlaneMat& hP,
-                  int P, long M, int d, int dffn, bool ln_done, cudaStream_t st) {
+                  int P, long M, int d, int dffn, bool ln_done, const float* next_g, const float* next_b, bool* fused, cudaStream_t st) {
     int rc = ln_done ? 0 : layernorm_planes_launch(x, w.ln_g, w.ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st);
     if (rc) return rc;
     GemmEpilogue e1 = {w.b1, 1, 1.f, nullptr, 0, 0.f};
     if ((rc = tc_gemm(yP, w1, P, M, dffn, d, e1, nullptr, 0, &hP, st))) return rc;
     GemmEpilogue e2 = {w.b2, 0, 0.5f, x, d, 0.f};
+    const bool fuse = next_g && gemm_tc_ln_fusable(M, d, P);
+    if (fused) *fused = fuse;
+    if (fuse) {
+        e2.ln_g = next_g;
+        e2.ln_b = next_b;
+        return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, &yP, st);
+    }
     return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, nullptr, st);
 }
 
@@ -166,8 +175,10 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
     for (int l = 0; l < c.num_blocks; ++l) {
         const css_conformer_block& b = m->blk[l];
         const BlockPlanes& q = m->bp[l];
-        if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, l > 0, st))) return rc;
-        if ((rc = layernorm_planes_launch(x, b.att_ln_g, b.att_ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st))) return rc;
+        bool att_ln_done = false;
+        if ((rc = ffn_tc(b.ff_in, q.ff_in_w1, q.ff_in_w2, x, yP, hP, P, M, d, dffn, l > 0, b.att_ln_g, b.att_ln_b, &att_ln_done, st))) return rc;
+        if (!att_ln_done &&
+            (rc = layernorm_planes_launch(x, b.att_ln_g, b.att_ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st))) return rc;
         GemmEpilogue eq = {b.bqkv, 0, 1.f, nullptr, 0, 0.f};
         if (attention_tc_supported(T, d / c.heads)) {
             // Q, K, V leave the GEMM epilogue as bf16 planes (in the `h` region) and feed the tensor-core attention directly
@@ -186,7 +197,7 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
                                b.bn_scale, b.bn_shift, b.pw2_w, b.pw2_b, 33};
         if ((rc = conv_module_launch(x, a, N, T, d, cp, st))) return rc;
         { float* t = x; x = a; a = t; }
-        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, false, st))) return rc;
+        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, false, nullptr, nullptr, nullptr, st))) return rc;
         // block output LN: fp32 for the residual stream, and in the same pass the planes the next GEMM reads -- the next
         // block's FFN-in norm of that output, or the output itself for the head GEMM after the last block
         const bool last = l == c.num_blocks - 1;

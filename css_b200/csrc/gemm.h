@@ -13,6 +13,10 @@ struct GemmEpilogue {
     const void* relu_mask = nullptr;   // bf16 plane 0 of the forward activation: result zeroed where it is <= 0
     int ldmask = 0;
     int accumulate = 0;                // 1: C += result (split-K over the SMs, fp32 atomics); bias/act/residual/planes unsupported
+    // fused LayerNorm (tcgen05 CTA-pair path, N == 256): C gets the GEMM result, `out` the split planes of
+    // LayerNorm(C row; ln_g, ln_b, eps 1e-5) -- see gemm_tc_ln_fusable()
+    const float* ln_g = nullptr;
+    const float* ln_b = nullptr;
 };
 
 int gemm_simt_launch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,
@@ -32,3 +36,5 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
                    const PlaneMat* out, cudaStream_t st);
 int split_planes_launch(const float* x, long rows, int cols, int ld, const PlaneMat& out, cudaStream_t st);
 int sm_count();
+// true when gemm_tc_planes can apply GemmEpilogue::ln_g / ln_b in its epilogue for this shape (otherwise run LayerNorm separately)
+bool gemm_tc_ln_fusable(long M, int N, int P);

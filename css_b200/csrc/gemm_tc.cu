@@ -126,6 +126,9 @@ struct TcEpilogue {
     const __nv_bfloat16* mask;   // forward activation (plane 0): output zeroed where mask <= 0 (ReLU backward)
     int ldmask;
     int ksplit;                  // > 1: the K range is split over `ksplit` work items that accumulate into c atomically
+    // EM 4: planes = split planes of LayerNorm(c row; ln_g, ln_b)
+    const float* ln_g;
+    const float* ln_b;
 };
 
 template <int P> struct Terms;
@@ -577,6 +580,133 @@ __device__ __forceinline__ void epilogue_tile_tma(const TcEpilogue& ep, const CU
     }
 }
 
+// ---- EM 4: (acc + bias) * alpha + residual -> fp32 C, and the split planes of LayerNorm(C row) -> planes (N == 256) ----
+// Pass 1 is the EM 2 epilogue plus per-row sums; the two warps that share a TMEM lane quadrant (column halves) swap their
+// partial sums through shared memory across a 64-thread named barrier.  Pass 2 runs after the accumulator has been handed
+// back to the MMA warp: every lane re-reads the C values it stored itself (L2), normalises and stores the planes.
+struct LnRowStats { float mean[8], rstd[8]; };
+
+template <int P>
+__device__ __forceinline__ void epilogue_ln_pass1(const TcEpilogue& ep, uint32_t tmem_acc, uint32_t stg, uint32_t stg_partner,
+                                                  long row_base, long M, int q, int chalf, int lane,
+                                                  const float4 (&bbv)[4], LnRowStats& st) {
+    constexpr int BN = 256;
+    const int cg = lane & 7, rsub = lane >> 3;
+    float s1[8], s2[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) s1[it] = s2[it] = 0.f;
+    const long row0 = row_base + rsub;
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c0 = chalf * (BN / 2) + cc * 32;
+        const int col = c0 + cg * 4;
+        float4 res4[8];
+        if (ep.residual) {
+            const float* rp = ep.residual + row0 * ep.ldr + col;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        uint32_t r[32];
+        tc_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + c0, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            sts128(stg + (lane * 8 + (j ^ (lane & 7))) * 16, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        float4 xs[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            xs[it] = lds128(stg + (rr * 8 + (cg ^ (rr & 7))) * 16);
+        }
+        float4 bb = bbv[0];
+#pragma unroll
+        for (int i = 1; i < 4; ++i) if (cc == i) bb = bbv[i];
+        float* cp = ep.c + row0 * ep.ldc + col;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            float4 o;
+            o.x = fmaf(xs[it].x + bb.x, ep.alpha, res4[it].x);
+            o.y = fmaf(xs[it].y + bb.y, ep.alpha, res4[it].y);
+            o.z = fmaf(xs[it].z + bb.z, ep.alpha, res4[it].z);
+            o.w = fmaf(xs[it].w + bb.w, ep.alpha, res4[it].w);
+            s1[it] += (o.x + o.y) + (o.z + o.w);
+            s2[it] += (o.x * o.x + o.y * o.y) + (o.z * o.z + o.w * o.w);
+            if (row0 + it * 4 < M) *reinterpret_cast<float4*>(cp + (long)(it * 4) * ep.ldc) = o;
+        }
+        __syncwarp();
+    }
+    // row sums over this warp's 128 columns: the 8 lanes of a row group hold the pieces
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            s1[it] += __shfl_xor_sync(0xffffffffu, s1[it], o);
+            s2[it] += __shfl_xor_sync(0xffffffffu, s2[it], o);
+        }
+    }
+    if (cg == 0) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stg + (it * 4 + rsub) * 8), "f"(s1[it]), "f"(s2[it]) : "memory");
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        float a, b;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a), "=f"(b) : "r"(stg_partner + (it * 4 + rsub) * 8) : "memory");
+        const float mean = (s1[it] + a) * (1.f / BN);
+        const float var = fmaxf((s2[it] + b) * (1.f / BN) - mean * mean, 0.f);
+        st.mean[it] = mean;
+        st.rstd[it] = rsqrtf(var + 1e-5f);
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");      // both warps have read before the staging tiles are reused
+}
+
+template <int P>
+__device__ __forceinline__ void epilogue_ln_pass2(const TcEpilogue& ep, long row_base, long M, int chalf, int lane, const LnRowStats& st) {
+    constexpr int BN = 256;
+    const int cg = lane & 7, rsub = lane >> 3;
+    const long row0 = row_base + rsub;
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int col = chalf * (BN / 2) + cc * 32 + cg * 4;
+        const float4 g4 = make_float4(__ldg(ep.ln_g + col), __ldg(ep.ln_g + col + 1), __ldg(ep.ln_g + col + 2), __ldg(ep.ln_g + col + 3));
+        const float4 b4 = make_float4(__ldg(ep.ln_b + col), __ldg(ep.ln_b + col + 1), __ldg(ep.ln_b + col + 2), __ldg(ep.ln_b + col + 3));
+        const float* cp = ep.c + row0 * ep.ldc + col;
+        float4 x[8];
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+            x[it] = (row0 + it * 4 < M) ? __ldcg(reinterpret_cast<const float4*>(cp + (long)(it * 4) * ep.ldc)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        __nv_bfloat16* pp = ep.planes + row0 * ep.ldp + col;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            if (row0 + it * 4 >= M) continue;
+            const float m = st.mean[it], rs = st.rstd[it];
+            float v0 = (x[it].x - m) * rs * g4.x + b4.x, v1 = (x[it].y - m) * rs * g4.y + b4.y;
+            float v2 = (x[it].z - m) * rs * g4.z + b4.z, v3 = (x[it].w - m) * rs * g4.w + b4.w;
+            __nv_bfloat16* dst = pp + (long)(it * 4) * ep.ldp;
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const __nv_bfloat162 h01 = __floats2bfloat162_rn(v0, v1);
+                const __nv_bfloat162 h23 = __floats2bfloat162_rn(v2, v3);
+                uint2 w;
+                w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                *reinterpret_cast<uint2*>(dst + p * ep.plane_stride) = w;
+                if (p + 1 < P) {
+                    v0 -= __uint_as_float(w.x << 16); v1 -= __uint_as_float(w.x & 0xffff0000u);
+                    v2 -= __uint_as_float(w.y << 16); v3 -= __uint_as_float(w.y & 0xffff0000u);
+                }
+            }
+        }
+    }
+}
+
 template <int P, int BK>
 struct Cfg2 {
     static constexpr int BN = 256;
@@ -695,7 +825,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const int e = warp - 4;
         const int q = e & 3;
         const int chalf = e >> 2;
-        const uint32_t stg = smem_u32(smem + STAGES * C::STAGE_BYTES) + e * 4096;
+        const uint32_t stg0 = smem_u32(smem + STAGES * C::STAGE_BYTES);
+        const uint32_t stg = stg0 + e * 4096, stg_partner = stg0 + (e ^ 4) * 4096;    // partner: same rows, other column half
         if (EM == 3 && lane == 0) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmC)) : "memory");
         int acc = 0; uint32_t acc_phase = 0;
         for (int t = pair; t < total; t += n_pairs) {
@@ -705,6 +836,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
                 epilogue_tile_tma<P>(ep, &tmC, tmem_base + acc * BN, stg, row_base, nb, q, chalf, lane);
+            } else if constexpr (EM == 4) {
+                float4 bbv[BN / 64];
+                epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+                LnRowStats st;
+                epilogue_ln_pass1<P>(ep, tmem_base + acc * BN, stg, stg_partner, row_base, M, q, chalf, lane, bbv, st);
+                // the accumulator goes back to the MMA warp before the normalisation pass
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
+                epilogue_ln_pass2<P>(ep, row_base, M, chalf, lane, st);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+                continue;
             } else {
                 float4 bbv[BN / 64];
                 epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
@@ -818,10 +964,17 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
         if ((rc = make_map(&tc, ep.planes, M, ep.ldp, ep.ldp, ep.plane_stride, P, 32, 32))) return rc;
         em = 3;
     }
+    if (ep.ln_g) {
+        CSS_REQUIRE(N == C::BN && ep.c && ep.planes && ep.ln_b && ep.act == 0 && ep.clamp_max <= 0.f && ep.n_planes == P && ep.ldp == N &&
+                    (ep.ldc & 3) == 0 && (!ep.residual || (ep.ldr & 3) == 0) && ((uintptr_t)ep.c & 15) == 0 && ((uintptr_t)ep.residual & 15) == 0,
+                    "gemm_tc: fused LayerNorm needs N == 256, fp32 + %d-plane outputs, no activation", P);
+        em = 4;
+    }
     static bool attr = false;
     if (!attr) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
@@ -829,7 +982,8 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
     }
     const long tiles = ((M + 2 * BM - 1) / (2 * BM)) * (N / C::BN);
     const int pairs = (int)(tiles < sm_count() / 2 ? tiles : sm_count() / 2);
-    if (em == 3) gemm_tc2_kernel<P, BK, 3><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
+    if (em == 4) gemm_tc2_kernel<P, BK, 4><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
+    else if (em == 3) gemm_tc2_kernel<P, BK, 3><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
     else if (em == 1) gemm_tc2_kernel<P, BK, 1><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
     else if (em == 2) gemm_tc2_kernel<P, BK, 2><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
     else gemm_tc2_kernel<P, BK, 0><<<2 * pairs, 384, C::SMEM, st>>>(ta, tb, tc, M, N, K, ep);
@@ -863,6 +1017,13 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
     return css_check_launch("gemm_tc");
 }
 
+static int g_ln_fusion = 1;       // LayerNorm folded into the FFN-out GEMM epilogue (A/B switch; CSS_B200_GEMM_LN=0 disables)
+extern "C" void css_gemm_tc_ln_fusion(int on) { g_ln_fusion = on; }
+bool gemm_tc_ln_fusable(long M, int N, int P) {
+    static const bool env = !(getenv("CSS_B200_GEMM_LN") && getenv("CSS_B200_GEMM_LN")[0] == '0');
+    return g_ln_fusion && env && N == 256 && P <= 2 && M > 2 * BM && sm_count() >= 2 && two_cta_enabled();
+}
+
 static int g_tc_variant = 1;   // 0: BK=64 / 128B swizzle, 1: BK=32 / 64B swizzle (deeper ring)
 extern "C" void css_gemm_tc_variant(int v) { g_tc_variant = v; }
 
@@ -892,6 +1053,9 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     const bool wide = N > 128;
     const int v = g_tc_variant;
     const bool train = ep.mask != nullptr || ep.ksplit > 1;
+    ep.ln_g = e.ln_g;
+    ep.ln_b = e.ln_b;
+    CSS_REQUIRE(!e.ln_g || (!train && gemm_tc_ln_fusable(M, N, P)), "gemm_tc: fused LayerNorm unsupported for M=%ld N=%d P=%d", M, N, P);
     if (!train && P <= 2 && N % 256 == 0 && M > 2 * BM && sm_count() >= 2 && two_cta_enabled()) {
         if (P == 1) return v == 1 ? launch_cfg2<1, 32>(A, W, M, N, K, ep, st) : launch_cfg2<1, 64>(A, W, M, N, K, ep, st);
         return v == 1 ? launch_cfg2<2, 32>(A, W, M, N, K, ep, st) : launch_cfg2<2, 64>(A, W, M, N, K, ep, st);

@@ -245,6 +245,39 @@ def test_conformer_many_sequences_match_small_batches(cuda):
         assert torch.equal(whole[c], torch.cat([p[c] for p in parts], 0))
 
 
+@pytest.mark.parametrize("N,T", [(2, 150), (5, 203)])
+def test_gemm_layernorm_epilogue_matches_separate_launch(cuda, N, T):
+    """tcgen05 mode, M > 256: the attention-in LayerNorm is taken by the FFN-out GEMM's epilogue (row statistics across the
+    two column-half warps).  Same masks as with the separate LayerNorm launch to 2e-5 (sum/sum-of-squares vs two-pass
+    variance), and the oracle bound holds either way; M is not a multiple of the 256-row tile in either case."""
+    nv = _nv()
+    model = golden_conformer(num_blocks=2)
+    sd = cpu_state_dict(model)
+    g = torch.Generator().manual_seed(N * 31 + T)
+    f = torch.randn(N, T, 1799, generator=g) * 2 + 0.3
+    model = model.to(cuda)
+    old = nv.get_gemm_mode()
+    nv.set_gemm_mode(1)
+    try:
+        nv.lib().css_gemm_tc_ln_fusion(1)
+        model(f.to(cuda))                          # first call also splits the weights into planes
+        nv.launch_count(reset=True)
+        _, fused = model(f.to(cuda))
+        n_fused = nv.launch_count(reset=True)
+        nv.lib().css_gemm_tc_ln_fusion(0)
+        _, plain = model(f.to(cuda))
+        n_plain = nv.launch_count(reset=True)
+    finally:
+        nv.lib().css_gemm_tc_ln_fusion(1)
+        nv.set_gemm_mode(old)
+    assert n_plain - n_fused == 2              # one LayerNorm launch fewer per block
+    with torch.no_grad():
+        _, m_o = O.model_forward(f, sd)
+    for a, b, c in zip(fused, plain, m_o):
+        assert rel_inf(a, b.cpu()) < 2e-5
+        assert rel_inf(a, c) < 1e-4
+
+
 def test_conformer_bf16_mode_bound(cuda):
     """Plain bf16 tensor-core mode: stated looser bound (masks abs <= 5e-2 on a 2-block net)."""
     nv = _nv()
