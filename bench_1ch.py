@@ -146,6 +146,20 @@ def main():
     launches = nv.launch_count()
     clocks = sampler.stop() if rank == 0 else None
     ms_e2e = min(timed(step_e2e, args.steps), timed(step_e2e, args.steps))
+    # per-category kernel time (CUDA events around every launch on the launching stream) in a separate, untimed pass
+    import ctypes
+    lib = nv.lib()
+    ncat = 11
+    ms_c, work_c, cnt_c = (ctypes.c_double * ncat)(), (ctypes.c_double * ncat)(), (ctypes.c_long * ncat)()
+    lib.css_profile_enable(1)
+    step_resident()
+    torch.cuda.synchronize()
+    nv.check(lib.css_profile_collect(ms_c, work_c, cnt_c, ncat), "css_profile_collect")
+    lib.css_profile_enable(0)
+    names = ("gemm", "attention", "conv_module", "layernorm", "lstm_step", "stft", "features_mvn", "doa_merge", "stitch", "mvdr", "istft_peak")
+    kernels = {names[i]: {"ms_per_step": round(ms_c[i], 3), "launches": int(cnt_c[i]),
+                          "achieved": round(work_c[i] / (ms_c[i] * 1e-3) / (1e12 if i in (0, 1, 4) else 1e9), 1),
+                          "unit": "TFLOP/s" if i in (0, 1, 4) else "GB/s"} for i in range(ncat) if cnt_c[i] and ms_c[i] > 0}
     if rank == 0:
         audio = world * n_rec * seconds * args.steps
         name = {"conformer": "configs[1]: 1-ch Conformer CSS inference", "blstm": "configs[0]: 1-ch BLSTM 1024x3 mask estimator (conf/config_1ch.yaml) chunked CSS inference"}[wl]
@@ -161,7 +175,7 @@ def main():
                 "clocks": clocks,
                 "e2e": {"value": audio / (ms_e2e * 1e-3), "unit": "xRT", "ms_per_step": ms_e2e / args.steps,
                         "h2d_bytes_per_step": n_rec * T * 4, "d2h_bytes_per_step": n_rec * probe.numel() * 4},
-                "gpu_launches": int(launches)}
+                "gpu_launches": int(launches), "kernels": kernels}
         if world == 1 and not args.no_cpu_baseline:
             xrt, cores = cpu_port(wl, args.blocks, cpu_seconds)
             line["cpu_baseline"] = {"value": xrt, "unit": "xRT", "cores": cores, "kind": "port",

@@ -3,10 +3,14 @@
 // recurrence steps each run ONE kernel for both directions: a (chunks x H) . (H x 4H) product
 // tiled 64 x (32 hidden units x 4 gates) with the LSTM cell fused in the epilogue, so the gates
 // never touch HBM.  Chunks are the batch axis that keeps the step kernel wide.
+// Two step kernels: fp32 FMAs (GEMM mode 0) and, in the tensor-core modes, mma.sync bf16 with the three-term split
+// (h and W_hh kept as bf16 hi/lo planes; the epilogue writes the planes of h_t for the next step).
 #include "common.cuh"
+#include <cuda_bf16.h>
 #include "conformer.h"
 #include "gemm.h"
 #include "../../include/css_b200.h"
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -112,10 +116,217 @@ lstm_step_kernel(const float* __restrict__ xproj, const float* __restrict__ w_hh
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Tensor-core step (GEMM modes 1, 2): gates = h_{t-1} . W_hh^T as mma.sync.m16n8k16 bf16 over hi/lo planes,
+// hi.hi + hi.lo + lo.hi in fp32 accumulators (the same split as the tcgen05 GEMMs and the attention kernel).
+// Warp tile: 32 sequences x (8 hidden units x 4 gates), so a thread's accumulators hold i, f, g, o of the same
+// (sequence, unit) and the cell update needs no exchange.  CTA = WM x WN warps; K = H streamed in 64-wide chunks
+// through a 3-stage cp.async ring.  whh planes: [dir][plane][4H][H] bf16; h planes: [dir][plane][N][H] bf16.
+// ---------------------------------------------------------------------------------------------
+namespace {
+constexpr int LM_BK = 64;
+constexpr int LM_ROWB = 144;          // bytes per smem row: 64 bf16 + 16 B pad (conflict-free ldmatrix)
+constexpr int LM_STAGES = 3;
+
+__device__ __forceinline__ void lm_mma(float* c, const uint32_t* a, uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void lm_ldsm4(uint32_t addr, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void lm_cp16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ float lm_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
+
+template <int WM, int WN>
+struct LmCfg {
+    static constexpr int BM = 32 * WM;            // sequences per CTA
+    static constexpr int JB = 8 * WN;             // hidden units per CTA
+    static constexpr int BROWS = 4 * JB;          // W_hh rows per CTA: [gate][unit]
+    static constexpr int A_PLANE = BM * LM_ROWB;
+    static constexpr int B_PLANE = BROWS * LM_ROWB;
+    static constexpr int STAGE = 2 * A_PLANE + 2 * B_PLANE;
+    static constexpr int SMEM = LM_STAGES * STAGE;
+    static constexpr int THREADS = 32 * WM * WN;
+};
+
+template <int WM, int WN>
+__global__ void __launch_bounds__(32 * WM * WN)
+lstm_step_mma_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, const __nv_bfloat16* __restrict__ h_prev,
+                     __nv_bfloat16* __restrict__ h_next, float* __restrict__ c_state, float* __restrict__ out, long N, int T, int H, int s) {
+    using C = LmCfg<WM, WN>;
+    extern __shared__ __align__(128) uint8_t lm_smem[];
+    const int dir = blockIdx.z;
+    const int t = dir ? (T - 1 - s) : s;
+    const long n0 = (long)blockIdx.x * C::BM;
+    const int j0 = blockIdx.y * C::JB;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int wm = warp / WN, wn = warp - wm * WN;
+    const long plane_h = N * (long)H, plane_w = 4L * H * H;
+    const __nv_bfloat16* hp = h_prev + (long)dir * 2 * plane_h;
+    const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(lm_smem);
+
+    auto load_stage = [&](int kc, int stage) {
+        const uint32_t sa = sbase + stage * C::STAGE;
+        const int k0 = kc * LM_BK;
+        // A: 2 planes x BM rows x 8 chunks of 16 B
+        for (int i = tid; i < 2 * C::BM * 8; i += C::THREADS) {
+            const int ch = i & 7, r = (i >> 3) % C::BM, p = i / (8 * C::BM);
+            long n = n0 + r;
+            if (n >= N) n = N - 1;                                     // rows past N are computed and dropped
+            lm_cp16(sa + p * C::A_PLANE + r * LM_ROWB + ch * 16, hp + p * plane_h + n * H + k0 + ch * 8);
+        }
+        const uint32_t sb = sa + 2 * C::A_PLANE;
+        for (int i = tid; i < 2 * C::BROWS * 8; i += C::THREADS) {
+            const int ch = i & 7, r = (i >> 3) % C::BROWS, p = i / (8 * C::BROWS);
+            const int g = r / C::JB, u = r - g * C::JB;
+            lm_cp16(sb + p * C::B_PLANE + r * LM_ROWB + ch * 16, wp + p * plane_w + ((long)g * H + j0 + u) * H + k0 + ch * 8);
+        }
+    };
+
+    float acc[2][4][4];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[m][g][i] = 0.f;
+
+    const int nk = H / LM_BK;
+    load_stage(0, 0);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    if (nk > 1) load_stage(1, 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    // ldmatrix lane addressing.  A (16 x 16, row-major): matrices (r0-7,k0-7), (r8-15,k0-7), (r0-7,k8-15), (r8-15,k8-15)
+    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_k = (lane >> 4) * 8;
+    // B: per gate one x4 = hi(k0-7), hi(k8-15), lo(k0-7), lo(k8-15) of the warp's 8 units
+    const int b_row = lane & 7, b_plane = lane >> 4, b_k = ((lane >> 3) & 1) * 8;
+    for (int kc = 0; kc < nk; ++kc) {
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncthreads();
+        if (kc + 2 < nk) load_stage(kc + 2, (kc + 2) % LM_STAGES);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const uint32_t sa = sbase + (kc % LM_STAGES) * C::STAGE;
+        const uint32_t sb = sa + 2 * C::A_PLANE;
+#pragma unroll
+        for (int kk = 0; kk < LM_BK / 16; ++kk) {
+            uint32_t ah[2][4], al[2][4];
+#pragma unroll
+            for (int m = 0; m < 2; ++m) {
+                const uint32_t addr = sa + (wm * 32 + m * 16 + a_row) * LM_ROWB + (kk * 16 + a_k) * 2;
+                lm_ldsm4(addr, ah[m]);
+                lm_ldsm4(addr + C::A_PLANE, al[m]);
+            }
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                uint32_t b[4];      // hi b0, hi b1, lo b0, lo b1
+                lm_ldsm4(sb + b_plane * C::B_PLANE + (g * C::JB + wn * 8 + b_row) * LM_ROWB + (kk * 16 + b_k) * 2, b);
+#pragma unroll
+                for (int m = 0; m < 2; ++m) {
+                    lm_mma(acc[m][g], al[m], b[0], b[1]);
+                    lm_mma(acc[m][g], ah[m], b[2], b[3]);
+                    lm_mma(acc[m][g], ah[m], b[0], b[1]);
+                }
+            }
+        }
+    }
+    // fused cell update (gate order i, f, g, o as torch.nn.LSTM): thread holds rows gid, gid+8 and units 2q, 2q+1 of each m-tile
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + wn * 8 + 2 * q;
+    __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const long n = n0 + wm * 32 + m * 16 + gid + half * 8;
+            if (n >= N) continue;
+            const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
+            const float2 xi = *reinterpret_cast<const float2*>(xp), xf = *reinterpret_cast<const float2*>(xp + H);
+            const float2 xg = *reinterpret_cast<const float2*>(xp + 2 * H), xo = *reinterpret_cast<const float2*>(xp + 3 * H);
+            const long si = ((long)dir * N + n) * H + j;
+            const float2 cp = *reinterpret_cast<const float2*>(c_state + si);
+            float2 c, h;
+            c.x = lm_sigmoid(acc[m][1][2 * half] + xf.x) * cp.x + lm_sigmoid(acc[m][0][2 * half] + xi.x) * tanhf(acc[m][2][2 * half] + xg.x);
+            c.y = lm_sigmoid(acc[m][1][2 * half + 1] + xf.y) * cp.y + lm_sigmoid(acc[m][0][2 * half + 1] + xi.y) * tanhf(acc[m][2][2 * half + 1] + xg.y);
+            h.x = lm_sigmoid(acc[m][3][2 * half] + xo.x) * tanhf(c.x);
+            h.y = lm_sigmoid(acc[m][3][2 * half + 1] + xo.y) * tanhf(c.y);
+            *reinterpret_cast<float2*>(c_state + si) = c;
+            *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
+            *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
+            *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+        }
+    }
+}
+
+template <int WM, int WN>
+int lstm_step_mma_launch(const float* xp, const __nv_bfloat16* whh, const __nv_bfloat16* hp, __nv_bfloat16* hn, float* cs, float* y,
+                         long N, int T, int H, int s, cudaStream_t st) {
+    using C = LmCfg<WM, WN>;
+    static bool attr = false;
+    if (!attr) {
+        cudaError_t e = cudaFuncSetAttribute(lstm_step_mma_kernel<WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        CSS_REQUIRE(e == cudaSuccess, "lstm_step_mma: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
+        attr = true;
+    }
+    dim3 grid((unsigned)((N + C::BM - 1) / C::BM), H / C::JB, 2);
+    lstm_step_mma_kernel<WM, WN><<<grid, C::THREADS, C::SMEM, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
+    return 0;
+}
+}  // namespace
+
 struct BlstmModel {
     css_blstm_desc d;
     std::vector<css_blstm_layer> lay;
+    void* whh_planes = nullptr;      // per layer: [dir][plane][4H][H] bf16 (built on the first tensor-core forward)
+    PlaneMat embed_w{}, head_w{};    // Linear weights as bf16 hi/lo planes for the tcgen05 GEMM (same allocation)
+    std::vector<PlaneMat> w_ih;
 };
+extern "C" int css_get_gemm_mode(void);
+
+static size_t whh_layer_elems(const css_blstm_desc& d) { const size_t H = d.hdim / 2; return 2 * 2 * 4 * H * H; }
+
+static inline int embed_kp(const css_blstm_desc& d) { return (d.ldin + 63) / 64 * 64; }    // K of the embedding GEMM (zero padded)
+
+static int build_whh_planes(BlstmModel* m, cudaStream_t st) {
+    if (m->whh_planes) return 0;
+    const css_blstm_desc& c = m->d;
+    const size_t per = whh_layer_elems(c);
+    const int H = c.hdim / 2;
+    const size_t h = c.hdim, nh = (size_t)c.num_bins * c.num_out, kpe = embed_kp(c);
+    auto bytes = [](size_t rows, size_t k) { return (2 * rows * k * 2 + 255) & ~(size_t)255; };
+    const size_t whh_bytes = (per * c.num_layers * 2 + 255) & ~(size_t)255;
+    const size_t total = whh_bytes + bytes(h, kpe) + bytes(nh, h) + c.num_layers * bytes(4 * h, h);
+    cudaError_t e = cudaMalloc(&m->whh_planes, total);
+    CSS_REQUIRE(e == cudaSuccess, "blstm: cannot allocate %zu B for the bf16 weight planes: %s", total, cudaGetErrorString(e));
+    int rc = 0;
+    char* wp = static_cast<char*>(m->whh_planes) + whh_bytes;
+    auto mk = [&](const float* w, size_t rows, size_t cols, size_t k) {
+        PlaneMat pm = {wp, (long)(rows * k), (int)k, 2};
+        wp += bytes(rows, k);
+        if (!rc) rc = split_planes_launch(w, (long)rows, (int)cols, (int)cols, pm, st);
+        return pm;
+    };
+    m->embed_w = mk(c.embed_w, h, c.ldin, kpe);
+    m->head_w = mk(c.head_w, nh, h, h);
+    m->w_ih.clear();
+    for (int l = 0; l < c.num_layers; ++l) m->w_ih.push_back(mk(m->lay[l].w_ih, 4 * h, h, h));
+    for (int l = 0; l < m->d.num_layers && !rc; ++l)
+        for (int dir = 0; dir < 2 && !rc; ++dir) {
+            __nv_bfloat16* base = static_cast<__nv_bfloat16*>(m->whh_planes) + per * l + (per / 2) * dir;
+            PlaneMat pm = {base, 4L * H * H, H, 2};
+            rc = split_planes_launch(dir ? m->lay[l].w_hh_b : m->lay[l].w_hh_f, 4L * H, H, H, pm, st);
+        }
+    if (rc) { cudaFree(m->whh_planes); m->whh_planes = nullptr; }
+    return rc;
+}
 
 extern "C" void* css_blstm_create(const css_blstm_desc* desc, const css_blstm_layer* layers) {
     if (!desc || !layers) { css_set_error("css_blstm_create: null descriptor"); return nullptr; }
@@ -129,7 +340,11 @@ extern "C" void* css_blstm_create(const css_blstm_desc* desc, const css_blstm_la
     m->lay.assign(layers, layers + desc->num_layers);
     return m;
 }
-extern "C" void css_blstm_destroy(void* model) { delete static_cast<BlstmModel*>(model); }
+extern "C" void css_blstm_destroy(void* model) {
+    BlstmModel* m = static_cast<BlstmModel*>(model);
+    if (m && m->whh_planes) cudaFree(m->whh_planes);
+    delete m;
+}
 
 static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 static inline int bl_head_pitch(const css_blstm_desc& d) { return ((d.num_bins * d.num_out + 7) / 8) * 8; }
@@ -137,8 +352,11 @@ static inline int bl_head_pitch(const css_blstm_desc& d) { return ((d.num_bins *
 extern "C" size_t css_blstm_workspace_bytes(const void* model, long N, int T) {
     const BlstmModel* m = static_cast<const BlstmModel*>(model);
     const size_t M = (size_t)N * T, h = m->d.hdim;
+    // x, y, xproj, h (two fp32 state buffers, reused as the two bf16 hi/lo plane sets of the tensor-core step), c, head
+    // ..., and the bf16 hi/lo planes of the current GEMM input (M x max(h, padded idim))
+    const size_t ka = h > (size_t)embed_kp(m->d) ? h : (size_t)embed_kp(m->d);
     return 2 * al256(M * h * 4) + al256(M * 4 * h * 4) + al256((size_t)N * h * 4) * 3 +
-           al256(M * bl_head_pitch(m->d) * 4);
+           al256(M * bl_head_pitch(m->d) * 4) + al256(M * ka * 4);
 }
 
 extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks,
@@ -158,23 +376,53 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
     float* hs0 = (float*)wp; wp += al256((size_t)N * h * 4);
     float* hs1 = (float*)wp; wp += al256((size_t)N * h * 4);
     float* cs = (float*)wp;  wp += al256((size_t)N * h * 4);
-    float* hd = (float*)wp;
+    float* hd = (float*)wp;  wp += al256((size_t)M * bl_head_pitch(c) * 4);
+    void* act = wp;
     int rc;
+    const bool tc = css_get_gemm_mode() != 0;
+    const int P = css_get_gemm_mode() == 2 ? 1 : 2;
+    // GEMM: tensor-core modes split the fp32 input into planes and run the tcgen05 kernel, mode 0 the fp32 SIMT kernel
+    auto linear = [&](const float* A, int lda, int K, const float* W, const PlaneMat& Wp, float* C, int ldc, int Nn, const GemmEpilogue& ep) -> int {
+        if (!tc) return gemm_dispatch(A, lda, W, lda, C, ldc, M, Nn, K, ep, st);
+        PlaneMat aP = {act, M * (long)Wp.ld, Wp.ld, 2};
+        int r = split_planes_launch(A, M, K, lda, aP, st);
+        if (r) return r;
+        css_prof_begin(0, 2.0 * (double)M * Nn * K, st);
+        r = gemm_tc_planes(aP, Wp, P, M, Nn, Wp.ld, ep, C, ldc, nullptr, st);
+        css_prof_end(st);
+        return r;
+    };
+    static const int lm_tile = getenv("CSS_B200_LSTM_TILE") ? atoi(getenv("CSS_B200_LSTM_TILE")) : 0;   // WM*10+WN (tuning)
+    if (tc && (rc = build_whh_planes(m, st))) return rc;
     if (apply_mvn && (rc = css_mvn_time(feat, N, T, c.idim, c.ldin, st))) return rc;
     GemmEpilogue ee = {c.embed_b, 0, 1.f, nullptr, 0, 0.f};
-    if ((rc = gemm_dispatch(feat, c.ldin, c.embed_w, c.ldin, y, h, M, h, c.ldin, ee, st))) return rc;
+    if ((rc = linear(feat, c.ldin, c.ldin, c.embed_w, m->embed_w, y, h, h, ee))) return rc;
     if ((rc = layernorm_launch(y, c.embed_ln_g, c.embed_ln_b, x, M, h, 1e-5f, 1, st))) return rc;
     for (int l = 0; l < c.num_layers; ++l) {
         const css_blstm_layer& L = m->lay[l];
         GemmEpilogue ep = {L.b_gates, 0, 1.f, nullptr, 0, 0.f};
-        if ((rc = gemm_dispatch(x, h, L.w_ih, h, xp, 4 * h, M, 4 * h, h, ep, st))) return rc;
+        if ((rc = linear(x, h, h, L.w_ih, tc ? m->w_ih[l] : PlaneMat{}, xp, 4 * h, 4 * h, ep))) return rc;
         cudaMemsetAsync(hs0, 0, (size_t)N * h * 4, st);
         cudaMemsetAsync(cs, 0, (size_t)N * h * 4, st);
         dim3 grid((unsigned)((N + LS_BN - 1) / LS_BN), H / LS_BJ, 2);
         float *hp = hs0, *hn = hs1;
+        // tensor-core step: [dir][plane][N][H] bf16 = N*h*4 bytes, the size of one fp32 state buffer
+        const __nv_bfloat16* whh = tc ? static_cast<const __nv_bfloat16*>(m->whh_planes) + whh_layer_elems(c) * l : nullptr;
         for (int s = 0; s < T; ++s) {
             css_prof_begin(4, 2.0 * 2.0 * (double)N * H * 4 * H, st);
-            lstm_step_kernel<<<grid, 256, 0, st>>>(xp, L.w_hh_f, L.w_hh_b, hp, hn, cs, y, N, T, H, s);
+            if (tc) {
+                __nv_bfloat16 *bp = reinterpret_cast<__nv_bfloat16*>(hp), *bn = reinterpret_cast<__nv_bfloat16*>(hn);
+                switch (lm_tile ? lm_tile : (N <= 192 ? 12 : 44)) {
+                    case 12: rc = lstm_step_mma_launch<1, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    case 14: rc = lstm_step_mma_launch<1, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    case 22: rc = lstm_step_mma_launch<2, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    case 24: rc = lstm_step_mma_launch<2, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    default: rc = lstm_step_mma_launch<4, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                }
+                if (rc) { css_prof_end(st); return rc; }
+            } else {
+                lstm_step_kernel<<<grid, 256, 0, st>>>(xp, L.w_hh_f, L.w_hh_b, hp, hn, cs, y, N, T, H, s);
+            }
             css_prof_end(st);
             if ((rc = css_check_launch("lstm_step"))) return rc;
             float* tmp = hp; hp = hn; hn = tmp;
@@ -183,10 +431,10 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
     }
     if (head) {
         GemmEpilogue eh = {c.head_b, 1, 1.f, nullptr, 0, 0.f};
-        return gemm_dispatch(x, h, c.head_w, h, head, ld_head, M, nh, h, eh, st);
+        return linear(x, h, h, c.head_w, m->head_w, head, ld_head, nh, eh);
     }
     const int ldh = bl_head_pitch(c);
     GemmEpilogue eh = {c.head_b, 1, 1.f, nullptr, 0, clamp_max};
-    if ((rc = gemm_dispatch(x, h, c.head_w, h, hd, ldh, M, nh, h, eh, st))) return rc;
+    if ((rc = linear(x, h, h, c.head_w, m->head_w, hd, ldh, nh, eh))) return rc;
     return masks_layout_launch(hd, ldh, masks, N, T, c.num_bins, c.num_out, st);
 }

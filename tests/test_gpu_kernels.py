@@ -310,8 +310,9 @@ def test_conformer_golden_masks(cuda, gemm_mode, golden):
         assert rel_inf(masks[c].cpu()[:, ::3, ::3], golden["A_masks2"][c]) < 1e-3
 
 
-@pytest.mark.parametrize("N,T", [(3, 150), (70, 20)])
-def test_blstm_forward_vs_oracle(cuda, N, T):
+@pytest.mark.parametrize("N,T", [(3, 150), (70, 20), (200, 12)])
+def test_blstm_forward_vs_oracle(cuda, gemm_mode, N, T):
+    """Mode 0: fp32 FMA recurrence; mode 1: mma.sync bf16x3 recurrence (32-row CTAs up to 192 sequences, 128-row CTAs above)."""
     model = golden_blstm()
     sd = cpu_state_dict(model)
     g = torch.Generator().manual_seed(N + T)
