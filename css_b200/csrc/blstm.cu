@@ -172,22 +172,32 @@ lstm_step_mma_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
     const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(lm_smem);
 
+    // every thread copies the same (row, chunk) slots of each stage: sources and destinations are worked out once
+    constexpr int A_IT = 2 * C::BM * 8 / C::THREADS, B_IT = 2 * C::BROWS * 8 / C::THREADS;
+    static_assert(A_IT * C::THREADS == 2 * C::BM * 8 && B_IT * C::THREADS == 2 * C::BROWS * 8, "copy slots must divide evenly");
+    const __nv_bfloat16* asrc[A_IT];
+    const __nv_bfloat16* bsrc[B_IT];
+    uint32_t adst[A_IT], bdst[B_IT];
+#pragma unroll
+    for (int it = 0; it < A_IT; ++it) {
+        const int rs = (tid >> 3) + it * (C::THREADS / 8), p = rs / C::BM, r = rs % C::BM;
+        long n = n0 + r;
+        if (n >= N) n = N - 1;                                         // rows past N are computed and dropped
+        asrc[it] = hp + p * plane_h + n * H + (tid & 7) * 8;
+        adst[it] = sbase + p * C::A_PLANE + r * LM_ROWB + (tid & 7) * 16;
+    }
+#pragma unroll
+    for (int it = 0; it < B_IT; ++it) {
+        const int rs = (tid >> 3) + it * (C::THREADS / 8), p = rs / C::BROWS, r = rs % C::BROWS;
+        const int g = r / C::JB, u = r - g * C::JB;
+        bsrc[it] = wp + p * plane_w + ((long)g * H + j0 + u) * H + (tid & 7) * 8;
+        bdst[it] = sbase + 2 * C::A_PLANE + p * C::B_PLANE + r * LM_ROWB + (tid & 7) * 16;
+    }
     auto load_stage = [&](int kc, int stage) {
-        const uint32_t sa = sbase + stage * C::STAGE;
-        const int k0 = kc * LM_BK;
-        // A: 2 planes x BM rows x 8 chunks of 16 B
-        for (int i = tid; i < 2 * C::BM * 8; i += C::THREADS) {
-            const int ch = i & 7, r = (i >> 3) % C::BM, p = i / (8 * C::BM);
-            long n = n0 + r;
-            if (n >= N) n = N - 1;                                     // rows past N are computed and dropped
-            lm_cp16(sa + p * C::A_PLANE + r * LM_ROWB + ch * 16, hp + p * plane_h + n * H + k0 + ch * 8);
-        }
-        const uint32_t sb = sa + 2 * C::A_PLANE;
-        for (int i = tid; i < 2 * C::BROWS * 8; i += C::THREADS) {
-            const int ch = i & 7, r = (i >> 3) % C::BROWS, p = i / (8 * C::BROWS);
-            const int g = r / C::JB, u = r - g * C::JB;
-            lm_cp16(sb + p * C::B_PLANE + r * LM_ROWB + ch * 16, wp + p * plane_w + ((long)g * H + j0 + u) * H + k0 + ch * 8);
-        }
+#pragma unroll
+        for (int it = 0; it < A_IT; ++it) lm_cp16(adst[it] + stage * C::STAGE, asrc[it] + kc * LM_BK);
+#pragma unroll
+        for (int it = 0; it < B_IT; ++it) lm_cp16(bdst[it] + stage * C::STAGE, bsrc[it] + kc * LM_BK);
     };
 
     float acc[2][4][4];
@@ -278,6 +288,145 @@ int lstm_step_mma_launch(const float* xp, const __nv_bfloat16* whh, const __nv_b
     }
     dim3 grid((unsigned)((N + C::BM - 1) / C::BM), H / C::JB, 2);
     lstm_step_mma_kernel<WM, WN><<<grid, C::THREADS, C::SMEM, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
+    return 0;
+}
+
+// Few sequences (one 60 s recording is 72 chunks): every CTA takes ALL K of its operands into shared memory at once -- up to
+// 80 sequences (five m16 warp tiles) x H of h_{t-1} and 8 hidden units x 4 gates x H of W_hh, hi and lo planes, 224 KB at
+// H = 512 -- as H/64 cp.async groups that the mma loop waits on one by one (no ring, no reuse barrier).  Rows are H bf16
+// wide without padding; 16-byte chunk c of row r sits at chunk c ^ (r & 7) (conflict-free ldmatrix).  grid.y = H/8 CTAs
+// per direction: 128 CTAs at H = 512, one wave.
+template <int MW>
+__global__ void __launch_bounds__(32 * MW)
+lstm_step_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, const __nv_bfloat16* __restrict__ h_prev,
+                     __nv_bfloat16* __restrict__ h_next, float* __restrict__ c_state, float* __restrict__ out, long N, int T, int H, int s) {
+    constexpr int RM = 16 * MW, THREADS = 32 * MW;
+    extern __shared__ __align__(128) uint8_t lm_smem[];
+    const int dir = blockIdx.z;
+    const int t = dir ? (T - 1 - s) : s;
+    const long n0 = (long)blockIdx.x * RM;
+    const int j0 = blockIdx.y * 8;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long plane_h = N * (long)H, plane_w = 4L * H * H;
+    const __nv_bfloat16* hp = h_prev + (long)dir * 2 * plane_h;
+    const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
+    const int pitch = H * 2;
+    const uint32_t sA = (uint32_t)__cvta_generic_to_shared(lm_smem);
+    const uint32_t a_plane = RM * pitch, b_plane_b = 32 * pitch;
+    const uint32_t sB = sA + 2 * a_plane;
+    const int ng = H >> 6;                                   // groups of 64 columns (8 chunks)
+    // every thread copies the same (row, chunk-of-8) slots in each group: source and destination are worked out once, a
+    // group then costs two adds per copy (the swizzle only touches the low three chunk bits, which a group offset leaves alone)
+    constexpr int A_IT = 2 * RM * 8 / THREADS, B_IT = (2 * 32 * 8 + THREADS - 1) / THREADS;
+    const __nv_bfloat16* asrc[A_IT];
+    uint32_t adst[A_IT];
+    const int c7 = tid & 7;
+#pragma unroll
+    for (int it = 0; it < A_IT; ++it) {
+        const int rs = (tid >> 3) + it * (THREADS / 8), p = rs / RM, r = rs - p * RM;
+        long n = n0 + r;
+        if (n >= N) n = N - 1;                               // rows past N are computed and dropped
+        asrc[it] = hp + p * plane_h + n * H + c7 * 8;
+        adst[it] = sA + p * a_plane + r * pitch + ((c7 ^ (r & 7)) << 4);
+    }
+    const __nv_bfloat16* bsrc[B_IT];
+    uint32_t bdst[B_IT];
+#pragma unroll
+    for (int it = 0; it < B_IT; ++it) {
+        int rs = (tid >> 3) + it * (THREADS / 8);
+        if (rs > 63) rs = 63;                                // (guarded below)
+        const int p = rs >> 5, r = rs & 31;                  // r = gate * 8 + unit
+        bsrc[it] = wp + p * plane_w + ((long)(r >> 3) * H + j0 + (r & 7)) * H + c7 * 8;
+        bdst[it] = sB + p * b_plane_b + r * pitch + ((c7 ^ (r & 7)) << 4);
+    }
+    for (int g = 0; g < ng; ++g) {
+#pragma unroll
+        for (int it = 0; it < A_IT; ++it) lm_cp16(adst[it] + g * 128, asrc[it] + g * 64);
+#pragma unroll
+        for (int it = 0; it < B_IT; ++it)
+            if ((tid >> 3) + it * (THREADS / 8) < 64) lm_cp16(bdst[it] + g * 128, bsrc[it] + g * 64);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    float acc[4][4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
+    const bool live = n0 + warp * 16 < N;                    // warp-uniform: m-tiles entirely past N skip the products
+    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
+    const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
+    const uint32_t a_base = sA + (warp * 16 + a_row) * pitch;
+    const uint32_t b_base = sB + b_pl * b_plane_b + b_row * pitch;
+    for (int g = 0; g < ng; ++g) {
+        switch (ng - 1 - g) {                                // groups still allowed in flight
+            case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+            case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+            case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+            case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+            case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
+            case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
+            case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
+            default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+        }
+        __syncthreads();
+        if (!live) continue;
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+            const int c0 = g * 8 + kk * 2;
+            uint32_t ah[4], al[4];
+            const uint32_t aaddr = a_base + (((c0 + a_c) ^ (a_row & 7)) << 4);
+            lm_ldsm4(aaddr, ah);
+            lm_ldsm4(aaddr + a_plane, al);
+            const uint32_t boff = ((c0 + b_c) ^ b_row) << 4;
+#pragma unroll
+            for (int gt = 0; gt < 4; ++gt) {
+                uint32_t b[4];      // hi b0, hi b1, lo b0, lo b1
+                lm_ldsm4(b_base + gt * 8 * pitch + boff, b);
+                lm_mma(acc[gt], al, b[0], b[1]);
+                lm_mma(acc[gt], ah, b[2], b[3]);
+                lm_mma(acc[gt], ah, b[0], b[1]);
+            }
+        }
+    }
+    if (!live) return;
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + 2 * q;
+    __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        const long n = n0 + warp * 16 + gid + half * 8;
+        if (n >= N) continue;
+        const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
+        const float2 xi = *reinterpret_cast<const float2*>(xp), xf = *reinterpret_cast<const float2*>(xp + H);
+        const float2 xg = *reinterpret_cast<const float2*>(xp + 2 * H), xo = *reinterpret_cast<const float2*>(xp + 3 * H);
+        const long si = ((long)dir * N + n) * H + j;
+        const float2 cp = *reinterpret_cast<const float2*>(c_state + si);
+        float2 c, h;
+        c.x = lm_sigmoid(acc[1][2 * half] + xf.x) * cp.x + lm_sigmoid(acc[0][2 * half] + xi.x) * tanhf(acc[2][2 * half] + xg.x);
+        c.y = lm_sigmoid(acc[1][2 * half + 1] + xf.y) * cp.y + lm_sigmoid(acc[0][2 * half + 1] + xi.y) * tanhf(acc[2][2 * half + 1] + xg.y);
+        h.x = lm_sigmoid(acc[3][2 * half] + xo.x) * tanhf(c.x);
+        h.y = lm_sigmoid(acc[3][2 * half + 1] + xo.y) * tanhf(c.y);
+        *reinterpret_cast<float2*>(c_state + si) = c;
+        *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
+        const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
+        const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
+        *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
+        *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+    }
+}
+
+constexpr int LM_RES_MW = 5;
+int lstm_step_res_launch(const float* xp, const __nv_bfloat16* whh, const __nv_bfloat16* hp, __nv_bfloat16* hn, float* cs, float* y,
+                         long N, int T, int H, int s, cudaStream_t st) {
+    const int smem = 2 * (16 * LM_RES_MW + 32) * H * 2;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        cudaError_t e = cudaFuncSetAttribute(lstm_step_res_kernel<LM_RES_MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        CSS_REQUIRE(e == cudaSuccess, "lstm_step_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+        attr_smem = smem;
+    }
+    dim3 grid((unsigned)((N + 16 * LM_RES_MW - 1) / (16 * LM_RES_MW)), H / 8, 2);
+    lstm_step_res_kernel<LM_RES_MW><<<grid, 32 * LM_RES_MW, smem, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
     return 0;
 }
 }  // namespace
@@ -412,7 +561,8 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
             css_prof_begin(4, 2.0 * 2.0 * (double)N * H * 4 * H, st);
             if (tc) {
                 __nv_bfloat16 *bp = reinterpret_cast<__nv_bfloat16*>(hp), *bn = reinterpret_cast<__nv_bfloat16*>(hn);
-                switch (lm_tile ? lm_tile : (N <= 192 ? 12 : 44)) {
+                switch (lm_tile ? lm_tile : (N <= 160 && H <= 512 ? 1 : (N <= 192 ? 12 : 44))) {
+                    case 1: rc = lstm_step_res_launch(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                     case 12: rc = lstm_step_mma_launch<1, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                     case 14: rc = lstm_step_mma_launch<1, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                     case 22: rc = lstm_step_mma_launch<2, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;

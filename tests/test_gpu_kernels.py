@@ -310,10 +310,13 @@ def test_conformer_golden_masks(cuda, gemm_mode, golden):
         assert rel_inf(masks[c].cpu()[:, ::3, ::3], golden["A_masks2"][c]) < 1e-3
 
 
-@pytest.mark.parametrize("N,T", [(3, 150), (70, 20), (200, 12)])
-def test_blstm_forward_vs_oracle(cuda, gemm_mode, N, T):
-    """Mode 0: fp32 FMA recurrence; mode 1: mma.sync bf16x3 recurrence (32-row CTAs up to 192 sequences, 128-row CTAs above)."""
-    model = golden_blstm()
+@pytest.mark.parametrize("N,T,hdim", [(3, 150, 256), (70, 20, 256), (170, 9, 512), (200, 12, 256), (72, 8, 1024), (90, 5, 1024)])
+def test_blstm_forward_vs_oracle(cuda, gemm_mode, N, T, hdim):
+    """Mode 0: fp32 FMA recurrence; mode 1: mma.sync bf16x3 recurrence -- operands resident in shared memory up to 160
+    sequences (one and two row groups, H = 128 and 512), 32-row CTAs up to 192, 128-row CTAs above."""
+    from tests.helpers import CONF_B1
+
+    model = golden_blstm(conf=dict(CONF_B1, blstm_hdim=hdim, blstm_num_layers=2))
     sd = cpu_state_dict(model)
     g = torch.Generator().manual_seed(N + T)
     f = torch.rand(N, T, 257, generator=g) * 3
