@@ -141,7 +141,42 @@ __device__ __forceinline__ void lm_ldsm4(uint32_t addr, uint32_t* r) {
 __device__ __forceinline__ void lm_cp16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }
-__device__ __forceinline__ float lm_sigmoid(float x) { return 1.f / (1.f + expf(-x)); }
+// ex2.approx-based forms (abs error ~1e-7): the libm expf/tanhf of the fp32 step kernel were a third of this kernel's instructions
+__device__ __forceinline__ float lm_sigmoid(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
+__device__ __forceinline__ float lm_tanh(float x) {
+    const float e = __expf(-2.f * fabsf(x));
+    return copysignf(__fdividef(1.f - e, 1.f + e), x);
+}
+struct LmCellIn { float2 xi, xf, xg, xo, c; };
+// gate pre-activations of (sequence n, time t, units j, j+1) and the cell state: requested before the k loop, used after it
+__device__ __forceinline__ LmCellIn lm_cell_load(const float* __restrict__ xproj, const float* __restrict__ c_state, long n, long N, int T,
+                                                 int t, int H, int dir, int j) {
+    LmCellIn in;
+    if (n >= N) n = N - 1;
+    const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
+    in.xi = __ldg(reinterpret_cast<const float2*>(xp));
+    in.xf = __ldg(reinterpret_cast<const float2*>(xp + H));
+    in.xg = __ldg(reinterpret_cast<const float2*>(xp + 2 * H));
+    in.xo = __ldg(reinterpret_cast<const float2*>(xp + 3 * H));
+    in.c = *reinterpret_cast<const float2*>(c_state + ((long)dir * N + n) * H + j);
+    return in;
+}
+// a0..a3: accumulators of gates i, f, g, o for units j, j+1 (the [2*half], [2*half+1] entries of an m16n8 tile)
+__device__ __forceinline__ void lm_cell_store(const LmCellIn& in, float ai0, float ai1, float af0, float af1, float ag0, float ag1, float ao0,
+                                              float ao1, float* __restrict__ c_state, float* __restrict__ out, __nv_bfloat16* __restrict__ hn,
+                                              long plane_h, long n, long N, int T, int t, int H, int dir, int j) {
+    float2 c, h;
+    c.x = lm_sigmoid(af0 + in.xf.x) * in.c.x + lm_sigmoid(ai0 + in.xi.x) * lm_tanh(ag0 + in.xg.x);
+    c.y = lm_sigmoid(af1 + in.xf.y) * in.c.y + lm_sigmoid(ai1 + in.xi.y) * lm_tanh(ag1 + in.xg.y);
+    h.x = lm_sigmoid(ao0 + in.xo.x) * lm_tanh(c.x);
+    h.y = lm_sigmoid(ao1 + in.xo.y) * lm_tanh(c.y);
+    *reinterpret_cast<float2*>(c_state + ((long)dir * N + n) * H + j) = c;
+    *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
+    const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
+    const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
+    *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
+    *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+}
 
 template <int WM, int WN>
 struct LmCfg {
@@ -208,11 +243,19 @@ lstm_step_mma_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[m][g][i] = 0.f;
 
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + wn * 8 + 2 * q;
     const int nk = H / LM_BK;
     load_stage(0, 0);
     asm volatile("cp.async.commit_group;" ::: "memory");
     if (nk > 1) load_stage(1, 1);
     asm volatile("cp.async.commit_group;" ::: "memory");
+    LmCellIn cin[2][2];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+            cin[m][half] = lm_cell_load(xproj, c_state, n0 + wm * 32 + m * 16 + gid + half * 8, N, T, t, H, dir, j);
     // ldmatrix lane addressing.  A (16 x 16, row-major): matrices (r0-7,k0-7), (r8-15,k0-7), (r0-7,k8-15), (r8-15,k8-15)
     const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_k = (lane >> 4) * 8;
     // B: per gate one x4 = hi(k0-7), hi(k8-15), lo(k0-7), lo(k8-15) of the warp's 8 units
@@ -247,8 +290,6 @@ lstm_step_mma_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
         }
     }
     // fused cell update (gate order i, f, g, o as torch.nn.LSTM): thread holds rows gid, gid+8 and units 2q, 2q+1 of each m-tile
-    const int gid = lane >> 2, q = lane & 3;
-    const int j = j0 + wn * 8 + 2 * q;
     __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
@@ -256,22 +297,9 @@ lstm_step_mma_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
         for (int half = 0; half < 2; ++half) {
             const long n = n0 + wm * 32 + m * 16 + gid + half * 8;
             if (n >= N) continue;
-            const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
-            const float2 xi = *reinterpret_cast<const float2*>(xp), xf = *reinterpret_cast<const float2*>(xp + H);
-            const float2 xg = *reinterpret_cast<const float2*>(xp + 2 * H), xo = *reinterpret_cast<const float2*>(xp + 3 * H);
-            const long si = ((long)dir * N + n) * H + j;
-            const float2 cp = *reinterpret_cast<const float2*>(c_state + si);
-            float2 c, h;
-            c.x = lm_sigmoid(acc[m][1][2 * half] + xf.x) * cp.x + lm_sigmoid(acc[m][0][2 * half] + xi.x) * tanhf(acc[m][2][2 * half] + xg.x);
-            c.y = lm_sigmoid(acc[m][1][2 * half + 1] + xf.y) * cp.y + lm_sigmoid(acc[m][0][2 * half + 1] + xi.y) * tanhf(acc[m][2][2 * half + 1] + xg.y);
-            h.x = lm_sigmoid(acc[m][3][2 * half] + xo.x) * tanhf(c.x);
-            h.y = lm_sigmoid(acc[m][3][2 * half + 1] + xo.y) * tanhf(c.y);
-            *reinterpret_cast<float2*>(c_state + si) = c;
-            *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
-            const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
-            *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
-            *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+            lm_cell_store(cin[m][half], acc[m][0][2 * half], acc[m][0][2 * half + 1], acc[m][1][2 * half], acc[m][1][2 * half + 1],
+                          acc[m][2][2 * half], acc[m][2][2 * half + 1], acc[m][3][2 * half], acc[m][3][2 * half + 1], c_state, out, hn,
+                          plane_h, n, N, T, t, H, dir, j);
         }
     }
 }
@@ -353,6 +381,11 @@ lstm_step_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
     const bool live = n0 + warp * 16 < N;                    // warp-uniform: m-tiles entirely past N skip the products
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + 2 * q;
+    LmCellIn cin[2];
+#pragma unroll
+    for (int half = 0; half < 2; ++half) cin[half] = lm_cell_load(xproj, c_state, n0 + warp * 16 + gid + half * 8, N, T, t, H, dir, j);
     const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
     const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
     const uint32_t a_base = sA + (warp * 16 + a_row) * pitch;
@@ -389,29 +422,13 @@ lstm_step_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
         }
     }
     if (!live) return;
-    const int gid = lane >> 2, q = lane & 3;
-    const int j = j0 + 2 * q;
     __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
         const long n = n0 + warp * 16 + gid + half * 8;
         if (n >= N) continue;
-        const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
-        const float2 xi = *reinterpret_cast<const float2*>(xp), xf = *reinterpret_cast<const float2*>(xp + H);
-        const float2 xg = *reinterpret_cast<const float2*>(xp + 2 * H), xo = *reinterpret_cast<const float2*>(xp + 3 * H);
-        const long si = ((long)dir * N + n) * H + j;
-        const float2 cp = *reinterpret_cast<const float2*>(c_state + si);
-        float2 c, h;
-        c.x = lm_sigmoid(acc[1][2 * half] + xf.x) * cp.x + lm_sigmoid(acc[0][2 * half] + xi.x) * tanhf(acc[2][2 * half] + xg.x);
-        c.y = lm_sigmoid(acc[1][2 * half + 1] + xf.y) * cp.y + lm_sigmoid(acc[0][2 * half + 1] + xi.y) * tanhf(acc[2][2 * half + 1] + xg.y);
-        h.x = lm_sigmoid(acc[3][2 * half] + xo.x) * tanhf(c.x);
-        h.y = lm_sigmoid(acc[3][2 * half + 1] + xo.y) * tanhf(c.y);
-        *reinterpret_cast<float2*>(c_state + si) = c;
-        *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
-        const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
-        const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
-        *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
-        *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+        lm_cell_store(cin[half], acc[0][2 * half], acc[0][2 * half + 1], acc[1][2 * half], acc[1][2 * half + 1], acc[2][2 * half],
+                      acc[2][2 * half + 1], acc[3][2 * half], acc[3][2 * half + 1], c_state, out, hn, plane_h, n, N, T, t, H, dir, j);
     }
 }
 
@@ -541,7 +558,7 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         css_prof_end(st);
         return r;
     };
-    static const int lm_tile = getenv("CSS_B200_LSTM_TILE") ? atoi(getenv("CSS_B200_LSTM_TILE")) : 0;   // WM*10+WN (tuning)
+    static const int lm_tile = getenv("CSS_B200_LSTM_TILE") ? atoi(getenv("CSS_B200_LSTM_TILE")) : 0;   // 1 resident, 12 / 22 = WM, WN of the ring kernel (tuning)
     if (tc && (rc = build_whh_planes(m, st))) return rc;
     if (apply_mvn && (rc = css_mvn_time(feat, N, T, c.idim, c.ldin, st))) return rc;
     GemmEpilogue ee = {c.embed_b, 0, 1.f, nullptr, 0, 0.f};
@@ -561,13 +578,11 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
             css_prof_begin(4, 2.0 * 2.0 * (double)N * H * 4 * H, st);
             if (tc) {
                 __nv_bfloat16 *bp = reinterpret_cast<__nv_bfloat16*>(hp), *bn = reinterpret_cast<__nv_bfloat16*>(hn);
-                switch (lm_tile ? lm_tile : (N <= 160 && H <= 512 ? 1 : (N <= 192 ? 12 : 44))) {
+                // measured on B200 (N = 747, H = 512): 64 x 64 CTAs 49 us per step, 128 x 128 CTAs 58 us (1.3 waves of one CTA per SM)
+                switch (lm_tile ? lm_tile : (N <= 160 && H <= 512 ? 1 : (N <= 192 ? 12 : 22))) {
                     case 1: rc = lstm_step_res_launch(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                     case 12: rc = lstm_step_mma_launch<1, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
-                    case 14: rc = lstm_step_mma_launch<1, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
-                    case 22: rc = lstm_step_mma_launch<2, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
-                    case 24: rc = lstm_step_mma_launch<2, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
-                    default: rc = lstm_step_mma_launch<4, 4>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    default: rc = lstm_step_mma_launch<2, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                 }
                 if (rc) { css_prof_end(st); return rc; }
             } else {
