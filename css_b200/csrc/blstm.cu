@@ -319,6 +319,36 @@ int lstm_step_mma_launch(const float* xp, const __nv_bfloat16* whh, const __nv_b
     return 0;
 }
 
+// One 64-column group of the resident kernels: 4 k16 steps x (4 gate tiles x 3 product terms).  The fragments of step kk + 1
+// are requested (6 ldmatrix.x4) before the 12 HMMAs of step kk are issued -- with one warp per scheduler the loop was
+// otherwise one shared-memory round trip per gate tile (ncu: 35 cycles per HMMA, short-scoreboard + wait stalls) -- and the
+// HMMAs go term by term over the four gate accumulators, so consecutive ones are independent.  Every accumulator still sees
+// lo.hi, hi.lo, hi.hi in that order: the sums are the bits the ring kernel produces.
+__device__ __forceinline__ void lm_group_mma(float (&acc)[4][4], int c_first, uint32_t a_base, uint32_t a_plane, int a_c, int a_row,
+                                             uint32_t b_base, int pitch, int b_c, int b_row) {
+    uint32_t fa[2][8], fb[2][16];
+    auto fetch = [&](int buf, int c0) {
+        const uint32_t aaddr = a_base + (((c0 + a_c) ^ (a_row & 7)) << 4);
+        lm_ldsm4(aaddr, &fa[buf][0]);                        // hi plane of h
+        lm_ldsm4(aaddr + a_plane, &fa[buf][4]);              // lo plane
+        const uint32_t boff = ((c0 + b_c) ^ b_row) << 4;
+#pragma unroll
+        for (int gt = 0; gt < 4; ++gt) lm_ldsm4(b_base + gt * 8 * pitch + boff, &fb[buf][4 * gt]);   // hi b0, hi b1, lo b0, lo b1
+    };
+    fetch(0, c_first);
+#pragma unroll
+    for (int kk = 0; kk < 4; ++kk) {
+        const int cur = kk & 1;
+        if (kk < 3) fetch(cur ^ 1, c_first + (kk + 1) * 2);
+#pragma unroll
+        for (int gt = 0; gt < 4; ++gt) lm_mma(acc[gt], &fa[cur][4], fb[cur][4 * gt], fb[cur][4 * gt + 1]);
+#pragma unroll
+        for (int gt = 0; gt < 4; ++gt) lm_mma(acc[gt], &fa[cur][0], fb[cur][4 * gt + 2], fb[cur][4 * gt + 3]);
+#pragma unroll
+        for (int gt = 0; gt < 4; ++gt) lm_mma(acc[gt], &fa[cur][0], fb[cur][4 * gt], fb[cur][4 * gt + 1]);
+    }
+}
+
 // Few sequences (one 60 s recording is 72 chunks): every CTA takes ALL K of its operands into shared memory at once -- up to
 // 80 sequences (five m16 warp tiles) x H of h_{t-1} and 8 hidden units x 4 gates x H of W_hh, hi and lo planes, 224 KB at
 // H = 512 -- as H/64 cp.async groups that the mma loop waits on one by one (no ring, no reuse barrier).  Rows are H bf16
@@ -403,23 +433,7 @@ lstm_step_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __res
         }
         __syncthreads();
         if (!live) continue;
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk) {
-            const int c0 = g * 8 + kk * 2;
-            uint32_t ah[4], al[4];
-            const uint32_t aaddr = a_base + (((c0 + a_c) ^ (a_row & 7)) << 4);
-            lm_ldsm4(aaddr, ah);
-            lm_ldsm4(aaddr + a_plane, al);
-            const uint32_t boff = ((c0 + b_c) ^ b_row) << 4;
-#pragma unroll
-            for (int gt = 0; gt < 4; ++gt) {
-                uint32_t b[4];      // hi b0, hi b1, lo b0, lo b1
-                lm_ldsm4(b_base + gt * 8 * pitch + boff, b);
-                lm_mma(acc[gt], al, b[0], b[1]);
-                lm_mma(acc[gt], ah, b[2], b[3]);
-                lm_mma(acc[gt], ah, b[0], b[1]);
-            }
-        }
+        lm_group_mma(acc, g * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
     }
     if (!live) return;
     __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
@@ -444,6 +458,179 @@ int lstm_step_res_launch(const float* xp, const __nv_bfloat16* whh, const __nv_b
     }
     dim3 grid((unsigned)((N + 16 * LM_RES_MW - 1) / (16 * LM_RES_MW)), H / 8, 2);
     lstm_step_res_kernel<LM_RES_MW><<<grid, 32 * LM_RES_MW, smem, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
+    return 0;
+}
+
+// Whole recurrence of a layer in ONE launch (few sequences, the 60 s case): the CTA layout and the arithmetic of
+// lstm_step_res_kernel, with the T steps as a loop inside the kernel.  W_hh of the CTA (8 units x 4 gates x H, hi and lo
+// planes, 64 KB at H = 512) is copied into shared memory once and stays; the cell state of a thread's (sequence, unit) pairs
+// stays in registers; per step only the planes of h_{t-1} come in (cp.async.cg from L2) and the planes of h_t go out, the two
+// h buffers alternating.  The CTAs of one direction meet at a counter in global memory after every step (release: bar.sync +
+// fence + atomic add by thread 0; acquire: relaxed spin + fence + bar.sync); the two directions never wait for each other.  The
+// gate pre-activations of the next step are requested before the spin.  All CTAs must be co-resident: cooperative launch,
+// grid <= one CTA per SM (checked by the host, which otherwise keeps the per-step launches).  A spin that sees no progress
+// for ~1 s gives up and raises sync[2] (results are then wrong, the GPU is not hung).
+__device__ __forceinline__ void lm_x_load(LmCellIn& in, const float* __restrict__ xproj, long n, long N, int T, int t, int H, int dir, int j) {
+    if (n >= N) n = N - 1;
+    const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
+    in.xi = __ldg(reinterpret_cast<const float2*>(xp));
+    in.xf = __ldg(reinterpret_cast<const float2*>(xp + H));
+    in.xg = __ldg(reinterpret_cast<const float2*>(xp + 2 * H));
+    in.xo = __ldg(reinterpret_cast<const float2*>(xp + 3 * H));
+}
+
+template <int MW>
+__global__ void __launch_bounds__(32 * MW)
+lstm_seq_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, __nv_bfloat16* __restrict__ hbuf0,
+                    __nv_bfloat16* __restrict__ hbuf1, float* __restrict__ out, unsigned* __restrict__ sync, long N, int T, int H) {
+    constexpr int RM = 16 * MW, THREADS = 32 * MW;
+    extern __shared__ __align__(128) uint8_t lm_smem[];
+    const int dir = blockIdx.z;
+    const long n0 = (long)blockIdx.x * RM;
+    const int j0 = blockIdx.y * 8;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const long plane_h = N * (long)H, plane_w = 4L * H * H;
+    const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
+    const int pitch = H * 2;
+    const uint32_t sA = (uint32_t)__cvta_generic_to_shared(lm_smem);
+    const uint32_t a_plane = RM * pitch, b_plane_b = 32 * pitch;
+    const uint32_t sB = sA + 2 * a_plane;
+    const int ng = H >> 6;
+    constexpr int A_IT = 2 * RM * 8 / THREADS, B_IT = (2 * 32 * 8 + THREADS - 1) / THREADS;
+    long aoff[A_IT];                                         // element offset inside one h buffer
+    uint32_t adst[A_IT];
+    const int c7 = tid & 7;
+#pragma unroll
+    for (int it = 0; it < A_IT; ++it) {
+        const int rs = (tid >> 3) + it * (THREADS / 8), p = rs / RM, r = rs - p * RM;
+        long n = n0 + r;
+        if (n >= N) n = N - 1;
+        aoff[it] = (long)dir * 2 * plane_h + p * plane_h + n * H + c7 * 8;
+        adst[it] = sA + p * a_plane + r * pitch + ((c7 ^ (r & 7)) << 4);
+    }
+    const bool live = n0 + warp * 16 < N;
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + 2 * q;
+    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
+    const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
+    const uint32_t a_base = sA + (warp * 16 + a_row) * pitch;
+    const uint32_t b_base = sB + b_pl * b_plane_b + b_row * pitch;
+    const unsigned ncta = gridDim.x * gridDim.y;             // CTAs of one direction
+    unsigned* ctr = sync + dir;
+    bool dead = false;
+    LmCellIn cin[2];
+    cin[0].c = cin[1].c = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int half = 0; half < 2; ++half) lm_x_load(cin[half], xproj, n0 + warp * 16 + gid + half * 8, N, T, dir ? T - 1 : 0, H, dir, j);
+    for (int s = 0; s < T; ++s) {
+        const int t = dir ? (T - 1 - s) : s;
+        const __nv_bfloat16* hp = (s & 1) ? hbuf1 : hbuf0;
+        __nv_bfloat16* hn = ((s & 1) ? hbuf0 : hbuf1) + (long)dir * 2 * plane_h;
+        for (int g = 0; g < ng; ++g) {
+#pragma unroll
+            for (int it = 0; it < A_IT; ++it) lm_cp16(adst[it] + g * 128, hp + aoff[it] + g * 64);
+            if (s == 0) {
+#pragma unroll
+                for (int it = 0; it < B_IT; ++it) {
+                    const int rs = (tid >> 3) + it * (THREADS / 8);
+                    if (rs < 64) {
+                        const int p = rs >> 5, r = rs & 31;  // r = gate * 8 + unit
+                        lm_cp16(sB + p * b_plane_b + r * pitch + ((c7 ^ (r & 7)) << 4) + g * 128,
+                                wp + p * plane_w + ((long)(r >> 3) * H + j0 + (r & 7)) * H + c7 * 8 + g * 64);
+                    }
+                }
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+        float acc[4][4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
+        for (int g = 0; g < ng; ++g) {
+            switch (ng - 1 - g) {
+                case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+                case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+                case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+                case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+                case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
+                case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
+                case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
+                default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+            }
+            __syncthreads();
+            if (!live) continue;
+            lm_group_mma(acc, g * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
+        }
+        if (live) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const long n = n0 + warp * 16 + gid + half * 8;
+                if (n >= N) continue;
+                const LmCellIn& in = cin[half];
+                const float ai0 = acc[0][2 * half], ai1 = acc[0][2 * half + 1], af0 = acc[1][2 * half], af1 = acc[1][2 * half + 1];
+                const float ag0 = acc[2][2 * half], ag1 = acc[2][2 * half + 1], ao0 = acc[3][2 * half], ao1 = acc[3][2 * half + 1];
+                float2 c, h;                                  // same expressions as lm_cell_store
+                c.x = lm_sigmoid(af0 + in.xf.x) * in.c.x + lm_sigmoid(ai0 + in.xi.x) * lm_tanh(ag0 + in.xg.x);
+                c.y = lm_sigmoid(af1 + in.xf.y) * in.c.y + lm_sigmoid(ai1 + in.xi.y) * lm_tanh(ag1 + in.xg.y);
+                h.x = lm_sigmoid(ao0 + in.xo.x) * lm_tanh(c.x);
+                h.y = lm_sigmoid(ao1 + in.xo.y) * lm_tanh(c.y);
+                cin[half].c = c;
+                *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
+                const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
+                const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
+                *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
+                *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+            }
+        }
+        if (s + 1 == T) break;
+#pragma unroll
+        for (int half = 0; half < 2; ++half)
+            lm_x_load(cin[half], xproj, n0 + warp * 16 + gid + half * 8, N, T, dir ? (T - 2 - s) : (s + 1), H, dir, j);
+        __syncthreads();                                     // this CTA's h_t stores are issued, its reads of the h_{t-1} tile are done
+        if (tid == 0) {
+            __threadfence();
+            atomicAdd(ctr, 1u);
+            if (!dead) {
+                const unsigned target = (unsigned)(s + 1) * ncta;
+                const long long t0 = clock64();
+                unsigned v;
+                for (;;) {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");   // the fence below orders the h loads
+                    if (v >= target) break;
+                    if (clock64() - t0 > 2000000000LL) { dead = true; atomicExch(sync + 2, 1u); break; }
+                }
+            }
+            __threadfence();
+        }
+        __syncthreads();
+    }
+}
+
+static int lstm_seq_res_ok(long N, int H) {                  // 1: the whole grid fits the device at once
+    static int sms = 0, coop = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    }
+    return coop && H % 64 == 0 && H <= 512 && N <= 16 * LM_RES_MW && 2 * (H / 8) <= sms;
+}
+
+int lstm_seq_res_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* y, unsigned* sync,
+                        long N, int T, int H, cudaStream_t st) {
+    int smem = 2 * (16 * LM_RES_MW + 32) * H * 2;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        cudaError_t e = cudaFuncSetAttribute(lstm_seq_res_kernel<LM_RES_MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        CSS_REQUIRE(e == cudaSuccess, "lstm_seq_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+        attr_smem = smem;
+    }
+    dim3 grid(1, H / 8, 2);
+    void* args[] = {(void*)&xp, (void*)&whh, (void*)&h0, (void*)&h1, (void*)&y, (void*)&sync, (void*)&N, (void*)&T, (void*)&H};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)lstm_seq_res_kernel<LM_RES_MW>, grid, dim3(32 * LM_RES_MW), args, (size_t)smem, st);
+    CSS_REQUIRE(e == cudaSuccess, "lstm_seq_res: cooperative launch failed: %s", cudaGetErrorString(e));
     return 0;
 }
 }  // namespace
@@ -492,6 +679,17 @@ static int build_whh_planes(BlstmModel* m, cudaStream_t st) {
         }
     if (rc) { cudaFree(m->whh_planes); m->whh_planes = nullptr; }
     return rc;
+}
+
+static int g_lstm_plan = -1;
+extern "C" int css_get_lstm_plan(void) {
+    if (g_lstm_plan < 0) g_lstm_plan = getenv("CSS_B200_LSTM_TILE") ? atoi(getenv("CSS_B200_LSTM_TILE")) : 0;
+    return g_lstm_plan;
+}
+extern "C" int css_set_lstm_plan(int plan) {
+    CSS_REQUIRE(plan == 0 || plan == 1 || plan == 3 || plan == 12 || plan == 22, "css_set_lstm_plan: unknown plan %d", plan);
+    g_lstm_plan = plan;
+    return 0;
 }
 
 extern "C" void* css_blstm_create(const css_blstm_desc* desc, const css_blstm_layer* layers) {
@@ -558,7 +756,7 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         css_prof_end(st);
         return r;
     };
-    static const int lm_tile = getenv("CSS_B200_LSTM_TILE") ? atoi(getenv("CSS_B200_LSTM_TILE")) : 0;   // 1 resident, 12 / 22 = WM, WN of the ring kernel (tuning)
+    const int lm_tile = css_get_lstm_plan();   // 1 resident per step, 3 resident whole sequence, 12 / 22 = WM, WN of the ring kernel
     if (tc && (rc = build_whh_planes(m, st))) return rc;
     if (apply_mvn && (rc = css_mvn_time(feat, N, T, c.idim, c.ldin, st))) return rc;
     GemmEpilogue ee = {c.embed_b, 0, 1.f, nullptr, 0, 0.f};
@@ -574,6 +772,16 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         float *hp = hs0, *hn = hs1;
         // tensor-core step: [dir][plane][N][H] bf16 = N*h*4 bytes, the size of one fp32 state buffer
         const __nv_bfloat16* whh = tc ? static_cast<const __nv_bfloat16*>(m->whh_planes) + whh_layer_elems(c) * l : nullptr;
+        // few sequences: the T steps of the layer in one cooperative launch (0 = default; 1 forces the per-step launches)
+        if (tc && (lm_tile == 0 || lm_tile == 3) && lstm_seq_res_ok(N, H)) {
+            css_prof_begin(4, (double)T * 2.0 * 2.0 * (double)N * H * 4 * H, st);
+            rc = lstm_seq_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), y,
+                                     reinterpret_cast<unsigned*>(cs), N, T, H, st);   // cs (zeroed above) holds the step counters
+            css_prof_end(st);
+            if (rc || (rc = css_check_launch("lstm_seq"))) return rc;
+            if ((rc = layernorm_launch(y, L.ln_g, L.ln_b, x, M, h, 1e-5f, 0, st))) return rc;
+            continue;
+        }
         for (int s = 0; s < T; ++s) {
             css_prof_begin(4, 2.0 * 2.0 * (double)N * H * 4 * H, st);
             if (tc) {

@@ -328,6 +328,34 @@ def test_blstm_forward_vs_oracle(cuda, gemm_mode, N, T, hdim):
     assert rel_inf(y_pred, y_o) < 1e-4
 
 
+@pytest.mark.parametrize("N,T,hdim", [(1, 150, 256), (72, 150, 1024), (80, 31, 512), (37, 2, 1024)])
+def test_blstm_whole_sequence_launch_equals_per_step(cuda, N, T, hdim):
+    """Plan 3 (all T steps of a layer in one cooperative launch, W_hh and the cell state on chip, per-direction step counter
+    in global memory) against plan 1 (one launch per step): the same arithmetic, so the masks are equal bit for bit."""
+    from css_b200 import _native as nv
+    from tests.helpers import CONF_B1
+
+    if nv.get_gemm_mode() == 0:
+        pytest.skip("tensor-core recurrence only")
+    model = golden_blstm(conf=dict(CONF_B1, blstm_hdim=hdim, blstm_num_layers=2)).to(cuda)
+    g = torch.Generator().manual_seed(7 * N + T)
+    f = (torch.rand(N, T, 257, generator=g) * 3).to(cuda)
+    lib = nv.lib()
+    before = lib.css_get_lstm_plan()
+    try:
+        nv.check(lib.css_set_lstm_plan(1), "css_set_lstm_plan")
+        _, m_step = model(f.clone())
+        nv.check(lib.css_set_lstm_plan(3), "css_set_lstm_plan")
+        for _ in range(3):                                   # repeated: the step counters are re-zeroed per layer launch
+            _, m_seq = model(f.clone())
+            torch.cuda.synchronize()
+            for a, b in zip(m_seq, m_step):
+                assert torch.equal(a, b)
+    finally:
+        lib.css_set_lstm_plan(before)
+    assert lib.css_set_lstm_plan(7) != 0
+
+
 def test_session_protocol(cuda):
     """The ORT-session plug-in contract of css/executor/separator.py:94-103."""
     from css_b200.utils.model_util import B200Session
