@@ -349,127 +349,24 @@ __device__ __forceinline__ void lm_group_mma(float (&acc)[4][4], int c_first, ui
     }
 }
 
-// Few sequences (one 60 s recording is 72 chunks): every CTA takes ALL K of its operands into shared memory at once -- up to
+// Few sequences (one 60 s recording is 72 chunks; up to 160): every CTA takes ALL K of its operands into shared memory -- up to
 // 80 sequences (five m16 warp tiles) x H of h_{t-1} and 8 hidden units x 4 gates x H of W_hh, hi and lo planes, 224 KB at
 // H = 512 -- as H/64 cp.async groups that the mma loop waits on one by one (no ring, no reuse barrier).  Rows are H bf16
 // wide without padding; 16-byte chunk c of row r sits at chunk c ^ (r & 7) (conflict-free ldmatrix).  grid.y = H/8 CTAs
 // per direction: 128 CTAs at H = 512, one wave.
-template <int MW>
-__global__ void __launch_bounds__(32 * MW)
-lstm_step_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, const __nv_bfloat16* __restrict__ h_prev,
-                     __nv_bfloat16* __restrict__ h_next, float* __restrict__ c_state, float* __restrict__ out, long N, int T, int H, int s) {
-    constexpr int RM = 16 * MW, THREADS = 32 * MW;
-    extern __shared__ __align__(128) uint8_t lm_smem[];
-    const int dir = blockIdx.z;
-    const int t = dir ? (T - 1 - s) : s;
-    const long n0 = (long)blockIdx.x * RM;
-    const int j0 = blockIdx.y * 8;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const long plane_h = N * (long)H, plane_w = 4L * H * H;
-    const __nv_bfloat16* hp = h_prev + (long)dir * 2 * plane_h;
-    const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
-    const int pitch = H * 2;
-    const uint32_t sA = (uint32_t)__cvta_generic_to_shared(lm_smem);
-    const uint32_t a_plane = RM * pitch, b_plane_b = 32 * pitch;
-    const uint32_t sB = sA + 2 * a_plane;
-    const int ng = H >> 6;                                   // groups of 64 columns (8 chunks)
-    // every thread copies the same (row, chunk-of-8) slots in each group: source and destination are worked out once, a
-    // group then costs two adds per copy (the swizzle only touches the low three chunk bits, which a group offset leaves alone)
-    constexpr int A_IT = 2 * RM * 8 / THREADS, B_IT = (2 * 32 * 8 + THREADS - 1) / THREADS;
-    const __nv_bfloat16* asrc[A_IT];
-    uint32_t adst[A_IT];
-    const int c7 = tid & 7;
-#pragma unroll
-    for (int it = 0; it < A_IT; ++it) {
-        const int rs = (tid >> 3) + it * (THREADS / 8), p = rs / RM, r = rs - p * RM;
-        long n = n0 + r;
-        if (n >= N) n = N - 1;                               // rows past N are computed and dropped
-        asrc[it] = hp + p * plane_h + n * H + c7 * 8;
-        adst[it] = sA + p * a_plane + r * pitch + ((c7 ^ (r & 7)) << 4);
-    }
-    const __nv_bfloat16* bsrc[B_IT];
-    uint32_t bdst[B_IT];
-#pragma unroll
-    for (int it = 0; it < B_IT; ++it) {
-        int rs = (tid >> 3) + it * (THREADS / 8);
-        if (rs > 63) rs = 63;                                // (guarded below)
-        const int p = rs >> 5, r = rs & 31;                  // r = gate * 8 + unit
-        bsrc[it] = wp + p * plane_w + ((long)(r >> 3) * H + j0 + (r & 7)) * H + c7 * 8;
-        bdst[it] = sB + p * b_plane_b + r * pitch + ((c7 ^ (r & 7)) << 4);
-    }
-    for (int g = 0; g < ng; ++g) {
-#pragma unroll
-        for (int it = 0; it < A_IT; ++it) lm_cp16(adst[it] + g * 128, asrc[it] + g * 64);
-#pragma unroll
-        for (int it = 0; it < B_IT; ++it)
-            if ((tid >> 3) + it * (THREADS / 8) < 64) lm_cp16(bdst[it] + g * 128, bsrc[it] + g * 64);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    }
-    float acc[4][4];
-#pragma unroll
-    for (int g = 0; g < 4; ++g)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
-    const bool live = n0 + warp * 16 < N;                    // warp-uniform: m-tiles entirely past N skip the products
-    const int gid = lane >> 2, q = lane & 3;
-    const int j = j0 + 2 * q;
-    LmCellIn cin[2];
-#pragma unroll
-    for (int half = 0; half < 2; ++half) cin[half] = lm_cell_load(xproj, c_state, n0 + warp * 16 + gid + half * 8, N, T, t, H, dir, j);
-    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
-    const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
-    const uint32_t a_base = sA + (warp * 16 + a_row) * pitch;
-    const uint32_t b_base = sB + b_pl * b_plane_b + b_row * pitch;
-    for (int g = 0; g < ng; ++g) {
-        switch (ng - 1 - g) {                                // groups still allowed in flight
-            case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
-            case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
-            case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
-            case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
-            case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
-            case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
-            case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
-            default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
-        }
-        __syncthreads();
-        if (!live) continue;
-        lm_group_mma(acc, g * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
-    }
-    if (!live) return;
-    __nv_bfloat16* hn = h_next + (long)dir * 2 * plane_h;
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        const long n = n0 + warp * 16 + gid + half * 8;
-        if (n >= N) continue;
-        lm_cell_store(cin[half], acc[0][2 * half], acc[0][2 * half + 1], acc[1][2 * half], acc[1][2 * half + 1], acc[2][2 * half],
-                      acc[2][2 * half + 1], acc[3][2 * half], acc[3][2 * half + 1], c_state, out, hn, plane_h, n, N, T, t, H, dir, j);
-    }
-}
-
-constexpr int LM_RES_MW = 5;
-int lstm_step_res_launch(const float* xp, const __nv_bfloat16* whh, const __nv_bfloat16* hp, __nv_bfloat16* hn, float* cs, float* y,
-                         long N, int T, int H, int s, cudaStream_t st) {
-    const int smem = 2 * (16 * LM_RES_MW + 32) * H * 2;
-    static int attr_smem = 0;
-    if (smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(lstm_step_res_kernel<LM_RES_MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        CSS_REQUIRE(e == cudaSuccess, "lstm_step_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
-        attr_smem = smem;
-    }
-    dim3 grid((unsigned)((N + 16 * LM_RES_MW - 1) / (16 * LM_RES_MW)), H / 8, 2);
-    lstm_step_res_kernel<LM_RES_MW><<<grid, 32 * LM_RES_MW, smem, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
-    return 0;
-}
-
-// Whole recurrence of a layer in ONE launch (few sequences, the 60 s case): the CTA layout and the arithmetic of
-// lstm_step_res_kernel, with the T steps as a loop inside the kernel.  W_hh of the CTA (8 units x 4 gates x H, hi and lo
-// planes, 64 KB at H = 512) is copied into shared memory once and stays; the cell state of a thread's (sequence, unit) pairs
-// stays in registers; per step only the planes of h_{t-1} come in (cp.async.cg from L2) and the planes of h_t go out, the two
-// h buffers alternating.  The CTAs of one direction meet at a counter in global memory after every step (release: bar.sync +
-// fence + atomic add by thread 0; acquire: relaxed spin + fence + bar.sync); the two directions never wait for each other.  The
-// gate pre-activations of the next step are requested before the spin.  All CTAs must be co-resident: cooperative launch,
-// grid <= one CTA per SM (checked by the host, which otherwise keeps the per-step launches).  A spin that sees no progress
-// for ~1 s gives up and raises sync[2] (results are then wrong, the GPU is not hung).
+//
+// The kernel runs steps [s_begin, s_end) of a layer.  One step per launch (N <= 160, two row groups) or -- N <= 80 -- the WHOLE
+// recurrence in one cooperative launch: W_hh of the CTA (64 KB at H = 512) is copied into shared memory once and stays, the cell
+// state of a thread's (sequence, unit) pairs stays in registers, per step only the planes of h_{t-1} come in (cp.async.cg from
+// L2) and the planes of h_t go out, the two h buffers alternating.  The CTAs of one direction meet at a counter in global memory
+// after every step (release: bar.sync + fence + atomic add by thread 0; acquire: relaxed spin + fence + bar.sync); the two
+// directions never wait for each other.  The gate pre-activations of the next step are requested before the spin.  All CTAs
+// must be co-resident: cooperative launch, grid <= one CTA per SM (checked by the host, which otherwise keeps the per-step
+// launches).  A spin that sees no progress for ~1 s gives up and raises sync[2] (results are then wrong, the GPU is not hung).
+//
+// KS = 2: two sets of MW warps, set k owns the 64-column groups g = k (mod 2) -- it copies them, waits for them behind its own
+// named barrier and multiplies them -- so every scheduler carries 2-3 warps instead of 1-2 (five warps on four schedulers left
+// one of them with twice the HMMAs).  The partial sums of set 1 cross to set 0 through the (then idle) h tile.
 __device__ __forceinline__ void lm_x_load(LmCellIn& in, const float* __restrict__ xproj, long n, long N, int T, int t, int H, int dir, int j) {
     if (n >= N) n = N - 1;
     const float* xp = xproj + (n * T + t) * (long)(8 * H) + (long)dir * 4 * H + j;
@@ -478,61 +375,86 @@ __device__ __forceinline__ void lm_x_load(LmCellIn& in, const float* __restrict_
     in.xg = __ldg(reinterpret_cast<const float2*>(xp + 2 * H));
     in.xo = __ldg(reinterpret_cast<const float2*>(xp + 3 * H));
 }
+__device__ __forceinline__ void lm_wait_groups(int n) {      // at most n cp.async groups of this thread still in flight
+    switch (n) {
+        case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
+        case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
+        case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
+        case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
+        case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
+        case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
+        case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
+        default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+    }
+}
 
-template <int MW>
-__global__ void __launch_bounds__(32 * MW)
-lstm_seq_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, __nv_bfloat16* __restrict__ hbuf0,
-                    __nv_bfloat16* __restrict__ hbuf1, float* __restrict__ out, unsigned* __restrict__ sync, long N, int T, int H) {
-    constexpr int RM = 16 * MW, THREADS = 32 * MW;
+template <int MW, int KS>
+__global__ void __launch_bounds__(32 * MW * KS)
+lstm_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, __nv_bfloat16* __restrict__ hbuf0,
+                __nv_bfloat16* __restrict__ hbuf1, float* __restrict__ c_state, float* __restrict__ out, unsigned* __restrict__ sync,
+                long N, int T, int H, int s_begin, int s_end) {
+    constexpr int RM = 16 * MW, SET = 32 * MW;
     extern __shared__ __align__(128) uint8_t lm_smem[];
     const int dir = blockIdx.z;
     const long n0 = (long)blockIdx.x * RM;
     const int j0 = blockIdx.y * 8;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int ks = warp / MW, mt = warp - ks * MW, tl = tid - ks * SET;    // k set, m tile, thread index inside the set
     const long plane_h = N * (long)H, plane_w = 4L * H * H;
     const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
     const int pitch = H * 2;
     const uint32_t sA = (uint32_t)__cvta_generic_to_shared(lm_smem);
     const uint32_t a_plane = RM * pitch, b_plane_b = 32 * pitch;
     const uint32_t sB = sA + 2 * a_plane;
-    const int ng = H >> 6;
-    constexpr int A_IT = 2 * RM * 8 / THREADS, B_IT = (2 * 32 * 8 + THREADS - 1) / THREADS;
+    const int ngl = (H >> 6) / KS;                           // 64-column groups of this set: g = i * KS + ks
+    // every thread copies the same (row, chunk-of-8) slots in each group: offsets are worked out once (the swizzle only touches
+    // the low three chunk bits, which a group offset leaves alone)
+    constexpr int A_IT = 2 * RM * 8 / SET, B_IT = (2 * 32 * 8 + SET - 1) / SET;
     long aoff[A_IT];                                         // element offset inside one h buffer
     uint32_t adst[A_IT];
-    const int c7 = tid & 7;
+    const int c7 = tl & 7;
 #pragma unroll
     for (int it = 0; it < A_IT; ++it) {
-        const int rs = (tid >> 3) + it * (THREADS / 8), p = rs / RM, r = rs - p * RM;
+        const int rs = (tl >> 3) + it * (SET / 8), p = rs / RM, r = rs - p * RM;
         long n = n0 + r;
-        if (n >= N) n = N - 1;
+        if (n >= N) n = N - 1;                               // rows past N are computed and dropped
         aoff[it] = (long)dir * 2 * plane_h + p * plane_h + n * H + c7 * 8;
         adst[it] = sA + p * a_plane + r * pitch + ((c7 ^ (r & 7)) << 4);
     }
-    const bool live = n0 + warp * 16 < N;
+    const bool live = n0 + mt * 16 < N;                      // warp-uniform: m-tiles entirely past N skip the products
+    const bool owner = live && ks == 0;                      // the warp that holds the cell state and writes h_t
     const int gid = lane >> 2, q = lane & 3;
     const int j = j0 + 2 * q;
     const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
     const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
-    const uint32_t a_base = sA + (warp * 16 + a_row) * pitch;
+    const uint32_t a_base = sA + (mt * 16 + a_row) * pitch;
     const uint32_t b_base = sB + b_pl * b_plane_b + b_row * pitch;
     const unsigned ncta = gridDim.x * gridDim.y;             // CTAs of one direction
     unsigned* ctr = sync + dir;
     bool dead = false;
     LmCellIn cin[2];
-    cin[0].c = cin[1].c = make_float2(0.f, 0.f);
 #pragma unroll
-    for (int half = 0; half < 2; ++half) lm_x_load(cin[half], xproj, n0 + warp * 16 + gid + half * 8, N, T, dir ? T - 1 : 0, H, dir, j);
-    for (int s = 0; s < T; ++s) {
+    for (int half = 0; half < 2; ++half) {
+        long n = n0 + mt * 16 + gid + half * 8;
+        if (n >= N) n = N - 1;
+        cin[half].c = make_float2(0.f, 0.f);
+        if (owner) {
+            if (s_begin > 0) cin[half].c = *reinterpret_cast<const float2*>(c_state + ((long)dir * N + n) * H + j);
+            lm_x_load(cin[half], xproj, n, N, T, dir ? T - 1 - s_begin : s_begin, H, dir, j);
+        }
+    }
+    for (int s = s_begin; s < s_end; ++s) {
         const int t = dir ? (T - 1 - s) : s;
         const __nv_bfloat16* hp = (s & 1) ? hbuf1 : hbuf0;
         __nv_bfloat16* hn = ((s & 1) ? hbuf0 : hbuf1) + (long)dir * 2 * plane_h;
-        for (int g = 0; g < ng; ++g) {
+        for (int i = 0; i < ngl; ++i) {
+            const int g = i * KS + ks;
 #pragma unroll
             for (int it = 0; it < A_IT; ++it) lm_cp16(adst[it] + g * 128, hp + aoff[it] + g * 64);
-            if (s == 0) {
+            if (s == s_begin) {
 #pragma unroll
                 for (int it = 0; it < B_IT; ++it) {
-                    const int rs = (tid >> 3) + it * (THREADS / 8);
+                    const int rs = (tl >> 3) + it * (SET / 8);
                     if (rs < 64) {
                         const int p = rs >> 5, r = rs & 31;  // r = gate * 8 + unit
                         lm_cp16(sB + p * b_plane_b + r * pitch + ((c7 ^ (r & 7)) << 4) + g * 128,
@@ -547,25 +469,32 @@ lstm_seq_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __rest
         for (int g = 0; g < 4; ++g)
 #pragma unroll
             for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
-        for (int g = 0; g < ng; ++g) {
-            switch (ng - 1 - g) {
-                case 0: asm volatile("cp.async.wait_group 0;" ::: "memory"); break;
-                case 1: asm volatile("cp.async.wait_group 1;" ::: "memory"); break;
-                case 2: asm volatile("cp.async.wait_group 2;" ::: "memory"); break;
-                case 3: asm volatile("cp.async.wait_group 3;" ::: "memory"); break;
-                case 4: asm volatile("cp.async.wait_group 4;" ::: "memory"); break;
-                case 5: asm volatile("cp.async.wait_group 5;" ::: "memory"); break;
-                case 6: asm volatile("cp.async.wait_group 6;" ::: "memory"); break;
-                default: asm volatile("cp.async.wait_group 7;" ::: "memory"); break;
+        for (int i = 0; i < ngl; ++i) {
+            lm_wait_groups(ngl - 1 - i);
+            if (KS == 1) __syncthreads();
+            else asm volatile("bar.sync %0, %1;" ::"r"(1 + ks), "n"(SET) : "memory");
+            if (live) lm_group_mma(acc, (i * KS + ks) * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
+        }
+        if (KS > 1) {                                        // partial sums of set 1 -> set 0, through the h tile
+            float4* part = reinterpret_cast<float4*>(lm_smem);
+            __syncthreads();                                 // both sets are done reading the h tile
+            if (live && ks == 1) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) part[g * SET + tl] = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
             }
             __syncthreads();
-            if (!live) continue;
-            lm_group_mma(acc, g * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
+            if (owner) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    const float4 v = part[g * SET + tl];
+                    acc[g][0] += v.x; acc[g][1] += v.y; acc[g][2] += v.z; acc[g][3] += v.w;
+                }
+            }
         }
-        if (live) {
+        if (owner) {
 #pragma unroll
             for (int half = 0; half < 2; ++half) {
-                const long n = n0 + warp * 16 + gid + half * 8;
+                const long n = n0 + mt * 16 + gid + half * 8;
                 if (n >= N) continue;
                 const LmCellIn& in = cin[half];
                 const float ai0 = acc[0][2 * half], ai1 = acc[0][2 * half + 1], af0 = acc[1][2 * half], af1 = acc[1][2 * half + 1];
@@ -583,16 +512,18 @@ lstm_seq_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __rest
                 *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
             }
         }
-        if (s + 1 == T) break;
+        if (s + 1 == s_end) break;
+        if (owner) {
 #pragma unroll
-        for (int half = 0; half < 2; ++half)
-            lm_x_load(cin[half], xproj, n0 + warp * 16 + gid + half * 8, N, T, dir ? (T - 2 - s) : (s + 1), H, dir, j);
-        __syncthreads();                                     // this CTA's h_t stores are issued, its reads of the h_{t-1} tile are done
+            for (int half = 0; half < 2; ++half)
+                lm_x_load(cin[half], xproj, n0 + mt * 16 + gid + half * 8, N, T, dir ? (T - 2 - s) : (s + 1), H, dir, j);
+        }
+        __syncthreads();                                     // this CTA's h_t stores are issued, its reads of the h tile are done
         if (tid == 0) {
             __threadfence();
             atomicAdd(ctr, 1u);
             if (!dead) {
-                const unsigned target = (unsigned)(s + 1) * ncta;
+                const unsigned target = (unsigned)(s - s_begin + 1) * ncta;
                 const long long t0 = clock64();
                 unsigned v;
                 for (;;) {
@@ -605,8 +536,16 @@ lstm_seq_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __rest
         }
         __syncthreads();
     }
+    if (owner && s_end < T) {                                // the next launch continues from here
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const long n = n0 + mt * 16 + gid + half * 8;
+            if (n < N) *reinterpret_cast<float2*>(c_state + ((long)dir * N + n) * H + j) = cin[half].c;
+        }
+    }
 }
 
+constexpr int LM_RES_MW = 5;
 static int lstm_seq_res_ok(long N, int H) {                  // 1: the whole grid fits the device at once
     static int sms = 0, coop = 0;
     if (!sms) {
@@ -618,20 +557,33 @@ static int lstm_seq_res_ok(long N, int H) {                  // 1: the whole gri
     return coop && H % 64 == 0 && H <= 512 && N <= 16 * LM_RES_MW && 2 * (H / 8) <= sms;
 }
 
-int lstm_seq_res_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* y, unsigned* sync,
-                        long N, int T, int H, cudaStream_t st) {
+// steps [s_begin, s_end) of one layer; more than one step per launch needs lstm_seq_res_ok (cooperative launch, zeroed `sync`)
+template <int KS>
+int lstm_res_launch_ks(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* cs, float* y, unsigned* sync,
+                       long N, int T, int H, int s_begin, int s_end, cudaStream_t st) {
     int smem = 2 * (16 * LM_RES_MW + 32) * H * 2;
     static int attr_smem = 0;
     if (smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(lstm_seq_res_kernel<LM_RES_MW>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-        CSS_REQUIRE(e == cudaSuccess, "lstm_seq_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+        cudaError_t e = cudaFuncSetAttribute(lstm_res_kernel<LM_RES_MW, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        CSS_REQUIRE(e == cudaSuccess, "lstm_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
         attr_smem = smem;
     }
-    dim3 grid(1, H / 8, 2);
-    void* args[] = {(void*)&xp, (void*)&whh, (void*)&h0, (void*)&h1, (void*)&y, (void*)&sync, (void*)&N, (void*)&T, (void*)&H};
-    cudaError_t e = cudaLaunchCooperativeKernel((const void*)lstm_seq_res_kernel<LM_RES_MW>, grid, dim3(32 * LM_RES_MW), args, (size_t)smem, st);
-    CSS_REQUIRE(e == cudaSuccess, "lstm_seq_res: cooperative launch failed: %s", cudaGetErrorString(e));
+    dim3 grid((unsigned)((N + 16 * LM_RES_MW - 1) / (16 * LM_RES_MW)), H / 8, 2), block(32 * LM_RES_MW * KS);
+    if (s_end - s_begin == 1) {
+        lstm_res_kernel<LM_RES_MW, KS><<<grid, block, smem, st>>>(xp, whh, h0, h1, cs, y, sync, N, T, H, s_begin, s_end);
+        return 0;
+    }
+    void* args[] = {(void*)&xp, (void*)&whh, (void*)&h0, (void*)&h1, (void*)&cs, (void*)&y, (void*)&sync, (void*)&N, (void*)&T, (void*)&H,
+                    (void*)&s_begin, (void*)&s_end};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)lstm_res_kernel<LM_RES_MW, KS>, grid, block, args, (size_t)smem, st);
+    CSS_REQUIRE(e == cudaSuccess, "lstm_res: cooperative launch failed: %s", cudaGetErrorString(e));
     return 0;
+}
+int lstm_res_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* cs, float* y, unsigned* sync,
+                    long N, int T, int H, int s_begin, int s_end, cudaStream_t st) {
+    static const int ks_env = getenv("CSS_B200_LSTM_KS") ? atoi(getenv("CSS_B200_LSTM_KS")) : 2;      // tuning: 1 = one warp set
+    if (ks_env == 2 && (H >> 6) % 2 == 0) return lstm_res_launch_ks<2>(xp, whh, h0, h1, cs, y, sync, N, T, H, s_begin, s_end, st);
+    return lstm_res_launch_ks<1>(xp, whh, h0, h1, cs, y, sync, N, T, H, s_begin, s_end, st);
 }
 }  // namespace
 
@@ -775,8 +727,9 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         // few sequences: the T steps of the layer in one cooperative launch (0 = default; 1 forces the per-step launches)
         if (tc && (lm_tile == 0 || lm_tile == 3) && lstm_seq_res_ok(N, H)) {
             css_prof_begin(4, (double)T * 2.0 * 2.0 * (double)N * H * 4 * H, st);
-            rc = lstm_seq_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), y,
-                                     reinterpret_cast<unsigned*>(cs), N, T, H, st);   // cs (zeroed above) holds the step counters
+            cudaMemsetAsync(hd, 0, 16, st);                  // step counters (the head buffer is not in use yet)
+            rc = lstm_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), cs, y,
+                                 reinterpret_cast<unsigned*>(hd), N, T, H, 0, T, st);
             css_prof_end(st);
             if (rc || (rc = css_check_launch("lstm_seq"))) return rc;
             if ((rc = layernorm_launch(y, L.ln_g, L.ln_b, x, M, h, 1e-5f, 0, st))) return rc;
@@ -788,7 +741,7 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
                 __nv_bfloat16 *bp = reinterpret_cast<__nv_bfloat16*>(hp), *bn = reinterpret_cast<__nv_bfloat16*>(hn);
                 // measured on B200 (N = 747, H = 512): 64 x 64 CTAs 49 us per step, 128 x 128 CTAs 58 us (1.3 waves of one CTA per SM)
                 switch (lm_tile ? lm_tile : (N <= 160 && H <= 512 ? 1 : (N <= 192 ? 12 : 22))) {
-                    case 1: rc = lstm_step_res_launch(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
+                    case 1: rc = lstm_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), cs, y, nullptr, N, T, H, s, s + 1, st); break;
                     case 12: rc = lstm_step_mma_launch<1, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                     default: rc = lstm_step_mma_launch<2, 2>(xp, whh, bp, bn, cs, y, N, T, H, s, st); break;
                 }

@@ -190,7 +190,7 @@ int css_get_gemm_mode(void);
 /* Launch plan of the tensor-core BLSTM recurrence (blstm.py:156-160): 0 = chosen from (sequences, hidden size); 1 = one launch
  * per time step with operands resident in shared memory; 3 = all T steps of a layer in one cooperative launch (<= 80
  * sequences, falls back to 0 when the grid cannot be co-resident); 12 / 22 = streamed 32- / 64-sequence CTAs per step.
- * Initialised from CSS_B200_LSTM_TILE.  The plans compute identical bits; this exists for A/B timing and the parity test. */
+ * Initialised from CSS_B200_LSTM_TILE.  Plans 1 and 3 compute identical bits; this exists for A/B timing and the parity test. */
 int css_set_lstm_plan(int plan);
 int css_get_lstm_plan(void);
 
