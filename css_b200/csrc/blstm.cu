@@ -545,6 +545,168 @@ lstm_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict
     }
 }
 
+// Whole recurrence, two warp groups.  The sequences of a batch are independent recurrences, so nothing ties the m tiles of a
+// CTA to each other: group 0 (m tiles 0-1, rows 0-31) and group 1 (m tiles 2-4, rows 32-79) each have their rows of the h
+// tile, their two k sets, their named barriers and their own step counter per direction, and drift apart -- while one group
+// waits for its counter the other one multiplies, and the HMMAs of a group meet half the contention.  W_hh is copied once by
+// all threads before the groups separate.  Same arithmetic per (sequence, unit) as lstm_res_kernel<5, 2>: equal bits.
+__device__ __forceinline__ void lm_bar(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+__global__ void __launch_bounds__(320)
+lstm_res2_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict__ whh, __nv_bfloat16* __restrict__ hbuf0,
+                 __nv_bfloat16* __restrict__ hbuf1, float* __restrict__ out, unsigned* __restrict__ sync, long N, int T, int H) {
+    constexpr int RM = 80;
+    extern __shared__ __align__(128) uint8_t lm_smem[];
+    const int dir = blockIdx.z;
+    const long n0 = (long)blockIdx.x * RM;
+    const int j0 = blockIdx.y * 8;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int grp = warp >= 4;                               // warps 0-3: m tiles 0, 1; warps 4-9: m tiles 2, 3, 4
+    const int n_mt = grp ? 3 : 2, gw0 = grp ? 4 : 0, row0 = grp ? 32 : 0, rows = n_mt * 16;
+    const int wg = warp - gw0, ks = wg / n_mt, mt = (grp ? 2 : 0) + wg - ks * n_mt;
+    const int SETN = 32 * n_mt, GRPN = 2 * SETN;
+    const int tl = tid - (gw0 + ks * n_mt) * 32;             // thread index inside the k set
+    const int bar_grp = 1 + grp, bar_set = 3 + 2 * grp + ks;
+    const long plane_h = N * (long)H, plane_w = 4L * H * H;
+    const __nv_bfloat16* wp = whh + (long)dir * 2 * plane_w;
+    const int pitch = H * 2;
+    const uint32_t sA = (uint32_t)__cvta_generic_to_shared(lm_smem);
+    const uint32_t a_plane = RM * pitch, b_plane_b = 32 * pitch;
+    const uint32_t sB = sA + 2 * a_plane;
+    const int ngl = (H >> 6) / 2;                            // 64-column groups of this set: g = 2 i + ks
+    // W_hh slice of the CTA: 64 row-planes x H/8 chunks, once, by everybody
+    const int cpr = H >> 3;
+    for (int idx = tid; idx < 64 * cpr; idx += 320) {
+        const int rs = idx / cpr, c = idx - rs * cpr, p = rs >> 5, r = rs & 31;        // r = gate * 8 + unit
+        lm_cp16(sB + p * b_plane_b + r * pitch + (((c & 7) ^ (r & 7)) << 4) + (c >> 3) * 128,
+                wp + p * plane_w + ((long)(r >> 3) * H + j0 + (r & 7)) * H + c * 8);
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    long aoff[8];
+    uint32_t adst[8];
+    const int c7 = tl & 7;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+        const int rs = (tl + it * SETN) >> 3, p = rs / rows, r = row0 + rs - p * rows;
+        long n = n0 + r;
+        if (n >= N) n = N - 1;                               // rows past N are computed and dropped
+        aoff[it] = (long)dir * 2 * plane_h + p * plane_h + n * H + c7 * 8;
+        adst[it] = sA + p * a_plane + r * pitch + ((c7 ^ (r & 7)) << 4);
+    }
+    const bool live = n0 + mt * 16 < N;
+    const bool owner = live && ks == 0;
+    const int gid = lane >> 2, q = lane & 3;
+    const int j = j0 + 2 * q;
+    const int a_row = (lane & 7) + ((lane >> 3) & 1) * 8, a_c = lane >> 4;
+    const int b_row = lane & 7, b_pl = lane >> 4, b_c = (lane >> 3) & 1;
+    const uint32_t a_base = sA + (mt * 16 + a_row) * pitch;
+    const uint32_t b_base = sB + b_pl * b_plane_b + b_row * pitch;
+    const unsigned ncta = gridDim.x * gridDim.y;
+    unsigned* ctr = sync + dir * 2 + grp;
+    float4* part = reinterpret_cast<float4*>(lm_smem + row0 * pitch);      // inside this group's rows of the h tile
+    bool dead = false;
+    LmCellIn cin[2];
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+        cin[half].c = make_float2(0.f, 0.f);
+        if (owner) lm_x_load(cin[half], xproj, n0 + mt * 16 + gid + half * 8, N, T, dir ? T - 1 : 0, H, dir, j);
+    }
+    for (int s = 0; s < T; ++s) {
+        const int t = dir ? (T - 1 - s) : s;
+        const __nv_bfloat16* hp = (s & 1) ? hbuf1 : hbuf0;
+        __nv_bfloat16* hn = ((s & 1) ? hbuf0 : hbuf1) + (long)dir * 2 * plane_h;
+        for (int i = 0; i < ngl; ++i) {
+            const int g = i * 2 + ks;
+#pragma unroll
+            for (int it = 0; it < 8; ++it) lm_cp16(adst[it] + g * 128, hp + aoff[it] + g * 64);
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        }
+        float acc[4][4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc[g][i] = 0.f;
+        for (int i = 0; i < ngl; ++i) {
+            lm_wait_groups(ngl - 1 - i);
+            lm_bar(bar_set, SETN);
+            if (live) lm_group_mma(acc, (i * 2 + ks) * 8, a_base, a_plane, a_c, a_row, b_base, pitch, b_c, b_row);
+        }
+        lm_bar(bar_grp, GRPN);                               // both sets are done reading this group's rows of the h tile
+        if (live && ks == 1) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) part[g * SETN + tl] = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
+        }
+        lm_bar(bar_grp, GRPN);
+        if (owner) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const float4 v = part[g * SETN + tl];
+                acc[g][0] += v.x; acc[g][1] += v.y; acc[g][2] += v.z; acc[g][3] += v.w;
+            }
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const long n = n0 + mt * 16 + gid + half * 8;
+                if (n >= N) continue;
+                const LmCellIn& in = cin[half];
+                const float ai0 = acc[0][2 * half], ai1 = acc[0][2 * half + 1], af0 = acc[1][2 * half], af1 = acc[1][2 * half + 1];
+                const float ag0 = acc[2][2 * half], ag1 = acc[2][2 * half + 1], ao0 = acc[3][2 * half], ao1 = acc[3][2 * half + 1];
+                float2 c, h;                                  // same expressions as lm_cell_store
+                c.x = lm_sigmoid(af0 + in.xf.x) * in.c.x + lm_sigmoid(ai0 + in.xi.x) * lm_tanh(ag0 + in.xg.x);
+                c.y = lm_sigmoid(af1 + in.xf.y) * in.c.y + lm_sigmoid(ai1 + in.xi.y) * lm_tanh(ag1 + in.xg.y);
+                h.x = lm_sigmoid(ao0 + in.xo.x) * lm_tanh(c.x);
+                h.y = lm_sigmoid(ao1 + in.xo.y) * lm_tanh(c.y);
+                cin[half].c = c;
+                *reinterpret_cast<float2*>(out + (n * T + t) * (long)(2 * H) + (long)dir * H + j) = h;
+                const __nv_bfloat162 hi = __floats2bfloat162_rn(h.x, h.y);
+                const __nv_bfloat162 lo = __floats2bfloat162_rn(h.x - __bfloat162float(hi.x), h.y - __bfloat162float(hi.y));
+                *reinterpret_cast<__nv_bfloat162*>(hn + n * H + j) = hi;
+                *reinterpret_cast<__nv_bfloat162*>(hn + plane_h + n * H + j) = lo;
+            }
+        }
+        if (s + 1 == T) break;
+        if (owner) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half)
+                lm_x_load(cin[half], xproj, n0 + mt * 16 + gid + half * 8, N, T, dir ? (T - 2 - s) : (s + 1), H, dir, j);
+        }
+        lm_bar(bar_grp, GRPN);                               // the group's h_t stores are issued, its reads of the partial sums are done
+        if (wg == 0 && lane == 0) {
+            __threadfence();
+            atomicAdd(ctr, 1u);
+            if (!dead) {
+                const unsigned target = (unsigned)(s + 1) * ncta;
+                const long long t0 = clock64();
+                unsigned v;
+                for (;;) {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
+                    if (v >= target) break;
+                    if (clock64() - t0 > 2000000000LL) { dead = true; atomicExch(sync + 8, 1u); break; }
+                }
+            }
+            __threadfence();
+        }
+        lm_bar(bar_grp, GRPN);
+    }
+}
+
+int lstm_res2_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* y, unsigned* sync, long N, int T,
+                     int H, cudaStream_t st) {
+    int smem = 2 * (80 + 32) * H * 2;
+    static int attr_smem = 0;
+    if (smem > attr_smem) {
+        cudaError_t e = cudaFuncSetAttribute(lstm_res2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        CSS_REQUIRE(e == cudaSuccess, "lstm_res2: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
+        attr_smem = smem;
+    }
+    dim3 grid(1, H / 8, 2), block(320);
+    void* args[] = {(void*)&xp, (void*)&whh, (void*)&h0, (void*)&h1, (void*)&y, (void*)&sync, (void*)&N, (void*)&T, (void*)&H};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)lstm_res2_kernel, grid, block, args, (size_t)smem, st);
+    CSS_REQUIRE(e == cudaSuccess, "lstm_res2: cooperative launch failed: %s", cudaGetErrorString(e));
+    return 0;
+}
+
 constexpr int LM_RES_MW = 5;
 static int lstm_seq_res_ok(long N, int H) {                  // 1: the whole grid fits the device at once
     static int sms = 0, coop = 0;
@@ -727,9 +889,14 @@ extern "C" int css_blstm_forward(void* model, float* feat, long N, int T, int ap
         // few sequences: the T steps of the layer in one cooperative launch (0 = default; 1 forces the per-step launches)
         if (tc && (lm_tile == 0 || lm_tile == 3) && lstm_seq_res_ok(N, H)) {
             css_prof_begin(4, (double)T * 2.0 * 2.0 * (double)N * H * 4 * H, st);
-            cudaMemsetAsync(hd, 0, 16, st);                  // step counters (the head buffer is not in use yet)
-            rc = lstm_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), cs, y,
-                                 reinterpret_cast<unsigned*>(hd), N, T, H, 0, T, st);
+            cudaMemsetAsync(hd, 0, 64, st);                  // step counters (the head buffer is not in use yet)
+            static const int two_groups = getenv("CSS_B200_LSTM_GROUPS") ? atoi(getenv("CSS_B200_LSTM_GROUPS")) == 2 : 1;   // B200, 72 x 512: 3.47 -> 3.29 ms per 3 layers
+            if (two_groups && (H >> 6) % 2 == 0 && N > 32)
+                rc = lstm_res2_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), y,
+                                      reinterpret_cast<unsigned*>(hd), N, T, H, st);
+            else
+                rc = lstm_res_launch(xp, whh, reinterpret_cast<__nv_bfloat16*>(hs0), reinterpret_cast<__nv_bfloat16*>(hs1), cs, y,
+                                     reinterpret_cast<unsigned*>(hd), N, T, H, 0, T, st);
             css_prof_end(st);
             if (rc || (rc = css_check_launch("lstm_seq"))) return rc;
             if ((rc = layernorm_launch(y, L.ln_g, L.ln_b, x, M, h, 1e-5f, 0, st))) return rc;
