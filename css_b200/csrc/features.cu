@@ -4,7 +4,8 @@
 #include <cuda_bf16.h>
 
 #define FEAT_EPS 1.1920928955078125e-07f
-#define FEAT_THREADS 288   // 9 warps cover 257 bins
+#define FEAT_THREADS 96    // bins per CTA: three CTAs (3 warps each) cover the 257 bins of a chunk
+#define FEAT_SPLIT 3        // 2,241 short CTAs for a 10-min session instead of 747 long ones in 1.7 waves
 #define FEAT_TT 32         // time tile of the transposing mag store
 
 // unit phasor of a * conj(b); atan2(0,0) = 0 convention -> (1, 0) when a product vanishes
@@ -59,15 +60,16 @@ __device__ __forceinline__ float ipd_atan2(float y, float x) {
     return copysignf(r, y);
 }
 
-// One block per chunk; thread k owns bin k.  spec element (d, chunk b, frame t, bin k) lives at
+// FEAT_SPLIT blocks per chunk; a thread owns one bin.  spec element (d, chunk b, frame t, bin k) lives at
 // spec[(d*stride_d + b*stride_chunk + t) * CSS_KP + k].
-__global__ void __launch_bounds__(FEAT_THREADS, 3)
+__global__ void __launch_bounds__(FEAT_THREADS, 9)
 features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T,
                 const int* __restrict__ ipd_l, const int* __restrict__ ipd_r, int n_pairs,
                 float* __restrict__ mag, float* __restrict__ feat, int ldf) {
-    __shared__ float tile[FEAT_TT][CSS_NBINS + 1];
+    __shared__ float tile[FEAT_TT][FEAT_THREADS + 1];
     const long b = blockIdx.x;
-    const int k = threadIdx.x;
+    const int k0 = blockIdx.y * FEAT_THREADS, k = k0 + threadIdx.x;
+    const int nb = min(FEAT_THREADS, CSS_NBINS - k0);         // bins of this CTA
     const bool act = k < CSS_NBINS;
     const float2* base = spec + (b * stride_chunk) * CSS_KP + k;
 
@@ -136,7 +138,7 @@ features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chun
                     if (p < n_pairs) xl[p] = pl[p][o];
                 if (same_r && n_pairs > 0) xr0 = pr[0][o];
                 float m = sqrtf(x0.x * x0.x + x0.y * x0.y);
-                tile[tt][k] = m;
+                tile[tt][threadIdx.x] = m;
                 float* fr = frow + (long)t * ldf + k;
                 fr[0] = (fmaxf(m, FEAT_EPS) - m_mean) * inv;
 #pragma unroll
@@ -148,14 +150,15 @@ features_kernel(const float2* __restrict__ spec, long stride_d, long stride_chun
             }
         __syncthreads();
         // mag[b][bin][t]: consecutive threads walk t inside a bin row
-        for (int i = threadIdx.x; i < CSS_NBINS * tn; i += blockDim.x) {
+        for (int i = threadIdx.x; i < nb * tn; i += blockDim.x) {
             const int bin = i / tn, tt = i - bin * tn;
-            mrow[(long)bin * T + t0 + tt] = tile[tt][bin];
+            mrow[(long)(k0 + bin) * T + t0 + tt] = tile[tt][bin];
         }
         __syncthreads();
     }
     // zero the K padding of the feature rows
     const int F = CSS_NBINS * (n_pairs + 1);
+    if (blockIdx.y == 0)
     for (int i = threadIdx.x; i < T * (ldf - F); i += blockDim.x) {
         const int t = i / (ldf - F), c = i - t * (ldf - F);
         frow[(long)t * ldf + F + c] = 0.f;
@@ -187,7 +190,7 @@ extern "C" int css_features(const void* spec, long stride_d, long stride_chunk, 
     CSS_REQUIRE(n_pairs >= 0 && n_pairs <= 8, "css_features: at most 8 IPD pairs supported, got %d", n_pairs);
     CSS_REQUIRE(ldf >= CSS_NBINS * (n_pairs + 1), "css_features: feature pitch %d too small", ldf);
     CssProfScope prof(6, (double)n_chunks * T * CSS_NBINS * ((n_pairs ? 7 : 1) * 8.0 + (n_pairs + 1) * 4.0 + 4.0), st);
-    features_kernel<<<(unsigned)n_chunks, FEAT_THREADS, 0, st>>>((const float2*)spec, stride_d, stride_chunk, T, ipd_l,
+    features_kernel<<<dim3((unsigned)n_chunks, FEAT_SPLIT), FEAT_THREADS, 0, st>>>((const float2*)spec, stride_d, stride_chunk, T, ipd_l,
                                                                  ipd_r, n_pairs, mag, feat, ldf);
     return css_check_launch("css_features");
 }
