@@ -48,12 +48,21 @@ def require_cuda(t, name="tensor"):
     return t
 
 
+class DevPtr(ctypes.c_void_p):
+    """A device pointer that remembers which GPU it lives on, so that ``call`` can launch on that GPU."""
+
+    device = None
+
+
 def ptr(t):
-    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+    p = DevPtr(0 if t is None else t.data_ptr())
+    if t is not None and t.is_cuda:
+        p.device = t.device.index
+    return p
 
 
-def stream():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+def stream(device=None):
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
 def check(rc, what=""):
@@ -63,9 +72,20 @@ def check(rc, what=""):
 
 
 def call(name, *args):
-    """Call an `int css_xxx(...)` entry point, appending the current stream, raising on error."""
+    """Call an `int css_xxx(...)` entry point, appending the current stream, raising on error.
+
+    The kernels are launched on the device that owns the tensors (all pointer arguments must live on one GPU), on that
+    device's current stream -- not on whatever device happens to be current in the calling thread."""
     fn = getattr(lib(), name)
-    check(fn(*args, stream()), name)
+    devs = {a.device for a in args if isinstance(a, DevPtr) and a.device is not None}
+    if len(devs) > 1:
+        raise NativeError(f"{name}: tensors live on different GPUs {sorted(devs)}")
+    dev = devs.pop() if devs else torch.cuda.current_device()
+    if dev == torch.cuda.current_device():
+        check(fn(*args, stream()), name)
+    else:
+        with torch.cuda.device(dev):
+            check(fn(*args, stream(dev)), name)
 
 
 def set_gemm_mode(mode):

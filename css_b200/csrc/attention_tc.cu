@@ -377,13 +377,12 @@ int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_pl
                                   attention_tc_kernel<false, true, 20>,  attention_tc_kernel<false, true, 19>,
                                   attention_tc_kernel<true, false, 20>,  attention_tc_kernel<true, false, 19>,
                                   attention_tc_kernel<true, true, 20>,   attention_tc_kernel<true, true, 19>};
-    static bool attr = false;
-    if (!attr) {
+    static CssPerDevice attr;
+    if (attr.first()) {
         for (int i = 0; i < 8; ++i) {
             cudaError_t e = cudaFuncSetAttribute(kerns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
             CSS_REQUIRE(e == cudaSuccess, "attention_tc: cannot reserve %d B of shared memory: %s", SMEM_BYTES, cudaGetErrorString(e));
         }
-        attr = true;
     }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

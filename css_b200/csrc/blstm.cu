@@ -308,11 +308,10 @@ template <int WM, int WN>
 int lstm_step_mma_launch(const float* xp, const __nv_bfloat16* whh, const __nv_bfloat16* hp, __nv_bfloat16* hn, float* cs, float* y,
                          long N, int T, int H, int s, cudaStream_t st) {
     using C = LmCfg<WM, WN>;
-    static bool attr = false;
-    if (!attr) {
+    static CssPerDevice attr;
+    if (attr.first()) {
         cudaError_t e = cudaFuncSetAttribute(lstm_step_mma_kernel<WM, WN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "lstm_step_mma: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
-        attr = true;
     }
     dim3 grid((unsigned)((N + C::BM - 1) / C::BM), H / C::JB, 2);
     lstm_step_mma_kernel<WM, WN><<<grid, C::THREADS, C::SMEM, st>>>(xp, whh, hp, hn, cs, y, N, T, H, s);
@@ -362,7 +361,8 @@ __device__ __forceinline__ void lm_group_mma(float (&acc)[4][4], int c_first, ui
 // after every step (release: bar.sync + fence + atomic add by thread 0; acquire: relaxed spin + fence + bar.sync); the two
 // directions never wait for each other.  The gate pre-activations of the next step are requested before the spin.  All CTAs
 // must be co-resident: cooperative launch, grid <= one CTA per SM (checked by the host, which otherwise keeps the per-step
-// launches).  A spin that sees no progress for ~1 s gives up and raises sync[2] (results are then wrong, the GPU is not hung).
+// launches).  A spin that sees no progress for ~1 s (a lost co-residency guarantee: preemption, a debugger) traps: the launch
+// fails with a CUDA error at the next synchronisation instead of hanging the GPU or returning masks computed from stale h.
 //
 // KS = 2: two sets of MW warps, set k owns the 64-column groups g = k (mod 2) -- it copies them, waits for them behind its own
 // named barrier and multiplies them -- so every scheduler carries 2-3 warps instead of 1-2 (five warps on four schedulers left
@@ -529,7 +529,7 @@ lstm_res_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restrict
                 for (;;) {
                     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");   // the fence below orders the h loads
                     if (v >= target) break;
-                    if (clock64() - t0 > 2000000000LL) { dead = true; atomicExch(sync + 2, 1u); break; }
+                    if (clock64() - t0 > 2000000000LL) { atomicExch(sync + 2, 1u); __trap(); }   // fail loudly (below)
                 }
             }
             __threadfence();
@@ -682,7 +682,7 @@ lstm_res2_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restric
                 for (;;) {
                     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(ctr) : "memory");
                     if (v >= target) break;
-                    if (clock64() - t0 > 2000000000LL) { dead = true; atomicExch(sync + 8, 1u); break; }
+                    if (clock64() - t0 > 2000000000LL) { atomicExch(sync + 8, 1u); __trap(); }
                 }
             }
             __threadfence();
@@ -694,7 +694,8 @@ lstm_res2_kernel(const float* __restrict__ xproj, const __nv_bfloat16* __restric
 int lstm_res2_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* y, unsigned* sync, long N, int T,
                      int H, cudaStream_t st) {
     int smem = 2 * (80 + 32) * H * 2;
-    static int attr_smem = 0;
+    static int attr_smem_dev[CSS_MAX_DEVICES] = {};
+    int& attr_smem = attr_smem_dev[css_device()];
     if (smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(lstm_res2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         CSS_REQUIRE(e == cudaSuccess, "lstm_res2: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));
@@ -709,10 +710,10 @@ int lstm_res2_launch(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h
 
 constexpr int LM_RES_MW = 5;
 static int lstm_seq_res_ok(long N, int H) {                  // 1: the whole grid fits the device at once
-    static int sms = 0, coop = 0;
+    static int sms_dev[CSS_MAX_DEVICES] = {}, coop_dev[CSS_MAX_DEVICES] = {};
+    const int dev = css_device();
+    int &sms = sms_dev[dev], &coop = coop_dev[dev];
     if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     }
@@ -724,7 +725,8 @@ template <int KS>
 int lstm_res_launch_ks(const float* xp, const __nv_bfloat16* whh, __nv_bfloat16* h0, __nv_bfloat16* h1, float* cs, float* y, unsigned* sync,
                        long N, int T, int H, int s_begin, int s_end, cudaStream_t st) {
     int smem = 2 * (16 * LM_RES_MW + 32) * H * 2;
-    static int attr_smem = 0;
+    static int attr_smem_dev[CSS_MAX_DEVICES] = {};
+    int& attr_smem = attr_smem_dev[css_device()];
     if (smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(lstm_res_kernel<LM_RES_MW, KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         CSS_REQUIRE(e == cudaSuccess, "lstm_res: cannot reserve %d B of shared memory: %s", smem, cudaGetErrorString(e));

@@ -25,6 +25,24 @@ struct CssProfScope {
     ~CssProfScope() { css_prof_end(st); }
 };
 
+// Function attributes (the > 48 KB shared-memory opt-in) and SM counts are per DEVICE: caches are keyed by the current
+// device ordinal so that a second GPU in the same process gets its own setup.
+#define CSS_MAX_DEVICES 64
+static inline int css_device() {
+    int d = 0;
+    cudaGetDevice(&d);
+    return d & (CSS_MAX_DEVICES - 1);
+}
+struct CssPerDevice {
+    bool done[CSS_MAX_DEVICES] = {};
+    bool first() {
+        const int d = css_device();
+        if (done[d]) return false;
+        done[d] = true;
+        return true;
+    }
+};
+
 #define CSS_REQUIRE(cond, ...)            \
     do {                                  \
         if (!(cond)) {                    \

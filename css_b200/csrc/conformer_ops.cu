@@ -245,10 +245,9 @@ int attention_launch(const float* qkv, const float* pe, int pe_rows, float* out,
     const int v_smem = attention_smem_bytes(T, 1) <= 227 * 1024;
     const size_t smem = attention_smem_bytes(T, v_smem);
     CSS_REQUIRE(smem <= 227 * 1024, "attention: T=%d needs %zu B of shared memory", T, smem);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(relpos_attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        attr_set = true;
     }
     css_prof_begin(1, 6.0 * (double)N * H * T * T * ATT_DK, st);   // QK^T + Q.PE^T + PV
     relpos_attention_kernel<<<(unsigned)(N * H), ATT_WARPS * 32, smem, st>>>(qkv, pe, pe_rows, pe != nullptr, out, T, H, v_smem);
@@ -420,10 +419,9 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
     const long ctas = (long)pl.n_full * pl.full_tiles + (N - pl.n_full) * pl.tail_tiles;
     CSS_REQUIRE(ctas < (1L << 31), "conv_module: too many sequences (%ld)", N);
     const size_t smem = sizeof(float) * (size_t)(pl.full_len + 2 * CM_HALO) * CM_D;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_MAX_ROWS * CM_D * 4);
-        attr_set = true;
     }
     css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
     conv_module_kernel<<<(unsigned)ctas, CM_THREADS, smem, st>>>(x, out, T, pl, p);

@@ -248,10 +248,9 @@ int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* p
     CSS_REQUIRE(n > 0 && T > 1 && F > 0 && ld >= F && ldp >= F, "mvn_time_planes: bad shape");
     CSS_REQUIRE(T <= 512, "mvn_time_planes: T=%d exceeds the shared-memory tile (512 frames)", T);
     const size_t smem = sizeof(float) * (size_t)T * MVN_F;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(mvn_time_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 512 * MVN_F * 4);
-        attr_set = true;
     }
     dim3 grid((unsigned)n, (ldp + MVN_F - 1) / MVN_F);
     CssProfScope prof(6, (double)n * T * (F * 4.0 + (double)ldp * 2.0 * n_planes), st);

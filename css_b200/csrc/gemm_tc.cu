@@ -914,10 +914,10 @@ static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld
 }
 
 int sm_count() {
-    static int n = 0;
+    static int n_dev[CSS_MAX_DEVICES] = {};
+    const int dev = css_device();
+    int& n = n_dev[dev];
     if (!n) {
-        int dev = 0;
-        cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
         if (n <= 0) n = 148;
     }
@@ -970,15 +970,14 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
                     "gemm_tc: fused LayerNorm needs N == 256, fp32 + %d-plane outputs, no activation", P);
         em = 4;
     }
-    static bool attr = false;
-    if (!attr) {
+    static CssPerDevice attr;
+    if (attr.first()) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc2_kernel<P, BK, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
-        attr = true;
     }
     const long tiles = ((M + 2 * BM - 1) / (2 * BM)) * (N / C::BN);
     const int pairs = (int)(tiles < sm_count() / 2 ? tiles : sm_count() / 2);
@@ -999,14 +998,13 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
     if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
     const bool train = ep.mask != nullptr || ep.ksplit > 1;
     const int em = epilogue_mode(ep, P, N, train);
-    static bool attr = false;
-    if (!attr) {
+    static CssPerDevice attr;
+    if (attr.first()) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
-        attr = true;
     }
     const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (ep.ksplit > 1 ? ep.ksplit : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());

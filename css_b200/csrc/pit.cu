@@ -48,6 +48,14 @@ pit_pairwise_kernel(const float* __restrict__ est, const float* __restrict__ tgt
     }
 }
 
+// torch.min ordering over the stacked candidate losses (css/objectives/pit.py:52-56): NaN is the minimum and the first
+// NaN wins; otherwise the smaller loss, first index on ties.
+__device__ __forceinline__ bool pit_better(float l, int p, float best, int best_idx) {
+    if (isnan(l)) return !isnan(best) || p < best_idx;
+    if (isnan(best)) return false;
+    return l < best || (l == best && p < best_idx);
+}
+
 // one warp per utterance
 __global__ void __launch_bounds__(32)
 pit_search_kernel(const double* __restrict__ pair, int K, long n, float* __restrict__ loss, int* __restrict__ perm_out) {
@@ -63,16 +71,17 @@ pit_search_kernel(const double* __restrict__ pair, int K, long n, float* __restr
         double s = 0.0;
         for (int k = 0; k < K; ++k) s += pair[(b * K + perm[k]) * K + k];   // estimate[perm[k]] vs target[k]
         const float l = (float)(s / (double)(K * n));
-        if (l < best || (l == best && p < best_idx)) { best = l; best_idx = p; }
+        if (pit_better(l, p, best, best_idx)) { best = l; best_idx = p; }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const float ob = __shfl_xor_sync(0xffffffffu, best, o);
         const int oi = __shfl_xor_sync(0xffffffffu, best_idx, o);
-        if (ob < best || (ob == best && oi < best_idx)) { best = ob; best_idx = oi; }
+        if (pit_better(ob, oi, best, best_idx)) { best = ob; best_idx = oi; }
     }
     if (lane == 0) {
         int perm[PIT_MAXK];
+        if (best_idx < 0 || best_idx >= nperm) best_idx = 0;     // unreachable (every lane < nperm competes); keeps perm[] defined
         nth_perm(best_idx, K, perm);
         loss[b] = best;
         for (int k = 0; k < K; ++k) perm_out[b * K + k] = perm[k];

@@ -129,10 +129,9 @@ extern "C" int css_doa_merge(const void* spec, long stride_d, long stride_chunk,
     CSS_REQUIRE(lo >= 0 && hi <= CSS_NBINS && nf > 0, "css_doa_merge: bad band [%d,%d)", lo, hi);
     const size_t smem = sizeof(float2) * DOA_A * DOA_M * nf;
     CSS_REQUIRE(smem <= 200 * 1024, "css_doa_merge: band of %d bins needs too much shared memory", nf);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(doa_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
     }
     CssProfScope prof(7, (double)n_chunks * T * (CSS_NBINS * C * 4.0 + 7.0 * (hi - lo) * 8.0), st);
     doa_merge_kernel<<<(unsigned)n_chunks, 256, smem, st>>>((const float2*)spec, stride_d, stride_chunk, T,

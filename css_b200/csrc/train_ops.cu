@@ -362,10 +362,9 @@ int conv_train_fwd_launch(const float* x, float* out, float* cpre, float* bnsave
     int tile_len;
     const int n_tiles = conv_tiles(T, 188, &tile_len);
     const size_t smem = sizeof(float) * (size_t)(tile_len + 2 * CT_HALO) * CT_D;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(conv_train_pre_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * CT_D * 4);
-        attr_set = true;
     }
     cudaMemsetAsync(stats, 0, 2 * CT_D * sizeof(double), st);
     dim3 grid((unsigned)N, n_tiles);
@@ -508,10 +507,9 @@ int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave
     int rc = css_check_launch("conv_bwd_stats");
     if (rc) return rc;
     const size_t smem = sizeof(float) * 2 * (size_t)(CB_TILE + 2 * CT_HALO) * CT_D;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static CssPerDevice attr_set;
+    if (attr_set.first()) {
         cudaFuncSetAttribute(conv_bwd_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
     }
     dim3 grid((unsigned)N, (T + CB_TILE - 1) / CB_TILE);
     conv_bwd_dw_kernel<<<grid, 512, smem, st>>>(x, cpre, bnsave, g, bstats, 1.f / (float)M, du, T, p, gr);

@@ -125,6 +125,12 @@ class ConformerTrainEngine:
             self.bn_running[i, 1].copy_(blk.conv.BN.running_var)
             blk.conv.BN.running_mean.data = self.bn_running[i, 0]
             blk.conv.BN.running_var.data = self.bn_running[i, 1]
+        # BatchNorm1d.num_batches_tracked (a state_dict entry of the reference model): one vector, advanced once per
+        # train-mode forward
+        self.bn_tracked = torch.zeros(max(1, len(enc.encoders)), dtype=torch.long, device=dev)
+        for i, blk in enumerate(enc.encoders):
+            self.bn_tracked[i] = blk.conv.BN.num_batches_tracked.to(dev)
+            blk.conv.BN.num_batches_tracked.data = self.bn_tracked[i]
         self.desc, self.blocks = desc, blocks
         self.handle = self.lib.css_trainer_create(ctypes.byref(desc), blocks, nv.ptr(self.flat_p), nv.ptr(self.flat_g),
                                                   nv.ptr(self.bn_running))
@@ -184,7 +190,26 @@ class ConformerTrainEngine:
         head = torch.empty(N * T, d.num_bins * d.num_out, dtype=torch.float32, device=feat.device) if want_masks else None
         nv.call("css_trainer_forward", ctypes.c_void_p(self.handle), nv.ptr(feat), nv.c_long(N), nv.c_int(T), nv.ptr(y_pred),
                 nv.ptr(head), nv.c_int(0 if head is None else head.stride(0)), nv.ptr(ws), nv.c_size_t(ws.numel()))
+        self.bn_tracked += 1
         return y_pred, head
+
+    def enable_data_parallel(self, optim=None, group=None, buckets=4):
+        """Data-parallel training over ``torch.distributed``: rank 0's parameters and BatchNorm running
+        statistics are broadcast, the flat gradient is sum-all-reduced in ``buckets`` layer groups while the backward is
+        still running (``GradientExchange``), and the mean is folded into the optimiser (``grad_scale = 1/world``)."""
+        import torch.distributed as dist
+
+        from .optim import GradientExchange
+
+        if not dist.is_initialized() or dist.get_world_size(group) == 1:
+            return None
+        dist.broadcast(self.flat_p, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        dist.broadcast(self.bn_running, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        self.exchange = GradientExchange(self, buckets=buckets, group=group)
+        if optim is not None:
+            optim.grad_scale = 1.0 / self.exchange.world
+        self.model.invalidate()
+        return self.exchange
 
     def backward_part(self, feat, grad_y, hi, lo):
         N, T = self.ws_shape

@@ -3,8 +3,9 @@
 Same signature and control flow as the reference; the differences are under the hood:
 forward/backward are the native Conformer train kernels (bf16 tensor-core GEMMs when ``args.fp16`` -- the reference's
 AMP switch -- selects GEMM mode 2, split-bf16 fp32-class GEMMs otherwise), the gradient norm / clip / Adam update are the
-fused flat-buffer kernels of ``FusedAdam``, and with ``torch.distributed`` initialised the gradients are all-reduced
-over NCCL while the backward is still running.  Loss and gradient norm are logged without stalling the device every
+fused flat-buffer kernels of ``FusedAdam``, and with ``torch.distributed`` initialised ``engine.enable_data_parallel``
+is switched on (parameters broadcast from rank 0, gradients all-reduced over NCCL while the backward is still running,
+the mean folded into the optimiser).  Loss and gradient norm are logged without stalling the device every
 iteration: they are read back once per epoch.
 """
 import logging
@@ -16,22 +17,30 @@ from .. import _native as nv
 
 def train_one_epoch(args, generator, model, objective, optim, lr_sched, device="cuda"):
     engine = model.train_engine()
+    if getattr(engine, "exchange", None) is None and torch.distributed.is_available() and torch.distributed.is_initialized():
+        engine.enable_data_parallel(optim)        # broadcast from rank 0, bucketed all-reduce, grad_scale = 1/world
     exch = getattr(engine, "exchange", None)
-    if getattr(args, "gpu", True) and getattr(args, "fp16", False):
-        nv.set_gemm_mode(2)
+    # args.fp16 (the reference's AMP switch) selects single-plane bf16 GEMMs for the TRAINING forward/backward only: the
+    # reference scopes autocast to the training forward and validates in fp32, so the mode is restored on the way out
+    saved_mode = nv.get_gemm_mode()
     losses, norms = [], []
-    for i in range(1, args.batches_per_epoch + 1):
-        b = next(generator)
-        loss = objective(model, b, device=device)
-        loss.backward()
-        if exch is not None:
-            exch.finish()
-        norms.append(optim.clip_grad_norm_(args.grad_thresh))
-        optim.step()
-        optim.zero_grad()
-        lr_sched.step(1.0)
-        losses.append(loss.detach())
-        del b
+    try:
+        if getattr(args, "gpu", True) and getattr(args, "fp16", False):
+            nv.set_gemm_mode(2)
+        for i in range(1, args.batches_per_epoch + 1):
+            b = next(generator)
+            loss = objective(model, b, device=device)
+            loss.backward()
+            if exch is not None:
+                exch.finish()
+            norms.append(optim.clip_grad_norm_(args.grad_thresh))
+            optim.step()
+            optim.zero_grad()
+            lr_sched.step(1.0)
+            losses.append(loss.detach())
+            del b
+    finally:
+        nv.set_gemm_mode(saved_mode)
     losses = torch.stack(losses).cpu()
     norms = torch.stack(norms).cpu()
     for i, (l, n) in enumerate(zip(losses.tolist(), norms.tolist()), 1):

@@ -51,6 +51,12 @@ class FusedAdam:
     def zero_grad(self, set_to_none=False):
         self.engine.zero_grad()
 
+    @property
+    def state(self):
+        """torch.optim-style ``optimizer.state`` (scripts/python/train.py:219-222 walks it after a resume to move the
+        moment tensors to the GPU): one entry for the flat buffer."""
+        return {"flat": {"step": self.steps, "exp_avg": self.m, "exp_avg_sq": self.v}}
+
     def state_dict(self):
         return {"steps": self.steps, "m": self.m, "v": self.v,
                 "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}

@@ -402,9 +402,9 @@ def souden_mvdr(mix, target_scm, noise_scm, ref_mic=0, eps=1e-8):
 # Beamformer  (css/executor/beamformer.py)
 # --------------------------------------------------------------------------------------
 def centered_stft(x, n_fft=512, hop=256):
-    """css/executor/beamformer.py:137-145."""
+    """css/executor/beamformer.py:137-145.  (dtype follows x: float64 input gives the complex128 bracket chain.)"""
     return torch.stft(x, n_fft=n_fft, hop_length=hop, center=True, onesided=True,
-                      window=torch.hann_window(n_fft), return_complex=True)
+                      window=torch.hann_window(n_fft, dtype=x.dtype), return_complex=True)
 
 
 def normalize_scale(result, ch0, mask):
@@ -465,8 +465,15 @@ def placement_plan(n_chunks, T, hop, margin, wav_len, batch_size):
     return plan
 
 
-def continuous_process(X, masks, cfg, sr=16000, rescale=True):
-    """css/executor/beamformer.py:32-124.  X (D,T); masks 3x(F,L) -> two (1,T) waveforms."""
+def continuous_process(X, masks, cfg, sr=16000, rescale=True, dtype=None):
+    """css/executor/beamformer.py:32-124.  X (D,T); masks 3x(F,L) -> two (1,T) waveforms.
+
+    ``dtype=torch.float64`` runs the same chain (STFT, covariances, solve, apply, rescale, dedup, iSTFT, placement) in
+    float64 / complex128 on the given fp32 inputs: the "exact" answer the fp32 implementations are bracketed against.
+    """
+    if dtype is not None:
+        X = X.to(dtype)
+        masks = tuple(m.to(dtype) for m in masks)
     n_fft, hop_len = cfg["n_fft"], cfg["hop_size"]
     win, hop = int(cfg["eval_win"] * sr), int(cfg["eval_hop"] * sr)
     margin = cfg["proceed_margin"] * sr
@@ -475,8 +482,8 @@ def continuous_process(X, masks, cfg, sr=16000, rescale=True):
     D, T = X.shape
     Xc = X.unfold(-1, win + 256, hop).permute(1, 0, 2)
     m0, m1, mn = (m.unfold(1, mwin, mhop).permute(1, 0, 2) for m in masks)
-    res = torch.zeros(2, T)
-    window = torch.hann_window(n_fft)
+    res = torch.zeros(2, T, dtype=X.dtype)
+    window = torch.hann_window(n_fft, dtype=X.dtype)
     for i in range(math.ceil(Xc.shape[0] / bsz)):
         bs, be = i * bsz, min((i + 1) * bsz, Xc.shape[0]) + 1
         xb = Xc[bs:be]

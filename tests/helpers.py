@@ -78,3 +78,40 @@ def train_conformer(num_blocks=2, idim=1799, seed=3):
     conf = dict(CONF_C7, conformer_num_blocks=num_blocks, idim=idim, conformer_dropout_rate=0.0)
     torch.manual_seed(seed)
     return M.build_model("Conformer", conf).train()
+
+
+F_FLIP_SEED = 31
+
+
+def flip_set(n_chunks, seed=F_FLIP_SEED):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.rand(n_chunks, generator=g) < 0.4).tolist()
+
+
+def doa_case(seed=77):
+    """Constructed spectra X (4,7,257,150) c64 and masks (4,257,150,2) for case G (shared with the GPU test)."""
+    from oracle import css_oracle as O
+
+    sv, angles = O.steervec_7ch(257, 30)
+    g = torch.Generator().manual_seed(seed)
+    B, F, T = 4, 257, 150
+    pairs = [(3, 8), (10, 11), (20, 22), (5, 5)]            # steering-grid indices: 60, 12, 24 degrees apart; single
+    X = torch.zeros(B, 7, F, T, dtype=torch.complex64)
+    mask = torch.zeros(B, F, T, 2)
+    for b, (a0, a1) in enumerate(pairs):
+        own = torch.rand(F, T, generator=g) < 0.5            # TF bins of source 0; the rest belong to source 1
+        s0 = torch.randn(F, T, generator=g) + 1j * torch.randn(F, T, generator=g)
+        s1 = torch.randn(F, T, generator=g) + 1j * torch.randn(F, T, generator=g)
+        if b == 3:
+            # one source, no noise: X is exactly proportional to a steering vector -> radicand ~ 0 +- rounding
+            X[b] = (sv[:, a0, :].t().unsqueeze(-1) * s0.unsqueeze(0)).to(torch.complex64)
+            mask[b, :, :, 0] = own.float() * 0.9
+            mask[b, :, :, 1] = (~own).float() * 0.8
+            continue
+        d0 = sv[:, a0, :].t().unsqueeze(-1) * (s0 * own).unsqueeze(0)
+        d1 = sv[:, a1, :].t().unsqueeze(-1) * (s1 * ~own).unsqueeze(0)
+        noise = 0.05 * (torch.randn(7, F, T, generator=g) + 1j * torch.randn(7, F, T, generator=g))
+        X[b] = (d0 + d1 + noise).to(torch.complex64)
+        mask[b, :, :, 0] = torch.where(own, 0.9, 0.1) + 0.05 * torch.rand(F, T, generator=g)
+        mask[b, :, :, 1] = torch.where(own, 0.1, 0.9) - 0.05 * torch.rand(F, T, generator=g)
+    return X, mask, pairs

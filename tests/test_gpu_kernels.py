@@ -400,6 +400,28 @@ def test_pit_mse_golden_and_grad(cuda, golden):
         pit_loss(est[0].to(cuda), tgt[0, :, :10].to(cuda), axis=0)
 
 
+def test_pit_mse_nan_losses_follow_torch_min(cuda):
+    """Diverged training: torch.min over the stacked candidate losses (css/objectives/pit.py:52-56) returns NaN with the
+    index of the FIRST NaN candidate; the permutation stays a valid one and the loss is NaN (train.py skips the checkpoint
+    on np.isnan)."""
+    from css_b200.objectives.pit import pit_mse_batch
+
+    g = torch.Generator().manual_seed(12)
+    est = torch.rand(3, 2, 20, 257, generator=g)
+    tgt = torch.rand(3, 2, 20, 257, generator=g)
+    est[0, 0, 3, 5] = float("nan")            # every permutation of utterance 0 is NaN -> index 0 = (0, 1)
+    tgt[1] = est[1].flip(0)                   # utterance 1 is finite, swapped is best
+    est[2, 1, 0, 0] = float("inf")            # inf - finite: both candidates +inf -> first index
+    e = est.to(cuda).requires_grad_(True)
+    loss, perm, loss_b = pit_mse_batch(e, tgt.to(cuda))
+    loss.backward()
+    ref = [O.pit_loss(est[b], tgt[b], axis=0, return_permutation=True) for b in range(3)]
+    assert perm.cpu().tolist() == [list(r[1]) for r in ref] == [[0, 1], [1, 0], [0, 1]]
+    assert math.isnan(float(loss_b[0])) and math.isnan(float(ref[0][0]))
+    assert float(loss_b[1]) == pytest.approx(float(ref[1][0]), abs=1e-7)
+    assert math.isinf(float(loss_b[2])) and math.isnan(float(loss)) and torch.isfinite(e.grad[1]).all()
+
+
 def test_no_cpu_fallback(cuda):
     nv = _nv()
     from css_b200.executor.feature import FeatureExtractor, stft
