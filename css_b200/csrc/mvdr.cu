@@ -378,3 +378,48 @@ extern "C" int css_mvdr_finalize(void* Y, const float* energy, long n_chunks, in
     mvdr_finalize_kernel<<<grid, 256, 0, st>>>((float2*)Y, scal, T, rescale, dedup);
     return css_check_launch("css_mvdr_finalize");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Beamformer.normalize_scale as a stand-alone call (css/executor/beamformer.py:165-183):
+//   out[b] = result[b] * rms(mask[b] * ref[b]) / rms(result[b])   over the n = F*T elements of chunk b.
+// One CTA per chunk: both energies in one pass (fp32 terms, fp64 accumulation), then the scaled copy.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512)
+normalize_scale_kernel(const float2* __restrict__ result, const float2* __restrict__ ref, const float* __restrict__ mask, long n,
+                       float2* __restrict__ out) {
+    __shared__ double red[2][16];
+    __shared__ float gain_s;
+    const long b = blockIdx.x;
+    const float2* r = result + b * n;
+    const float2* x = ref + b * n;
+    const float* m = mask + b * n;
+    double ey = 0.0, em = 0.0;
+    for (long i = threadIdx.x; i < n; i += blockDim.x) {
+        const float2 y = r[i], z = x[i];
+        const float w = m[i];
+        ey += (double)(y.x * y.x + y.y * y.y);
+        em += (double)((w * z.x) * (w * z.x) + (w * z.y) * (w * z.y));
+    }
+    ey = warp_sum_d(ey);
+    em = warp_sum_d(em);
+    if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = ey; red[1][threadIdx.x >> 5] = em; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double sy = 0.0, sm = 0.0;
+        for (int i = 0; i < (int)(blockDim.x >> 5); ++i) { sy += red[0][i]; sm += red[1][i]; }
+        gain_s = sqrtf((float)(sm / (double)n)) / sqrtf((float)(sy / (double)n));
+    }
+    __syncthreads();
+    const float g = gain_s;
+    for (long i = threadIdx.x; i < n; i += blockDim.x) {
+        const float2 y = r[i];
+        out[b * n + i] = make_float2(y.x * g, y.y * g);
+    }
+}
+
+extern "C" int css_normalize_scale(const void* result, const void* ref, const float* mask, long n_chunks, long n, void* out,
+                                   cudaStream_t st) {
+    CSS_REQUIRE(n_chunks > 0 && n > 0, "css_normalize_scale: empty input");
+    normalize_scale_kernel<<<(unsigned)n_chunks, 512, 0, st>>>((const float2*)result, (const float2*)ref, mask, n, (float2*)out);
+    return css_check_launch("css_normalize_scale");
+}

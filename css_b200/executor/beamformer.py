@@ -165,6 +165,23 @@ class Beamformer:
         scratch = torch.empty(out.shape[0], dtype=torch.int32, device=out.device)
         nv.call("css_peak_normalize", nv.ptr(out), nv.c_int(out.shape[0]), nv.c_long(out.shape[1]), nv.c_float(0.9), nv.ptr(scratch))
 
+    def normalize_scale(self, result, ref_spec, mask):
+        """result (B,F,T) complex, ref_spec (B,F,T) complex (channel 0), mask (B,F,T) real -> result scaled so that its rms
+        over (F,T) equals the rms of mask * ref_spec, per chunk (beamformer.py:165-183).  Inside continuous_process the same
+        scale is applied by css_mvdr_finalize from energies reduced in the MVDR kernel; this method serves callers of the
+        reference surface that hold the spectra themselves."""
+        nv.require_cuda(result, "result")
+        dev = result.device
+        B = result.shape[0]
+        r = torch.view_as_real(result.to(torch.complex64).contiguous())
+        x = torch.view_as_real(ref_spec.to(dev, torch.complex64).contiguous())
+        m = mask.to(dev, torch.float32).contiguous()
+        if x.shape != r.shape or m.shape != result.shape:
+            raise RuntimeError(f"normalize_scale: shapes differ {tuple(result.shape)} {tuple(ref_spec.shape)} {tuple(mask.shape)}")
+        out = torch.empty_like(r)
+        nv.call("css_normalize_scale", nv.ptr(r), nv.ptr(x), nv.ptr(m), nv.c_long(B), nv.c_long(result[0].numel()), nv.ptr(out))
+        return torch.view_as_complex(out)
+
     def process_one_batch(self, x, speech_mask, noise_mask):
         """x: (B, D, N) windows, masks (B, F, T) -> beamformed (B, F, T) complex64 (beamformer.py:126-163)."""
         nv.require_cuda(x, "x")

@@ -7,7 +7,9 @@ DOA merge -- no per-chunk Python loop and no numpy round trip.
 
 backend "b200": ``model`` is a ``css_b200.models`` Conformer/BLSTM on a CUDA device (or
 ``model_path`` names a checkpoint saved by ``css_b200.utils.model_util.save_model``).
-The reference's only backend, "onnx", needs onnxruntime and is not part of this build.
+backend "onnx" (the reference's only backend, separator.py:26-34): ``model_path`` names an ONNX file; its weights are
+imported into the native model (css_b200/utils/onnx_import.py), no onnxruntime involved.  As in the reference the ONNX
+backend asserts ``batch_size == 1`` (separator.py:21-24).
 """
 import math
 
@@ -34,13 +36,18 @@ def steervec_7ch(nfreqs=257, nvecs=30, radius=0.0425, sndvelocity=340, samplerat
 class Separator:
     def __init__(self, separation_config, sr=16000, sess_options=None, device="cuda", backend="b200",
                  lowcut=80, highcut=2000, model=None, max_chunks_per_launch=2048, stream_first_fraction=0.125):
-        if backend not in ("b200", "native"):
+        if backend not in ("b200", "native", "onnx"):
             raise ValueError(f"Unknown backend: {backend}")
+        if backend == "onnx":
+            assert separation_config["batch_size"] == 1, "ONNX backend only supports batch size 1"      # separator.py:21-24
         self.device = torch.device(device)
         if self.device.type != "cuda":
             raise nv.NativeError("css_b200 runs only on CUDA devices (no CPU fallback)")
         if model is None:
-            model = get_b200_model(separation_config["model_path"], sess_options, self.device)[0]
+            path = separation_config["model_path"]
+            if backend == "onnx" and not str(path).endswith(".onnx"):
+                raise ValueError(f"backend 'onnx' expects an .onnx model_path, got {path}")
+            model = get_b200_model(path, sess_options, self.device)[0]
         self.separator = model if isinstance(model, B200Session) else B200Session(model)
         self.model = self.separator.model
         self.batch_size = separation_config["batch_size"]

@@ -48,16 +48,31 @@ def get_b200_model(model_path, sess_options=None, device="cuda"):
     from ..models import build_model
 
     if str(model_path).endswith(".onnx"):
-        raise ValueError(
-            f"{model_path}: ONNX checkpoints need onnxruntime, which is not part of this build; "
-            "pass `model=` or a checkpoint written by css_b200.utils.model_util.save_model"
-        )
+        return get_onnx_model(model_path, sess_options, device)
     ckpt = torch.load(model_path, map_location="cpu")
     model = build_model(ckpt["model_name"], ckpt["conf"])
     model.load_state_dict(ckpt["model"])
     model = model.to(device).eval()
     logging.info("loaded %s from %s", ckpt["model_name"], model_path)
     return B200Session(model), torch.device(device)
+
+
+def get_onnx_model(model_path, sess_options=None, device="cuda"):
+    """Reference signature (css/utils/model_util.py:12-25): -> (session, device).
+
+    The reference builds an ``onnxruntime.InferenceSession`` here.  This build reads the weights out of the ONNX file
+    (css_b200/utils/onnx_import.py; no onnxruntime involved) into the native Conformer / BLSTM and returns a session
+    object with the same ``get_inputs`` / ``run`` protocol.  ``sess_options`` (ORT thread counts) has no meaning on the GPU
+    and is ignored; a CPU ``device`` is rejected (no CPU path)."""
+    from .onnx_import import load_onnx_model
+
+    device = torch.device("cuda" if str(device) in ("gpu", "GPU") else device)
+    if device.type != "cuda":
+        raise RuntimeError("css_b200 runs only on CUDA devices (no CPU fallback): pass device='cuda'")
+    model, name, _ = load_onnx_model(model_path)
+    model = model.to(device).eval()
+    logging.info("imported %s from ONNX file %s", name, model_path)
+    return B200Session(model), device
 
 
 def to_numpy(tensor):

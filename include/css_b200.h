@@ -125,6 +125,10 @@ int css_mvdr_energy_blocks(void);
 /* normalize_scale (beamformer.py:165-183) + dedup (beamformer.py:68-80), in place; scal (B,5) */
 int css_mvdr_finalize(void* Y, const float* energy, long n_chunks, int T, int rescale, int dedup, float* scal,
                       css_stream_t stream);
+/* Beamformer.normalize_scale as a stand-alone call (beamformer.py:165-183): result, ref (n_chunks, n) complex64, mask
+ * (n_chunks, n) fp32 -> out = result * rms(mask * ref) / rms(result) per chunk */
+int css_normalize_scale(const void* result, const void* ref, const float* mask, long n_chunks, long n, void* out,
+                        css_stream_t stream);
 /* torch.istft + placement (beamformer.py:83-118): plan (n_items,4) int32 {chunk, s_begin, s_end, dst};
  * out (2, out_len) is accumulated into; items of one call must not overlap in out */
 int css_istft_place(const void* Y, int T, const int* plan, int n_items, float* out, long out_len, css_stream_t stream);
