@@ -63,6 +63,10 @@ def install_stubs():
     bf.SoudenMVDRBeamformer = SoudenMVDRBeamformer
     ast.dsp, dsp.beamforming = dsp, bf
     sys.modules.update({"asteroid": ast, "asteroid.dsp": dsp, "asteroid.dsp.beamforming": bf})
+    import importlib.machinery
+
+    for mod in (ort, ast, dsp, bf):           # importlib.util.find_spec (used by torch._dynamo) rejects a module without a spec
+        mod.__spec__ = importlib.machinery.ModuleSpec(mod.__name__, None)
     sys.path.insert(0, REF)
 
 
