@@ -25,6 +25,7 @@ if ROOT not in sys.path:
 METRIC = "audio_seconds_separated_per_second_7ch_conformer_css"
 UNIT = "xRT"
 SR = 16000
+TRAIN_DROPOUT = 0.0      # the native training step's dropout rate in the `train` region
 CONF_7CH = dict(idim=1799, num_bins=257, num_spk=2, num_noise=1, conformer_attention_dim=256,
                 conformer_attention_heads=4, conformer_linear_units=1024, conformer_num_blocks=16,
                 conformer_kernel_size=33, conformer_dropout_rate=0.1, conformer_relative_pos_emb=True)
@@ -41,6 +42,9 @@ def parse():
     p.add_argument("--gemm-mode", type=int, default=-1, help="-1 library default, 0 fp32 SIMT, 1 bf16x3 tcgen05, 2 bf16 tcgen05")
     p.add_argument("--cpu-seconds", type=float, default=24.0, help="audio length of the bounded CPU-baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-extra", action="store_true", help="skip the long_form / train regions (configs[4] / configs[3])")
+    p.add_argument("--extra-steps", type=int, default=3, help="timed steps of each extra region")
+    p.add_argument("--long-seconds", type=float, default=600.0, help="recording length of the long_form region")
     return p.parse_args()
 
 
@@ -154,8 +158,155 @@ def run_reference(args):
             "config": {"workload": f"7-ch Conformer CSS (conf/config_7ch.yaml), bounded CPU sample of {secs:g} s per step",
                        "blocks": args.blocks, "session_seconds": secs},
             "cpu_baseline": {"value": xrt, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "reference_processes": 1, "reference_note": "ONE host process on this box's cores, whatever --gpus says: at N > 1 the "
+            "driver's ratio compares N GPUs with one host",
             "e2e": {"value": xrt, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+def region_long_form(args, cfg, model, dev, rank, world, barrier, max_over_ranks):
+    """BASELINE configs[4] (long-form, strong scaling): ONE recording split into contiguous chunk ranges over the ranks
+    (css_b200.dist.ShardedCssPipeline).  Timed: resident waveform -> every rank's normalised sample range on its own GPU;
+    `e2e`: from the pinned host recording (each rank copies only its slice) to each rank's range back in ITS pinned host
+    buffer (N parallel D2H copies, no rank moves the whole output); `gathered`: the ranges collected on rank 0 over NCCL."""
+    import torch
+
+    from css_b200.dist import ShardedCssPipeline
+    from css_b200.synth import make_recording, n_chunks
+
+    secs = args.long_seconds
+    steps = max(1, args.extra_steps)
+    wav_host = make_recording(secs, channels=7, seed=4321).pin_memory()
+    wav_dev = wav_host.to(dev)
+    T = wav_host.shape[1]
+    sh = ShardedCssPipeline(cfg, model, dev, rank, world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, n):
+        barrier()
+        e0.record()
+        for _ in range(n):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)) / n
+
+    piece, (s0, s1) = sh(wav_dev, gather=False)
+    host_piece = torch.empty(2, max(1, s1 - s0), dtype=torch.float32).pin_memory()
+
+    def step_e2e():
+        p, _ = sh(wav_host, gather=False)
+        if p.shape[1]:
+            host_piece[:, : p.shape[1]].copy_(p, non_blocking=True)
+
+    for _ in range(3):
+        sh(wav_dev, gather=False)
+    ms = timed(lambda: sh(wav_dev, gather=False), steps)
+    coll = dict(sh.last_collective_bytes)
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, steps)
+    out = {"workload": f"configs[4] long-form, strong scaling: one {secs:g} s 7-ch recording ({n_chunks(T)} chunks) split into "
+                       f"contiguous chunk ranges over {world} GPU(s), 2-chunk recomputed halo",
+           "value": secs / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms, "steps": steps, "scaling": "strong",
+           "collective_bytes_per_step": coll,
+           "e2e": {"value": secs / (ms_e2e * 1e-3), "unit": UNIT, "ms_per_step": ms_e2e,
+                   "h2d_bytes_per_step_per_rank": int(7 * 4 * T / world), "d2h_bytes_per_step_per_rank": int(2 * 4 * T / world)}}
+    if world > 1:
+        sh(wav_dev, gather=True)
+        ms_g = timed(lambda: sh(wav_dev, gather=True), steps)
+        out["gathered"] = {"value": secs / (ms_g * 1e-3), "unit": UNIT, "ms_per_step": ms_g, "nccl_gather_bytes_per_step": 8 * T}
+        # one GPU on the same recording in the same run (rank 0 works, the others wait): strong-scaling efficiency
+        one = ShardedCssPipeline(cfg, model, dev, 0, 1)
+        if rank == 0:
+            for _ in range(3):
+                one(wav_dev, gather=False)
+        barrier()
+        e0.record()
+        if rank == 0:
+            for _ in range(steps):
+                one(wav_dev, gather=False)
+        e1.record()
+        barrier()
+        ms1 = max_over_ranks(e0.elapsed_time(e1)) / steps
+        out["one_gpu_ms_per_step"] = ms1
+        out["efficiency_vs_one_gpu"] = ms1 / (world * ms)
+    return out
+
+
+def region_train(args, dev, rank, world, barrier, max_over_ranks):
+    """BASELINE configs[3]: utterance-level PIT training step (css/trainer/iteration_types.py:34-63), 16-block 7-ch
+    Conformer, batch 32 x 250 frames per GPU, bf16 tensor-core GEMMs (gemm mode 2), clip 5.0 + Adam(1e-4, wd 1e-2);
+    N > 1: bucketed NCCL gradient all-reduce overlapped with the backward.  Inputs come from pinned host memory each step."""
+    import torch
+
+    import css_b200.models as M
+    from css_b200 import _native as nv
+    from css_b200.objectives import build_objective
+    from css_b200.trainer import FusedAdam
+
+    steps = max(1, args.extra_steps)
+    saved_mode = nv.get_gemm_mode()
+    nv.set_gemm_mode(2)
+    try:
+        conf = dict(CONF_7CH, conformer_num_blocks=args.blocks, conformer_dropout_rate=TRAIN_DROPOUT)
+        torch.manual_seed(0)
+        model = M.build_model("Conformer", conf).train().to(dev)
+        engine = model.train_engine()
+        opt = FusedAdam(engine, lr=1e-4, weight_decay=1e-2)
+        objective = build_objective("MSE", {})
+        g = torch.Generator().manual_seed(100 + rank)
+        B, T = 32, 250
+        s1 = (torch.rand(B, T, 257, generator=g) ** 2).pin_memory()
+        s2 = (torch.rand(B, T, 257, generator=g) ** 2).pin_memory()
+        mix = torch.empty(B, T, 1799)
+        mix[..., :257] = s1 + s2
+        mix[..., 257:] = (torch.rand(B, T, 1542, generator=g) * 2 - 1) * 3.14159
+        host = {"mix": mix.pin_memory(), "source1": s1, "source2": s2, "ovl": 0.5}
+        loss_host = torch.zeros(1).pin_memory()
+
+        def step():
+            batch = {k: (v.to(dev, non_blocking=True) if torch.is_tensor(v) else v) for k, v in host.items()}
+            loss = objective(model, batch, device=dev)
+            loss.backward()
+            if engine.exchange is not None:
+                engine.exchange.finish()
+            opt.clip_grad_norm_(5.0)
+            opt.step()
+            opt.zero_grad()
+            loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+        def timed(n):
+            barrier()
+            e0.record()
+            for _ in range(n):
+                step()
+            e1.record()
+            barrier()
+            return max_over_ranks(e0.elapsed_time(e1)) / n
+
+        for _ in range(3):
+            step()
+        ms_local = timed(steps)                                  # every rank alone: no exchange
+        out = {"workload": "configs[3]: PIT training step, 16-block 7-ch Conformer, batch 32 x 250 frames per GPU, bf16 GEMMs, "
+                           f"dropout {TRAIN_DROPOUT}, clip 5.0, Adam(1e-4, wd 1e-2); inputs from pinned host memory every step",
+               "unit": "utt/s", "steps": steps, "scaling": "weak", "h2d_bytes_per_step": (mix.numel() + 2 * s1.numel()) * 4,
+               "d2h_bytes_per_step": 4}
+        if world > 1:
+            engine.enable_data_parallel(opt)
+            step()
+            ms = timed(steps)
+            out.update(value=world * B / (ms * 1e-3), ms_per_step=ms, ms_per_step_without_exchange=ms_local,
+                       efficiency_vs_n_times_one_gpu=ms_local / ms, allreduce_bytes_per_step=int(engine.size) * 4,
+                       allreduce_buckets=len(engine.exchange.ranges))
+        else:
+            out.update(value=B / (ms_local * 1e-3), ms_per_step=ms_local, allreduce_bytes_per_step=0)
+        out["final_loss"] = float(loss_host[0])
+        return out
+    finally:
+        nv.set_gemm_mode(saved_mode)
 
 
 def run_b200(args):
@@ -240,7 +391,7 @@ def run_b200(args):
     # through CssPipeline.run_many, which double-buffers the H2D / D2H copies of consecutive recordings around the compute
     outs_host = [out_host, torch.empty_like(out_host).pin_memory()]
     pipe.run_many([wav_host] * 3, [outs_host[i % 2] for i in range(3)])
-    # the region is run twice and the faster pass reported (both are kept in the JSON): host<->device copy rates on a shared
+    # the region is run twice and the MEAN reported (both passes are kept in the JSON): host<->device copy rates on a shared
     # box vary from one second to the next, the kernels do not
     e2e_runs = []
     for _ in range(2):
@@ -250,7 +401,42 @@ def run_b200(args):
         e1.record()
         barrier()
         e2e_runs.append(max_over_ranks(e0.elapsed_time(e1)))
-    ms_e2e = min(e2e_runs)
+    ms_e2e = sum(e2e_runs) / len(e2e_runs)          # mean of the passes (both are kept in the JSON)
+
+    # ---- N > 1: the same e2e region with the NCCL gather of every rank's separated waveforms onto rank 0 (north_star: "NCCL
+    # over NVLink is used only to gather stitched outputs"); rank 0 alone copies all N results to the host
+    gathered = None
+    if world > 1:
+        from css_b200.dist import gather_waveforms
+
+        lengths = [T] * world
+        big_host = torch.empty(world, 2, T, dtype=torch.float32).pin_memory() if rank == 0 else None
+
+        def step_gather():
+            out = pipe(wav_host)
+            res = gather_waveforms({rank: out}, lengths, rank, world, dst=0)
+            if rank == 0:
+                for i, r in enumerate(res):
+                    big_host[i].copy_(r, non_blocking=True)
+
+        step_gather()
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            step_gather()
+        e1.record()
+        barrier()
+        ms_g = max_over_ranks(e0.elapsed_time(e1))
+        gathered = {"value": world * audio_s * args.steps / (ms_g * 1e-3), "unit": UNIT, "ms_per_step": ms_g / args.steps,
+                    "nccl_gather_bytes_per_step": (world - 1) * 2 * T * 4, "d2h_bytes_per_step_rank0": world * 2 * T * 4,
+                    "note": "every rank's (2, T) result gathered onto rank 0 over NCCL, rank 0 copies all of them to the host"}
+    del pipe
+    extra = {}
+    if not args.no_extra:
+        extra["long_form"] = region_long_form(args, cfg, model, dev, rank, world, barrier, max_over_ranks)
+        del model
+        torch.cuda.empty_cache()
+        extra["train"] = region_train(args, dev, rank, world, barrier, max_over_ranks)
 
     if rank != 0:
         if world > 1:
@@ -293,12 +479,20 @@ def run_b200(args):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps, "ms_per_step_runs": [round(t / args.steps, 3) for t in e2e_runs],
                     "h2d_bytes_per_step": wav_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},
             "gpu_launches": int(launches)}
+    if gathered:
+        line["e2e_gathered_to_rank0"] = gathered
+    line.update(extra)
     if world == 1 and not args.no_cpu_baseline:
         torch.cuda.synchronize()
         xrt, ms, cores = cpu_reference_run(args.cpu_seconds, args.blocks, 1, 0)
         line["cpu_baseline"] = {"value": xrt, "unit": UNIT, "cores": cores, "kind": "port",
                                 "sample": f"{args.cpu_seconds:g} s 7-ch session through oracle/css_oracle.py (torch CPU fp32, "
                                           f"{args.blocks}-block Conformer), 1 pass, {cores} threads"}
+        # the reference's own session setting is ONE thread (ORT intra/inter-op 1, scripts/python/separate_libricss.py:40-44)
+        one_s = min(args.cpu_seconds, 8.0)
+        xrt1, _, _ = cpu_reference_run(one_s, args.blocks, 1, 0, threads=1)
+        line["cpu_baseline_1thread"] = {"value": xrt1, "unit": UNIT, "cores": 1, "kind": "port",
+                                        "sample": f"{one_s:g} s 7-ch session, same oracle path, torch.set_num_threads(1)"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

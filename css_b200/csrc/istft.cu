@@ -73,8 +73,8 @@ extern "C" int css_istft_place(const void* Y, int T, const int* plan, int n_item
 // peak normalisation: x[r][:] *= 0.9 / max|x[r][:]|   (beamformer.py:122-123)
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-absmax_kernel(const float* __restrict__ x, long n, unsigned* __restrict__ mx) {
-    const float* row = x + (long)blockIdx.y * n;
+absmax_kernel(const float* __restrict__ x, long n, long ld, unsigned* __restrict__ mx) {
+    const float* row = x + (long)blockIdx.y * ld;
     float m = 0.f;
     bool nan = false;
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
@@ -89,23 +89,43 @@ absmax_kernel(const float* __restrict__ x, long n, unsigned* __restrict__ mx) {
     if ((threadIdx.x & 31) == 0) atomicMax(mx + blockIdx.y, bits);
 }
 __global__ void __launch_bounds__(256)
-peak_scale_kernel(float* __restrict__ x, long n, const unsigned* __restrict__ mx, float target) {
-    float* row = x + (long)blockIdx.y * n;
-    const float s = target / __uint_as_float(mx[blockIdx.y]);
+peak_scale_kernel(float* __restrict__ x, long n, long ld, const unsigned* __restrict__ mx, float target) {
+    float* row = x + (long)blockIdx.y * ld;
+    const float peak = __uint_as_float(mx[blockIdx.y]);
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
-        row[i] = row[i] * target / __uint_as_float(mx[blockIdx.y]);
-    (void)s;
+        row[i] = row[i] * target / peak;       // (x * 0.9) / max, the reference's order of operations
+}
+
+static dim3 peak_grid(int rows, long n) {
+    dim3 grid((unsigned)((n + 256 * 8 - 1) / (256 * 8)), rows);
+    if (grid.x > 148 * 8) grid.x = 148 * 8;
+    if (grid.x < 1) grid.x = 1;
+    return grid;
+}
+
+// The two halves of the peak normalisation as separate calls, for a recording whose samples are spread over several
+// GPUs: every rank takes the maximum of its own sample range (bits[r] = max(bits[r], float bits of max|x[r][:n]|), bits must
+// start at 0), the ranks combine the bits with an all-reduce(MAX) (order-preserving for non-negative floats), and
+// every rank scales its own range.  x: (rows, ld) with n <= ld valid samples per row.
+extern "C" int css_absmax(const float* x, int rows, long n, long ld, unsigned* bits, cudaStream_t st) {
+    CSS_REQUIRE(rows > 0 && n >= 0 && ld >= n, "css_absmax: bad shape");
+    if (n == 0) return 0;
+    CssProfScope prof(10, (double)rows * n * 4.0, st);
+    absmax_kernel<<<peak_grid(rows, n), 256, 0, st>>>(x, n, ld, bits);
+    return css_check_launch("css_absmax");
+}
+extern "C" int css_peak_scale(float* x, int rows, long n, long ld, float target, const unsigned* bits, cudaStream_t st) {
+    CSS_REQUIRE(rows > 0 && n >= 0 && ld >= n, "css_peak_scale: bad shape");
+    if (n == 0) return 0;
+    CssProfScope prof(10, (double)rows * n * 8.0, st);
+    peak_scale_kernel<<<peak_grid(rows, n), 256, 0, st>>>(x, n, ld, bits, target);
+    return css_check_launch("css_peak_scale");
 }
 
 extern "C" int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scratch, cudaStream_t st) {
     CSS_REQUIRE(rows > 0 && n > 0, "css_peak_normalize: empty input");
     cudaMemsetAsync(scratch, 0, sizeof(unsigned) * rows, st);
-    dim3 grid((unsigned)((n + 256 * 8 - 1) / (256 * 8)), rows);
-    if (grid.x > 148 * 8) grid.x = 148 * 8;
-    CssProfScope prof(10, (double)rows * n * 12.0, st);
-    absmax_kernel<<<grid, 256, 0, st>>>(x, n, scratch);
-    int rc = css_check_launch("absmax");
+    int rc = css_absmax(x, rows, n, n, scratch, st);
     if (rc) return rc;
-    peak_scale_kernel<<<grid, 256, 0, st>>>(x, n, scratch, target);
-    return css_check_launch("css_peak_normalize");
+    return css_peak_scale(x, rows, n, n, target, scratch, st);
 }

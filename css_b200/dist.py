@@ -9,6 +9,8 @@ import os
 import torch
 import torch.distributed as dist
 
+from . import _native as nv
+
 
 def init_from_env(backend=None):
     """Initialise torch.distributed from torchrun's environment; returns (rank, world, local_rank)."""
@@ -107,9 +109,11 @@ class ShardedCssPipeline:
     halo pair gets the same bit on both ranks), and the only data-path exchange is an all-gather of one parity bit per
     rank that turns the rank-local permutation states into global ones (stitcher.py:55-60 is a prefix XOR).  MVDR and
     the iSTFT placement run on the owned chunks with the GLOBAL placement plan (its 32-chunk batch seams are defined by
-    global chunk indices, beamformer.py:54-57); the per-rank partial waveforms are summed onto rank 0 (NCCL reduce over
-    NVLink), which applies the global peak normalisation (beamformer.py:122-123).  Results equal the single-GPU
-    pipeline's bit for bit.
+    global chunk indices, beamformer.py:54-57) into a buffer that covers only the rank's OWN sample range; a rank's last
+    chunk can spill <= 6,144 samples into its right neighbour's range (the `en == T` branch), exchanged by one small
+    all-gather; the global peak (beamformer.py:122-123) is an all-reduce(MAX) of two values and every rank scales its own
+    range.  No rank ever holds or moves the whole (2, T) output unless a single writer asks for it (``gather=True``).
+    Results equal the single-GPU pipeline's bit for bit.
     """
 
     def __init__(self, cfg, model, device, rank, world, group=None):
@@ -118,6 +122,7 @@ class ShardedCssPipeline:
         self.pipe = CssPipeline(cfg, model, device=device)
         self.rank, self.world, self.group = rank, world, group
         self.device = torch.device(device)
+        self._layers = {}
 
     def _phase1(self, wav, c0, c1, B):
         """Masks, local pair decisions and local prefix states of the chunk range [c0, c1) plus its halo."""
@@ -127,11 +132,16 @@ class ShardedCssPipeline:
         lo, hi = e0 * sep.eval_hop, (e1 - 1) * sep.eval_hop + sep.chunk_len
         if wav.is_cuda:
             local = wav[:, lo:hi].to(dev, torch.float32)
+            masks, mags = sep.separate(local)
+        elif wav.is_pinned() and wav.dtype == torch.float32 and e1 - e0 >= 64:
+            # the Separator streams a pinned host slice in pieces, the mask network of the first chunks running underneath the copy
+            masks, mags = sep.separate(wav[:, lo:hi])
+            local = sep.last["wav"]
         else:   # row-wise copies: a strided host slice would be staged through pageable memory
             local = torch.empty(wav.shape[0], hi - lo, dtype=torch.float32, device=dev)
             for d in range(wav.shape[0]):
                 local[d].copy_(wav[d, lo:hi], non_blocking=True)
-        masks, mags = sep.separate(local)
+            masks, mags = sep.separate(local)
         swap = st.stitch_device(mags, masks)
         state_local = torch.zeros(e1 - e0, dtype=torch.int32, device=dev)
         if e1 - e0 > 1:
@@ -139,32 +149,75 @@ class ShardedCssPipeline:
         return {"c0": c0, "c1": c1, "e0": e0, "e1": e1, "local": local, "masks": masks, "swap": swap, "state_local": state_local,
                 "spec": sep.last["spec"], "parity": owned_parity(state_local, c0, c1, e0).reshape(1)}
 
-    def _phase2(self, ctx, prefix, B, T, out):
-        """Global states -> stitched masks -> MVDR of the range -> placement of the OWNED chunks into out (2, T)."""
+    # ------------------------------------------------------------------ sample ownership
+    def sample_start(self, c, T):
+        """First output sample placed by chunk c (beamformer.py:104-118): 0 for chunk 0, else hop*c + margin - hop."""
+        bf = self.pipe.beamformer
+        return 0 if c == 0 else min(T, bf.eval_hop * c + bf.proceed_margin - bf.eval_hop)
+
+    def owned_samples(self, c0, c1, B, T):
+        """[s0, s1): the output samples whose LAST-rank-independent owner is the rank with chunks [c0, c1): from the first
+        sample its first chunk places to the first sample the next rank's first chunk places (the last rank owns the tail)."""
+        if c1 <= c0:
+            return 0, 0
+        return self.sample_start(c0, T), (T if c1 >= B else self.sample_start(c1, T))
+
+    @property
+    def spill(self):
+        """Samples a rank's last chunk can place beyond its own range: only the `en == T` branch (A.6 Q4) writes
+        wav_len - margin samples into the next chunk's region (6,144 for the shipped configs)."""
+        bf = self.pipe.beamformer
+        return max(0, bf.hop_length * (bf.mask_win - 1) - bf.proceed_margin)
+
+    def _phase2(self, ctx, prefix, B, T, out, s0=0):
+        """Global states -> stitched masks -> MVDR of the range -> placement of the OWNED chunks into out (2, n), whose
+        sample 0 is recording sample s0."""
         st, bf = self.pipe.stitcher, self.pipe.beamformer
         c0, c1, e0, e1 = ctx["c0"], ctx["c1"], ctx["e0"], ctx["e1"]
-        s0 = first_state(prefix, ctx["state_local"], c0, e0).reshape(1)
-        stitched = st.connect_device(ctx["swap"], ctx["masks"], state0=s0)
+        st0 = first_state(prefix, ctx["state_local"], c0, e0).reshape(1)
+        stitched = st.connect_device(ctx["swap"], ctx["masks"], state0=st0)
         Y = bf.beamform_chunks(ctx["local"], stitched, e1 - e0, spec=ctx["spec"])
-        layers = []
-        for items in bf._plan(B, T, out.device):
-            keep = (items[:, 0] >= c0) & (items[:, 0] < c1)
-            sub = items[keep].clone()
-            sub[:, 0] -= e0
-            layers.append(sub.contiguous())
+        key = (B, T, c0, c1, e0, s0, str(out.device))
+        layers = self._layers.get(key)
+        if layers is None:      # built once per shape: the boolean selection synchronises, the steady state must not
+            layers = []
+            for items in bf._plan(B, T, out.device):
+                keep = (items[:, 0] >= c0) & (items[:, 0] < c1)
+                sub = items[keep].clone()
+                sub[:, 0] -= e0
+                sub[:, 3] -= s0
+                layers.append(sub.contiguous())
+            self._layers[key] = layers
         bf.place(Y, layers, out)
         return st.last_state[c0 - e0 : c1 - e0]
 
-    def __call__(self, wav, return_intermediates=False):
-        """wav: (7, T) fp32 host (pinned) or device, the same on every rank -> (2, T) on rank 0, None elsewhere."""
+    def _finish_local(self, loc, own, spill_prev, bits):
+        """Add the previous rank's spill, take the maximum of the owned range into bits (2 x uint32)."""
+        if spill_prev is not None and own > 0:
+            n = min(spill_prev.shape[1], own)
+            loc[:, :n] += spill_prev[:, :n]
+        nv.call("css_absmax", nv.ptr(loc), nv.c_int(2), nv.c_long(own), nv.c_long(loc.shape[1]), nv.ptr(bits))
+
+    def __call__(self, wav, return_intermediates=False, gather=True):
+        """wav: (7, T) fp32 host (pinned) or device, the same on every rank.
+
+        gather=True : -> (2, T) on rank 0 (NCCL gather of the ranks' normalised sample ranges), None elsewhere.
+        gather=False: -> (slice (2, s1-s0), (s0, s1)) on every rank: each rank keeps (and can write / copy to the host) its
+                      own sample range; no waveform bytes cross the GPUs.
+
+        Exchange steps: all-gather of one permutation-parity bit per rank; all-gather of each rank's
+        <= 6,144-sample spill into its right neighbour's range (A.6 Q4); all-reduce(MAX) of the two peak values."""
         sep, bf = self.pipe.separator, self.pipe.beamformer
         D, T = wav.shape
         B = sep.n_chunks(T)
         if B < 1:
             raise RuntimeError(f"waveform of {T} samples is shorter than one window of {sep.chunk_len}")
-        c0, c1 = chunk_ranges(B, self.world)[self.rank]
+        ranges = chunk_ranges(B, self.world)
+        c0, c1 = ranges[self.rank]
         dev = self.device
-        out = torch.zeros(2, T, dtype=torch.float32, device=dev)
+        s0, s1 = self.owned_samples(c0, c1, B, T)
+        own, sp = s1 - s0, self.spill
+        loc = torch.zeros(2, own + sp, dtype=torch.float32, device=dev)
         ctx = self._phase1(wav, c0, c1, B) if c1 > c0 else None
         parity = ctx["parity"] if ctx else torch.zeros(1, dtype=torch.int32, device=dev)
         if self.world > 1:
@@ -175,30 +228,70 @@ class ShardedCssPipeline:
         states = None
         if ctx:
             prefix = (allp[: self.rank].sum() & 1).to(torch.int32).reshape(1)
-            states = self._phase2(ctx, prefix, B, T, out)
+            states = self._phase2(ctx, prefix, B, T, loc, s0)
+        bits = torch.zeros(2, dtype=torch.int32, device=dev)
+        spill_prev = None
+        if self.world > 1 and sp > 0:
+            spills = torch.empty(self.world, 2, sp, dtype=torch.float32, device=dev)
+            dist.all_gather_into_tensor(spills, loc[:, own:].contiguous(), group=self.group)
+            if self.rank > 0:
+                spill_prev = spills[self.rank - 1]
+        self._finish_local(loc, own, spill_prev, bits)
         if self.world > 1:
-            dist.reduce(out, dst=0, op=dist.ReduceOp.SUM, group=self.group)
-        if self.rank == 0:
-            bf.peak_normalize(out)
-        res = out if self.rank == 0 else None
-        return (res, {"state": states, "range": (c0, c1)}) if return_intermediates else res
+            dist.all_reduce(bits, op=dist.ReduceOp.MAX, group=self.group)    # float bits of non-negative values order as ints
+        nv.call("css_peak_scale", nv.ptr(loc), nv.c_int(2), nv.c_long(own), nv.c_long(loc.shape[1]), nv.c_float(0.9), nv.ptr(bits))
+        mine = loc[:, :own]
+        self.last_collective_bytes = {"parity": 4 * self.world, "spill": 8 * sp * self.world if self.world > 1 else 0, "peak": 8,
+                                      "gather": 8 * T if (gather and self.world > 1) else 0}
+        if not gather:
+            res = (mine, (s0, s1))
+        elif self.world == 1:
+            res = mine
+        else:
+            res = self._gather(mine, ranges, B, T)
+        return (res, {"state": states, "range": (c0, c1), "samples": (s0, s1)}) if return_intermediates else res
+
+    def _gather(self, mine, ranges, B, T):
+        """NCCL gather of the ranks' sample ranges onto rank 0 -> (2, T)."""
+        spans = [self.owned_samples(a, b, B, T) for a, b in ranges]
+        width = max(b - a for a, b in spans)
+        buf = torch.zeros(2, width, dtype=torch.float32, device=self.device)
+        buf[:, : mine.shape[1]] = mine
+        outs = [torch.empty_like(buf) for _ in range(self.world)] if self.rank == 0 else None
+        dist.gather(buf, outs, dst=0, group=self.group)
+        if self.rank != 0:
+            return None
+        full = torch.empty(2, T, dtype=torch.float32, device=self.device)
+        for (a, b), o in zip(spans, outs):
+            full[:, a:b] = o[:, : b - a]
+        return full
 
     def emulate(self, wav, world):
-        """Single-process emulation of a `world`-rank run (the ranks' work executed one after the other on this GPU,
-        the parity all-gather and the final sum done in place).  Used by the parity tests on one-GPU boxes."""
+        """Single-process emulation of a `world`-rank run (the ranks' work executed one after the other on this GPU, the
+        collectives done in place).  Used by the parity tests on one-GPU boxes."""
         sep, bf = self.pipe.separator, self.pipe.beamformer
         D, T = wav.shape
         B = sep.n_chunks(T)
-        out = torch.zeros(2, T, dtype=torch.float32, device=self.device)
+        dev = self.device
         ranges = chunk_ranges(B, world)
         ctxs = [self._phase1(wav, c0, c1, B) if c1 > c0 else None for c0, c1 in ranges]
-        zero = torch.zeros(1, dtype=torch.int32, device=self.device)
+        zero = torch.zeros(1, dtype=torch.int32, device=dev)
         allp = torch.cat([c["parity"] if c else zero for c in ctxs])
-        states = []
-        for r, ctx in enumerate(ctxs):
+        sp = self.spill
+        locs, states, spans = [], [], []
+        for r, (ctx, (c0, c1)) in enumerate(zip(ctxs, ranges)):
+            s0, s1 = self.owned_samples(c0, c1, B, T)
+            loc = torch.zeros(2, s1 - s0 + sp, dtype=torch.float32, device=dev)
             if ctx:
-                part = torch.zeros_like(out)
-                states.append(self._phase2(ctx, (allp[:r].sum() & 1).to(torch.int32).reshape(1), B, T, part))
-                out += part
-        bf.peak_normalize(out)
+                states.append(self._phase2(ctx, (allp[:r].sum() & 1).to(torch.int32).reshape(1), B, T, loc, s0))
+            locs.append(loc)
+            spans.append((s0, s1))
+        bits = torch.zeros(2, dtype=torch.int32, device=dev)
+        for r, (loc, (s0, s1)) in enumerate(zip(locs, spans)):
+            prev = locs[r - 1][:, spans[r - 1][1] - spans[r - 1][0]:] if r > 0 and sp > 0 else None
+            self._finish_local(loc, s1 - s0, prev.clone() if prev is not None else None, bits)
+        out = torch.zeros(2, T, dtype=torch.float32, device=dev)
+        for loc, (s0, s1) in zip(locs, spans):
+            nv.call("css_peak_scale", nv.ptr(loc), nv.c_int(2), nv.c_long(s1 - s0), nv.c_long(loc.shape[1]), nv.c_float(0.9), nv.ptr(bits))
+            out[:, s0:s1] = loc[:, : s1 - s0]
         return out, torch.cat(states)

@@ -135,6 +135,12 @@ int css_istft_place(const void* Y, int T, const int* plan, int n_items, float* o
 /* beamformer.py:122-123; scratch: `rows` uint32 */
 int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scratch, css_stream_t stream);
 
+/* The two halves of css_peak_normalize for a recording spread over several GPUs: bits[r] = max(bits[r], bits of
+ * max|x[r][:n]|) (caller zeroes bits; combine across ranks with all-reduce MAX), then x[r][:n] = x * target / peak.
+ * x is (rows, ld), n <= ld. */
+int css_absmax(const float* x, int rows, long n, long ld, unsigned* bits, css_stream_t stream);
+int css_peak_scale(float* x, int rows, long n, long ld, float target, const unsigned* bits, css_stream_t stream);
+
 /* ---- PIT-MSE: css/objectives/pit.py:5-62, css/objectives/mse.py:29-37 ---- */
 /* est/tgt (B,K,n); pair_ws (B,K,K) f64; loss_b (B); perm (B,K) int32; loss (1); grad (B,K,n) or NULL */
 int css_pit_mse(const float* est, const float* tgt, long B, int K, long n, double* pair_ws, float* loss_b, int* perm,

@@ -49,6 +49,31 @@ def test_sharded_equals_single_emulated(cuda, world):
     assert torch.equal(out, ref_wav)
 
 
+@pytest.mark.parametrize("world", [2, 13])
+def test_sharded_60s_q4_spill_crosses_a_rank_boundary(cuda, world):
+    """60 s = 72 chunks with T a multiple of the hop: chunks 42 and 66 take the `en == T` branch (A.6 Q4) and place 6,144
+    samples into the next chunk's region.  With 13 ranks chunk 66 is the last chunk of a rank's range, so that spill lands in
+    the right neighbour's sample range and has to be exchanged; the result still equals the single-GPU pipeline bit for bit."""
+    from css_b200.dist import ShardedCssPipeline, chunk_ranges
+    from css_b200.synth import make_recording
+
+    wav = make_recording(60, channels=7, seed=23)
+    if world == 13:
+        assert 67 in [c1 for _, c1 in chunk_ranges(72, world)]
+    ref_wav, ref_state = _single(wav, cuda)
+    sh = ShardedCssPipeline(cfg7(), golden_conformer(num_blocks=1).to(cuda), cuda, 0, 1)
+    _flip_some_chunks(sh.pipe.separator)
+    assert sh.spill == 6144
+    out, state = sh.emulate(wav, world)
+    assert torch.equal(state.cpu(), ref_state.cpu())
+    assert torch.equal(out, ref_wav)
+    # world == 1 through the real entry point: one rank owns every sample
+    res, info = sh(wav, return_intermediates=True)
+    assert torch.equal(res, ref_wav) and info["samples"] == (0, wav.shape[1])
+    piece, (s0, s1) = sh(wav, gather=False)
+    assert (s0, s1) == (0, wav.shape[1]) and torch.equal(piece, ref_wav)
+
+
 def test_short_recording_more_ranks_than_chunks(cuda):
     from css_b200.dist import ShardedCssPipeline
     from css_b200.synth import make_recording
@@ -74,9 +99,12 @@ def _nccl_worker(rank, world, port, q):
     sh = ShardedCssPipeline(cfg7(), golden_conformer(num_blocks=1).to(dev), dev, rank, world)
     _flip_some_chunks(sh.pipe.separator)
     out = sh(wav)
+    piece, (s0, s1) = sh(wav, gather=False)
     if rank == 0:
         ref_wav, _ = _single(wav, dev)
-        q.put(bool(torch.equal(out, ref_wav)))
+        q.put(bool(torch.equal(out, ref_wav)) and bool(torch.equal(piece, ref_wav[:, s0:s1])) and s0 == 0)
+    else:
+        assert out is None and s1 == wav.shape[1]
     dist.barrier()
     dist.destroy_process_group()
 

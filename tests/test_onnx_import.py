@@ -120,7 +120,7 @@ def test_separator_onnx_backend(cuda, tmp_path):
     from css_b200.synth import make_recording
     from css_b200.utils.model_util import get_onnx_model
 
-    m = _randomised_conformer(blocks=2)
+    m = _randomised_conformer(blocks=2, units=256)
     path = export_onnx(cpu_session_module(m), str(tmp_path / "c1.onnx"), 257, 150)
     cfg = cfg1()["separation"]
     cfg["model_path"] = path
@@ -136,7 +136,7 @@ def test_separator_onnx_backend(cuda, tmp_path):
     f = np.random.default_rng(0).standard_normal((1, 257, 150)).astype(np.float32)
     out = session.run(None, {session.get_inputs()[0].name: f})
     with torch.no_grad():
-        want = cpu_session_module(_randomised_conformer(blocks=2))(torch.from_numpy(f))
+        want = cpu_session_module(_randomised_conformer(blocks=2, units=256))(torch.from_numpy(f))
     assert len(out) == 3 and out[0].shape == (257, 150)
     for a, b in zip(out, want):
         assert rel_inf(torch.from_numpy(a), b) < 1e-4
