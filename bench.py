@@ -25,7 +25,7 @@ if ROOT not in sys.path:
 METRIC = "audio_seconds_separated_per_second_7ch_conformer_css"
 UNIT = "xRT"
 SR = 16000
-TRAIN_DROPOUT = 0.0      # the native training step's dropout rate in the `train` region
+TRAIN_DROPOUT = 0.1      # the reference's --conformer-dropout-rate default (css/models/conformer.py:40), used by train.sh
 CONF_7CH = dict(idim=1799, num_bins=257, num_spk=2, num_noise=1, conformer_attention_dim=256,
                 conformer_attention_heads=4, conformer_linear_units=1024, conformer_num_blocks=16,
                 conformer_kernel_size=33, conformer_dropout_rate=0.1, conformer_relative_pos_emb=True)

@@ -6,7 +6,7 @@
 
 One step = forward + PIT-MSE + backward + (N>1: bucketed NCCL gradient all-reduce overlapped with the backward) +
 clip_grad_norm(5.0) + Adam(lr 1e-4, wd 1e-2) on a batch of 32 synthetic 2-speaker 4 s (250-frame) 7-ch feature
-utterances per GPU, 16-block Conformer (22.0 M parameters, dropout 0), as css/trainer/iteration_types.py:34-63.
+utterances per GPU, 16-block Conformer (22.0 M parameters, dropout 0.1 as in the reference), as css/trainer/iteration_types.py:34-63.
 Prints one JSON line in bench.py's format (value = utterances/s over all GPUs; weak scaling: 32 utterances per GPU).
 The headline benchmark of the repo is bench.py (inference xRT); this file measures the training row of SURVEY 8.
 """
@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--frames", type=int, default=250)
     ap.add_argument("--blocks", type=int, default=16)
     ap.add_argument("--buckets", type=int, default=4)
+    ap.add_argument("--dropout", type=float, default=0.1, help="the reference trains with --conformer-dropout-rate 0.1")
     ap.add_argument("--gemm-mode", type=int, default=2, help="2 bf16 tcgen05 (config 4's compute type), 1 bf16x3 (fp32-class)")
     args = ap.parse_args()
     import torch
@@ -52,7 +53,7 @@ def main():
     dev = torch.device("cuda", local)
     lib = nv.lib()
     nv.set_gemm_mode(args.gemm_mode)
-    conf = dict(CONF_7CH, conformer_num_blocks=args.blocks, conformer_dropout_rate=0.0)
+    conf = dict(CONF_7CH, conformer_num_blocks=args.blocks, conformer_dropout_rate=args.dropout)
     torch.manual_seed(0)
     model = M.build_model("Conformer", conf).train().to(dev)
     engine = model.train_engine()
@@ -141,7 +142,7 @@ def main():
                 "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": {1: "bf16x3->f32", 2: "bf16"}[args.gemm_mode], "data": "synthetic",
                 "config": {"workload": "configs[3]: utterance-level PIT training step, 7-ch Conformer, batch 32 x 250 frames per GPU, "
-                                       "Adam(1e-4, wd 1e-2), clip 5.0, dropout 0", "blocks": args.blocks, "batch_per_gpu": B,
+                                       f"Adam(1e-4, wd 1e-2), clip 5.0, dropout {args.dropout:g}", "blocks": args.blocks, "batch_per_gpu": B,
                            "frames": T, "audio_seconds_per_step": world * B * T * 256 / 16000.0,
                            "parallelism": f"dp{world}, gradient all-reduce over NCCL in {args.buckets} buckets overlapped with backward",
                            "l2": "activations saved per step (~5 GB at 16 blocks) exceed L2", "gemm_mode": args.gemm_mode},

@@ -245,7 +245,7 @@ size_t attention_train_probs_floats(long N, int T, int H) {
 
 // qkv (N*T, 3*H*64) fp32 -> out (N*T, H*64); probs (saved for the backward) and scratch sized by the helpers above
 int attention_train_fwd_launch(const float* qkv, const float* pe, int pe_rows, float* out, float* probs, float* scratch, long N,
-                               int T, int H, int dk, bool split3, cudaStream_t st) {
+                               int T, int H, int dk, bool split3, const CssDrop* drop, cudaStream_t st) {
     CSS_REQUIRE(dk == 64 && T >= 1 && T <= 256 && N > 0 && N * H <= 65535, "attention_train: unsupported shape (T=%d dk=%d N=%ld)", T, dk, N);
     CSS_REQUIRE(!pe || T - 1 <= pe_rows / 2 - 1, "attention_train: relative positions exceed the embedding table");
     const int TP = (T + 31) & ~31, RP = 2 * TP, ld = 3 * H * dk, dm = H * dk;
@@ -266,7 +266,14 @@ int attention_train_fwd_launch(const float* qkv, const float* pe, int pe_rows, f
     const long rows = N * H * T;
     softmax_rel_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(S, pe ? R : nullptr, probs, rows, T, TP, RP);
     if ((rc = css_check_launch("softmax_rel"))) return rc;
-    BMat Pm = {probs, Nl * per, per, TP};
+    const float* pv = probs;
+    if (drop) {
+        // dropout on the probabilities (conformer.py:249): the dropped copy goes into the (now free) score buffer, `probs`
+        // keeps the originals for the softmax backward.  Element index = position in the [head][n][i][TP] buffer.
+        if ((rc = dropout_f32_launch(S, probs, nullptr, (long)N * H * per, *drop, 1.f, 0, st))) return rc;
+        pv = S;
+    }
+    BMat Pm = {pv, Nl * per, per, TP};
     BOut O = {out, (long)dk, (long)T * dm, dm};
     rc = bgemm(false, true, split3, Pm, V, O, T, dk, T, H, (int)N, 1.f, 0, 1, st);
     css_prof_end(st);
@@ -275,7 +282,8 @@ int attention_train_fwd_launch(const float* qkv, const float* pe, int pe_rows, f
 
 // dO (N*T, H*64) -> dqkv (N*T, 3*H*64) overwritten; dpe (pe_rows, 64) accumulated
 int attention_train_bwd_launch(const float* qkv, const float* pe, int pe_rows, const float* probs, const float* dO, float* dqkv,
-                               float* dpe, float* scratch, long N, int T, int H, int dk, bool split3, cudaStream_t st) {
+                               float* dpe, float* scratch, long N, int T, int H, int dk, bool split3, const CssDrop* drop,
+                               cudaStream_t st) {
     CSS_REQUIRE(dk == 64 && T >= 1 && T <= 256 && N > 0 && N * H <= 65535, "attention_train_bwd: unsupported shape");
     const int TP = (T + 31) & ~31, RP = 2 * TP, ld = 3 * H * dk, dm = H * dk;
     const long per = (long)T * TP, perR = (long)T * RP;
@@ -289,11 +297,18 @@ int attention_train_bwd_launch(const float* qkv, const float* pe, int pe_rows, c
     int rc;
     css_prof_begin(1, 14.0 * (double)N * H * T * T * dk, st);
     BOut dPo = {dP, Nl * per, per, TP};
+    if (drop) {
+        // dV = dropout(P)^T dO first: the dropped probabilities are re-derived into the dP buffer, which is free until dP is formed
+        if ((rc = dropout_f32_launch(dP, probs, nullptr, (long)N * H * per, *drop, 1.f, 0, st))) return rc;
+        BMat Pd = {dP, Nl * per, per, TP};
+        if ((rc = bgemm(true, true, split3, Pd, dOm, dV, T, dk, T, H, (int)N, 1.f, 0, 1, st))) return rc;
+    }
     if ((rc = bgemm(false, false, split3, dOm, V, dPo, T, T, dk, H, (int)N, 1.f, 0, 1, st))) return rc;          // dP = dO V^T
+    if (drop && (rc = dropout_f32_launch(dP, dP, nullptr, (long)N * H * per, *drop, 1.f, 0, st))) return rc;     // through the mask
     const long rows = N * H * T;
     ds_rel_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(probs, dP, pe ? dR : nullptr, rows, T, TP, RP);
     if ((rc = css_check_launch("ds_rel"))) return rc;
-    if ((rc = bgemm(true, true, split3, Pm, dOm, dV, T, dk, T, H, (int)N, 1.f, 0, 1, st))) return rc;             // dV = P^T dO
+    if (!drop && (rc = bgemm(true, true, split3, Pm, dOm, dV, T, dk, T, H, (int)N, 1.f, 0, 1, st))) return rc;    // dV = P^T dO
     if ((rc = bgemm(true, true, split3, dSm, Q, dK, T, dk, T, H, (int)N, 1.f, 0, 1, st))) return rc;              // dK = dS^T Q
     if ((rc = bgemm(false, true, split3, dSm, Kk, dQ, T, dk, T, H, (int)N, 1.f, 0, 1, st))) return rc;            // dQ = dS K
     if (pe) {

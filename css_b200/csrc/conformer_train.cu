@@ -26,6 +26,9 @@ struct Trainer {
     LinPlanes embed, head;
     std::vector<BlockLin> bl;
     int ldin, ldh, nhp;   // feature pitch of the planes (idim -> multiple of 64), fp32 head pitch, head K pitch (multiple of 64)
+    float drop_p = 0.f;   // dropout probability of the six nn.Dropout sites (conformer.py:127,249,254,302,317,319)
+    uint32_t drop_seed = 0;
+    CssDrop drop(int block, int k) const { return css_make_drop(drop_p, drop_seed, css_drop_site(block, k)); }
 };
 
 inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -44,7 +47,7 @@ struct Ws {
     // scratch
     double* bn_stats;
     float* bstats;
-    float *g, *dwide, *dn, *datt, *att_scratch, *tmp;
+    float *g, *gm, *dwide, *dn, *datt, *att_scratch, *tmp;
     PlaneMat gP, gT, dwP, dwT, actT;
     size_t bytes;
 };
@@ -80,6 +83,7 @@ void carve(const Trainer* t, long N, int T, char* base, Ws* w) {
     w->bn_stats = reinterpret_cast<double*>(take(2 * d * sizeof(double)));
     w->bstats = f32(2 * d);
     w->g = f32((size_t)M * d);
+    w->gm = f32((size_t)M * d);
     w->dwide = f32((size_t)M * wide);
     w->dn = f32((size_t)M * d);
     w->datt = f32((size_t)M * d);
@@ -132,28 +136,43 @@ int build_planes(Trainer* t, cudaStream_t st) {
 
 int mode_planes() { return css_get_gemm_mode() == 2 ? 1 : 2; }
 
+// blk / site: block index and the site id of the hidden-activation dropout (the output dropout is site + 1)
 int ffn_fwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const LinPlanes& w2, const float* xin, float* xout,
-            const PlaneMat& nP, const PlaneMat& hP, int P, long M, cudaStream_t st) {
+            const PlaneMat& nP, const PlaneMat& hP, int P, long M, int blk, int site, float* tmp, cudaStream_t st) {
     const int d = t->d.d_model, f = t->d.d_ffn;
     const float* p = t->params;
     int rc = layernorm_planes_launch(xin, p + o.ln_g, p + o.ln_b, nullptr, M, d, 1e-5f, 0, nP.ptr, nP.plane_stride, kP, st);
     if (rc) return rc;
     GemmEpilogue e1 = {p + o.b1, 1, 1.f, nullptr, 0, 0.f};
     if ((rc = tc(nP, w1.w, P, M, f, d, e1, nullptr, 0, &hP, st))) return rc;
-    GemmEpilogue e2 = {p + o.b2, 0, 0.5f, xin, d, 0.f};
-    return tc(hP, w2.w, P, M, d, f, e2, xout, d, nullptr, st);
+    if (t->drop_p <= 0.f) {
+        GemmEpilogue e2 = {p + o.b2, 0, 0.5f, xin, d, 0.f};
+        return tc(hP, w2.w, P, M, d, f, e2, xout, d, nullptr, st);
+    }
+    // net = Linear, ReLU, Dropout, Linear, Dropout (conformer.py:314-320): both dropouts as separate passes
+    if ((rc = dropout_planes_launch(hP.ptr, hP.plane_stride, kP, M, f, hP.ld, t->drop(blk, site), st))) return rc;
+    GemmEpilogue e2 = {p + o.b2, 0, 1.f, nullptr, 0, 0.f};
+    if ((rc = tc(hP, w2.w, P, M, d, f, e2, tmp, d, nullptr, st))) return rc;
+    return dropout_f32_launch(xout, tmp, xin, M * d, t->drop(blk, site + 1), 0.5f, 0, st);
 }
 
 // gradient of one macaron FFN: g (d loss / d x_out) -> g (d loss / d x_in), parameter gradients accumulated
 int ffn_bwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const LinPlanes& w2, const float* xin, const PlaneMat& nP,
-            const PlaneMat& hP, Ws& w, int P, cudaStream_t st) {
+            const PlaneMat& hP, Ws& w, int P, int blk, int site, cudaStream_t st) {
     const int d = t->d.d_model, f = t->d.d_ffn;
     const long M = w.M, Mp = w.Mp;
     float* gr = t->grads;
     const float* p = t->params;
     int rc;
     PlaneMat gT = view(w.gT, d, (int)Mp), dhP = view(w.dwP, M, f), dhT = view(w.dwT, f, (int)Mp);
-    if ((rc = split_t_launch(w.g, M, d, d, &w.gP, &gT, Mp, gr + o.b2, 0.5f, st))) return rc;
+    const bool dr = t->drop_p > 0.f;
+    const float hs = dr ? 1.f / (1.f - t->drop_p) : 1.f;          // hidden dropout: dh *= 1/(1-p) where kept (dropped h == 0 is masked)
+    const float* gb = w.g;                                        // gradient w.r.t. the branch output W2 h + b2 (before the 0.5)
+    if (dr) {
+        if ((rc = dropout_f32_launch(w.gm, w.g, nullptr, M * d, t->drop(blk, site + 1), 1.f, 0, st))) return rc;
+        gb = w.gm;
+    }
+    if ((rc = split_t_launch(gb, M, d, d, &w.gP, &gT, Mp, gr + o.b2, 0.5f, st))) return rc;
     // dW2 += 0.5 g^T h
     PlaneMat hT = view(w.actT, f, (int)Mp);
     if ((rc = transpose_planes_launch(hP, M, f, hT, Mp, st))) return rc;
@@ -161,7 +180,7 @@ int ffn_bwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const Lin
     ea.accumulate = 1;
     if ((rc = tc(gT, hT, P, d, f, (int)Mp, ea, gr + o.w2, f, nullptr, st))) return rc;
     // dh = 0.5 g W2, masked by the ReLU
-    GemmEpilogue eh = {nullptr, 0, 0.5f, nullptr, 0, 0.f};
+    GemmEpilogue eh = {nullptr, 0, 0.5f * hs, nullptr, 0, 0.f};
     eh.relu_mask = hP.ptr;
     eh.ldmask = hP.ld;
     if ((rc = tc(w.gP, w2.wT, P, M, f, d, eh, w.dwide, f, nullptr, st))) return rc;
@@ -249,6 +268,14 @@ extern "C" void* css_trainer_create(const css_conformer_train_desc* desc, const 
     return t;
 }
 
+extern "C" int css_trainer_set_dropout(void* trainer, float p, unsigned seed) {
+    Trainer* t = static_cast<Trainer*>(trainer);
+    CSS_REQUIRE(t && p >= 0.f && p < 1.f, "css_trainer_set_dropout: probability %g out of [0, 1)", (double)p);
+    t->drop_p = p;
+    t->drop_seed = seed;
+    return 0;
+}
+
 extern "C" void css_trainer_destroy(void* trainer) {
     Trainer* t = static_cast<Trainer*>(trainer);
     if (t && t->plane_mem) cudaFree(t->plane_mem);
@@ -279,22 +306,36 @@ extern "C" int css_trainer_forward(void* trainer, const float* feat, long N, int
     if ((rc = mvn_time_planes_launch(feat, N, T, c.idim, c.idim, w.fP.ptr, w.fP.plane_stride, t->ldin, kP, st))) return rc;
     GemmEpilogue ee = {p + c.embed_b, 0, 1.f, nullptr, 0, 0.f};
     if ((rc = tc(w.fP, t->embed.w, P, M, d, t->ldin, ee, w.ye, d, nullptr, st))) return rc;
-    if ((rc = layernorm_launch(w.ye, p + c.embed_ln_g, p + c.embed_ln_b, w.xe, M, d, 1e-5f, 1, st))) return rc;
+    const bool dr = t->drop_p > 0.f;
+    if (!dr) {
+        if ((rc = layernorm_launch(w.ye, p + c.embed_ln_g, p + c.embed_ln_b, w.xe, M, d, 1e-5f, 1, st))) return rc;
+    } else {                                      // embed = Linear, LayerNorm, Dropout, ReLU (conformer.py:124-128)
+        if ((rc = layernorm_launch(w.ye, p + c.embed_ln_g, p + c.embed_ln_b, w.tmp, M, d, 1e-5f, 0, st))) return rc;
+        if ((rc = dropout_f32_launch(w.xe, w.tmp, nullptr, M * d, t->drop(-1, 0), 1.f, 1, st))) return rc;
+    }
     const float* pe = c.pe >= 0 ? p + c.pe : nullptr;
     for (int l = 0; l < c.num_blocks; ++l) {
         const css_conformer_block_offsets& o = t->blk[l];
         const BlockLin& b = t->bl[l];
         SavedBlock& s = w.sb[l];
-        if ((rc = ffn_fwd(t, o.ff_in, b.ff_in_w1, b.ff_in_w2, s.x0, s.x1, s.n1, s.h1, P, M, st))) return rc;
+        if ((rc = ffn_fwd(t, o.ff_in, b.ff_in_w1, b.ff_in_w2, s.x0, s.x1, s.n1, s.h1, P, M, l, 0, w.dn, st))) return rc;
         if ((rc = layernorm_planes_launch(s.x1, p + o.att_ln_g, p + o.att_ln_b, nullptr, M, d, 1e-5f, 0, s.n2.ptr, s.n2.plane_stride, kP, st))) return rc;
         GemmEpilogue eq = {p + o.bqkv, 0, 1.f, nullptr, 0, 0.f};
         if ((rc = tc(s.n2, b.wqkv.w, P, M, 3 * d, d, eq, s.qkv, 3 * d, nullptr, st))) return rc;
-        if ((rc = attention_train_fwd_launch(s.qkv, pe, c.pe_rows, w.tmp, s.probs, w.att_scratch, N, T, c.heads, d / c.heads, P == 2, st))) return rc;
+        const CssDrop dp = t->drop(l, 2), dc = t->drop(l, 4);
+        if ((rc = attention_train_fwd_launch(s.qkv, pe, c.pe_rows, w.tmp, s.probs, w.att_scratch, N, T, c.heads, d / c.heads, P == 2,
+                                             dr ? &dp : nullptr, st))) return rc;
         if ((rc = split_planes_launch(w.tmp, M, d, d, s.att, st))) return rc;
-        GemmEpilogue eo = {p + o.bo, 0, 1.f, s.x1, d, 0.f};
-        if ((rc = tc(s.att, b.wo.w, P, M, d, d, eo, s.x2, d, nullptr, st))) return rc;
-        if ((rc = conv_train_fwd_launch(s.x2, s.x3, s.cpre, s.bnsave, w.bn_stats, N, T, conv_params(t, l), st))) return rc;
-        if ((rc = ffn_fwd(t, o.ff_out, b.ff_out_w1, b.ff_out_w2, s.x3, s.x4, s.n4, s.h4, P, M, st))) return rc;
+        if (!dr) {
+            GemmEpilogue eo = {p + o.bo, 0, 1.f, s.x1, d, 0.f};
+            if ((rc = tc(s.att, b.wo.w, P, M, d, d, eo, s.x2, d, nullptr, st))) return rc;
+        } else {                                  // x + dropout(linear_out(.)) (conformer.py:254)
+            GemmEpilogue eo = {p + o.bo, 0, 1.f, nullptr, 0, 0.f};
+            if ((rc = tc(s.att, b.wo.w, P, M, d, d, eo, w.tmp, d, nullptr, st))) return rc;
+            if ((rc = dropout_f32_launch(s.x2, w.tmp, s.x1, M * d, t->drop(l, 3), 1.f, 0, st))) return rc;
+        }
+        if ((rc = conv_train_fwd_launch(s.x2, s.x3, s.cpre, s.bnsave, w.bn_stats, N, T, conv_params(t, l), dr ? &dc : nullptr, st))) return rc;
+        if ((rc = ffn_fwd(t, o.ff_out, b.ff_out_w1, b.ff_out_w2, s.x3, s.x4, s.n4, s.h4, P, M, l, 5, w.dn, st))) return rc;
         const bool last = l == c.num_blocks - 1;
         float* xo = last ? w.xout : w.sb[l + 1].x0;
         if ((rc = layernorm_planes_launch(s.x4, p + o.out_ln_g, p + o.out_ln_b, xo, M, d, 1e-5f, 0, last ? w.yP.ptr : nullptr,
@@ -349,11 +390,22 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             // block output LayerNorm
             LnBwdArgs a0 = {s.x4, p + o.out_ln_g, nullptr, w.g, nullptr, w.g, 0, gr + o.out_ln_g, gr + o.out_ln_b, nullptr, nullptr, nullptr, nullptr};
             if ((rc = ln_bwd_launch(a0, M, d, 1e-5f, false, st))) return rc;
-            if ((rc = ffn_bwd(t, o.ff_out, b.ff_out_w1, b.ff_out_w2, s.x3, s.n4, s.h4, w, P, st))) return rc;
-            if ((rc = conv_train_bwd_launch(s.x2, s.cpre, s.bnsave, w.g, w.dn, w.bstats, N, T, conv_params(t, l), conv_grads(t, l), st))) return rc;
+            const bool dr = t->drop_p > 0.f;
+            if ((rc = ffn_bwd(t, o.ff_out, b.ff_out_w1, b.ff_out_w2, s.x3, s.n4, s.h4, w, P, l, 5, st))) return rc;
+            const float* gconv = w.g;
+            if (dr) {
+                if ((rc = dropout_f32_launch(w.gm, w.g, nullptr, M * d, t->drop(l, 4), 1.f, 0, st))) return rc;
+                gconv = w.gm;
+            }
+            if ((rc = conv_train_bwd_launch(s.x2, s.cpre, s.bnsave, w.g, gconv, w.dn, w.bstats, N, T, conv_params(t, l), conv_grads(t, l), st))) return rc;
             // ---- self-attention ----
             PlaneMat gT = view(w.gT, d, (int)Mp);
-            if ((rc = split_t_launch(w.g, M, d, d, &w.gP, &gT, Mp, gr + o.bo, 1.f, st))) return rc;
+            const float* gatt = w.g;
+            if (dr) {
+                if ((rc = dropout_f32_launch(w.gm, w.g, nullptr, M * d, t->drop(l, 3), 1.f, 0, st))) return rc;
+                gatt = w.gm;
+            }
+            if ((rc = split_t_launch(gatt, M, d, d, &w.gP, &gT, Mp, gr + o.bo, 1.f, st))) return rc;
             PlaneMat aT = view(w.actT, d, (int)Mp);
             if ((rc = transpose_planes_launch(s.att, M, d, aT, Mp, st))) return rc;
             GemmEpilogue ea = {nullptr, 0, 1.f, nullptr, 0, 0.f};
@@ -362,8 +414,9 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             GemmEpilogue ed = {nullptr, 0, 1.f, nullptr, 0, 0.f};
             if ((rc = tc(w.gP, b.wo.wT, P, M, d, d, ed, w.datt, d, nullptr, st))) return rc;
             float* dqkv = w.dwide;   // (M, 3d)
+            const CssDrop dp = t->drop(l, 2);
             if ((rc = attention_train_bwd_launch(s.qkv, pe, c.pe_rows, s.probs, w.datt, dqkv, pe ? gr + c.pe : nullptr, w.att_scratch,
-                                                 N, T, c.heads, d / c.heads, P == 2, st))) return rc;
+                                                 N, T, c.heads, d / c.heads, P == 2, dr ? &dp : nullptr, st))) return rc;
             PlaneMat dqP = view(w.dwP, M, 3 * d), dqT = view(w.dwT, 3 * d, (int)Mp);
             if ((rc = split_t_launch(dqkv, M, 3 * d, 3 * d, &dqP, &dqT, Mp, gr + o.bqkv, 1.f, st))) return rc;
             PlaneMat nT = view(w.actT, d, (int)Mp);
@@ -372,9 +425,13 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             if ((rc = tc(dqP, b.wqkv.wT, P, M, d, 3 * d, ed, w.dn, d, nullptr, st))) return rc;
             LnBwdArgs a1 = {s.x1, p + o.att_ln_g, nullptr, w.dn, nullptr, w.g, 1, gr + o.att_ln_g, gr + o.att_ln_b, nullptr, nullptr, nullptr, nullptr};
             if ((rc = ln_bwd_launch(a1, M, d, 1e-5f, false, st))) return rc;
-            if ((rc = ffn_bwd(t, o.ff_in, b.ff_in_w1, b.ff_in_w2, s.x0, s.n1, s.h1, w, P, st))) return rc;
+            if ((rc = ffn_bwd(t, o.ff_in, b.ff_in_w1, b.ff_in_w2, s.x0, s.n1, s.h1, w, P, l, 0, st))) return rc;
         } else {
-            // ---- input embedding: x_e = relu(LN(f W^T + b)) ----
+            // ---- input embedding: x_e = relu(dropout(LN(f W^T + b))) ----
+            if (t->drop_p > 0.f) {        // kept elements carry 1/(1-p); dropped ones have x_e == 0 and fall to the ReLU mask
+                const CssDrop none = {0, 0, 1.f / (1.f - t->drop_p)};
+                if ((rc = dropout_f32_launch(w.g, w.g, nullptr, M * d, none, 1.f, 0, st))) return rc;
+            }
             LnBwdArgs a = {w.ye, p + c.embed_ln_g, nullptr, w.g, w.xe, w.g, 0, gr + c.embed_ln_g, gr + c.embed_ln_b, nullptr, nullptr, nullptr, nullptr};
             if ((rc = ln_bwd_launch(a, M, d, 1e-5f, false, st))) return rc;
             PlaneMat gT = view(w.gT, d, (int)Mp);

@@ -1,5 +1,6 @@
 // Internal launch interface of the training-step kernels (train_ops.cu), used by conformer_train.cu.
 #pragma once
+#include "dropout.h"
 #include "gemm.h"
 #include <cuda_runtime.h>
 
@@ -35,11 +36,13 @@ int ln_bwd_launch(const LnBwdArgs& a, long M, int d, float eps, bool glu, cudaSt
 // split3: three-term TF32 split (fp32-class accuracy) instead of single TF32 products.
 size_t attention_train_scratch_floats(long N, int T, int H);
 size_t attention_train_probs_floats(long N, int T, int H);
+// drop != null: dropout on the attention probabilities (conformer.py:249); probs keeps the un-dropped probabilities
 int attention_train_fwd_launch(const float* qkv, const float* pe, int pe_rows, float* out, float* probs, float* scratch, long N,
-                               int T, int H, int dk, bool split3, cudaStream_t st);
+                               int T, int H, int dk, bool split3, const CssDrop* drop, cudaStream_t st);
 // dO (N*T, H*64) -> dqkv (N*T, 3*H*64) overwritten, dpe (pe_rows, 64) accumulated
 int attention_train_bwd_launch(const float* qkv, const float* pe, int pe_rows, const float* probs, const float* dO, float* dqkv,
-                               float* dpe, float* scratch, long N, int T, int H, int dk, bool split3, cudaStream_t st);
+                               float* dpe, float* scratch, long N, int T, int H, int dk, bool split3, const CssDrop* drop,
+                               cudaStream_t st);
 
 struct ConvTrainParams {
     const float *ln_g, *ln_b, *pw1_w, *pw1_b, *dw_w, *dw_b, *bn_g, *bn_b, *pw2_w, *pw2_b;
@@ -50,11 +53,13 @@ struct ConvTrainGrads {
 };
 // out = x + ConvModule_train(x): batch-statistics BatchNorm.  cpre (M,256) pre-BN activations and bnsave (512: mean, rstd)
 // are kept for the backward; stats (512 doubles) is scratch.
+// drop != null: out = x + dropout(ConvModule_train(x)) (conformer.py:302), element index = row * 256 + channel
 int conv_train_fwd_launch(const float* x, float* out, float* cpre, float* bnsave, double* stats, long N, int T,
-                          const ConvTrainParams& p, cudaStream_t st);
+                          const ConvTrainParams& p, const CssDrop* drop, cudaStream_t st);
 // g (M,256): gradient w.r.t. the module output on entry, w.r.t. its input on return.  du: scratch (M,256); bstats: 512 floats.
-int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave, float* g, float* du, float* bstats, long N,
-                          int T, const ConvTrainParams& p, const ConvTrainGrads& gr, cudaStream_t st);
+// gbranch: gradient w.r.t. the module's BRANCH output (== g without dropout, g * mask / (1-p) with it); read only.
+int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave, float* g, const float* gbranch, float* du,
+                          float* bstats, long N, int T, const ConvTrainParams& p, const ConvTrainGrads& gr, cudaStream_t st);
 
 // y_pred[n][k][t][f] = head[(n,t)][k*nb + f] * feat[(n,t)][f]   (css/models/conformer.py:103-104 with f_orig[..., :nb])
 int ypred_launch(const float* head, int ldh, const float* feat, int ldf, float* ypred, long N, int T, int nb, int K,

@@ -330,7 +330,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, double coun
 
 __global__ void __launch_bounds__(256)
 conv_train_apply_kernel(const float* __restrict__ x, const float* __restrict__ cpre, const float* __restrict__ bnsave,
-                        float* __restrict__ out, long M, ConvTrainParams p) {
+                        float* __restrict__ out, long M, ConvTrainParams p, CssDrop dr, int use_drop) {
     const float w2 = p.pw2_w[0], b2 = p.pw2_b[0];
     const long total = M * (CT_D / 4);
     for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
@@ -342,10 +342,19 @@ conv_train_apply_kernel(const float* __restrict__ x, const float* __restrict__ c
         const float4 g = reinterpret_cast<const float4*>(p.bn_g)[c4];
         const float4 b = reinterpret_cast<const float4*>(p.bn_b)[c4];
         float4 o;
-        o.x = xv.x + fmaxf((cv.x - mu.x) * rs.x * g.x + b.x, 0.f) * w2 + b2;
-        o.y = xv.y + fmaxf((cv.y - mu.y) * rs.y * g.y + b.y, 0.f) * w2 + b2;
-        o.z = xv.z + fmaxf((cv.z - mu.z) * rs.z * g.z + b.z, 0.f) * w2 + b2;
-        o.w = xv.w + fmaxf((cv.w - mu.w) * rs.w * g.w + b.w, 0.f) * w2 + b2;
+        if (use_drop) {
+            const uint32_t e = (uint32_t)(i * 4);
+            float br[4] = {fmaxf((cv.x - mu.x) * rs.x * g.x + b.x, 0.f) * w2 + b2, fmaxf((cv.y - mu.y) * rs.y * g.y + b.y, 0.f) * w2 + b2,
+                           fmaxf((cv.z - mu.z) * rs.z * g.z + b.z, 0.f) * w2 + b2, fmaxf((cv.w - mu.w) * rs.w * g.w + b.w, 0.f) * w2 + b2};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) br[k] = css_dropout_keep(dr, e + k) ? br[k] * dr.scale : 0.f;
+            o = make_float4(xv.x + br[0], xv.y + br[1], xv.z + br[2], xv.w + br[3]);
+        } else {
+            o.x = xv.x + fmaxf((cv.x - mu.x) * rs.x * g.x + b.x, 0.f) * w2 + b2;
+            o.y = xv.y + fmaxf((cv.y - mu.y) * rs.y * g.y + b.y, 0.f) * w2 + b2;
+            o.z = xv.z + fmaxf((cv.z - mu.z) * rs.z * g.z + b.z, 0.f) * w2 + b2;
+            o.w = xv.w + fmaxf((cv.w - mu.w) * rs.w * g.w + b.w, 0.f) * w2 + b2;
+        }
         reinterpret_cast<float4*>(out)[i] = o;
     }
 }
@@ -357,7 +366,7 @@ static int conv_tiles(int T, int max_tile, int* tile_len) {
 }
 
 int conv_train_fwd_launch(const float* x, float* out, float* cpre, float* bnsave, double* stats, long N, int T,
-                          const ConvTrainParams& p, cudaStream_t st) {
+                          const ConvTrainParams& p, const CssDrop* drop, cudaStream_t st) {
     CSS_REQUIRE(N > 0 && T > 0 && N * (long)T > 1 && x != out, "conv_train_fwd: bad arguments");
     int tile_len;
     const int n_tiles = conv_tiles(T, 188, &tile_len);
@@ -376,7 +385,8 @@ int conv_train_fwd_launch(const float* x, float* out, float* cpre, float* bnsave
     const long M = N * T;
     long g = (M * (CT_D / 4) + 255) / 256;
     if (g > 148 * 8) g = 148 * 8;
-    conv_train_apply_kernel<<<(unsigned)g, 256, 0, st>>>(x, cpre, bnsave, out, M, p);
+    CSS_REQUIRE(!drop || M * CT_D < (1L << 32), "conv_train_fwd: too many elements for the dropout index");
+    conv_train_apply_kernel<<<(unsigned)g, 256, 0, st>>>(x, cpre, bnsave, out, M, p, drop ? *drop : CssDrop{0, 0, 1.f}, drop ? 1 : 0);
     return css_check_launch("conv_train_apply");
 }
 
@@ -496,13 +506,13 @@ conv_bwd_dw_kernel(const float* __restrict__ x, const float* __restrict__ cpre, 
     }
 }
 
-int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave, float* g, float* du, float* bstats, long N,
-                          int T, const ConvTrainParams& p, const ConvTrainGrads& gr, cudaStream_t st) {
+int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave, float* g, const float* gbranch, float* du,
+                          float* bstats, long N, int T, const ConvTrainParams& p, const ConvTrainGrads& gr, cudaStream_t st) {
     CSS_REQUIRE(N > 0 && T > 0, "conv_train_bwd: bad arguments");
     const long M = N * T;
     cudaMemsetAsync(bstats, 0, 2 * CT_D * sizeof(float), st);
     const int rows_per_cta = 32;
-    conv_bwd_stats_kernel<<<(unsigned)((M + rows_per_cta - 1) / rows_per_cta), CT_D, 0, st>>>(g, cpre, bnsave, M, rows_per_cta,
+    conv_bwd_stats_kernel<<<(unsigned)((M + rows_per_cta - 1) / rows_per_cta), CT_D, 0, st>>>(gbranch, cpre, bnsave, M, rows_per_cta,
                                                                                              bstats, p, gr);
     int rc = css_check_launch("conv_bwd_stats");
     if (rc) return rc;
@@ -512,7 +522,7 @@ int conv_train_bwd_launch(const float* x, const float* cpre, const float* bnsave
         cudaFuncSetAttribute(conv_bwd_dw_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     }
     dim3 grid((unsigned)N, (T + CB_TILE - 1) / CB_TILE);
-    conv_bwd_dw_kernel<<<grid, 512, smem, st>>>(x, cpre, bnsave, g, bstats, 1.f / (float)M, du, T, p, gr);
+    conv_bwd_dw_kernel<<<grid, 512, smem, st>>>(x, cpre, bnsave, gbranch, bstats, 1.f / (float)M, du, T, p, gr);
     if ((rc = css_check_launch("conv_bwd_dw"))) return rc;
     LnBwdArgs a = {x, p.ln_g, p.ln_b, du, nullptr, g, 1, gr.ln_g, gr.ln_b, p.pw1_w, p.pw1_b, gr.pw1_w, gr.pw1_b};
     return ln_bwd_launch(a, M, CT_D, 1e-5f, true, st);

@@ -6,7 +6,8 @@ contract), same default PyTorch initialisation order, so a 
 ``torch.manual_seed`` yields the reference's weights.  The torch modules below are parameter
 containers only: ``forward`` hands the weight pointers to ``css_conformer_forward`` in
 libcss_b200.so.  In eval mode dropout is the identity and BatchNorm uses running stats; in train mode ``forward`` runs the native
-training step (css_b200/trainer), with batch-statistics BatchNorm and a native backward.
+training step (css_b200/trainer), with batch-statistics BatchNorm, counter-based dropout masks at the reference's six
+nn.Dropout sites (csrc/dropout.cu) and a native backward.
 """
 import ctypes
 
@@ -250,8 +251,6 @@ class Conformer(nn.Module):
         if F != self.in_features:
             raise RuntimeError(f"expected {self.in_features} input features, got {F}")
         if self.training and torch.is_grad_enabled():
-            if self.conf["dropout_rate"] != 0.0:
-                raise nv.NativeError("the native training step implements dropout_rate 0 (set conformer_dropout_rate=0.0)")
             from ..trainer.autograd import train_forward
 
             return train_forward(self, f)

@@ -139,6 +139,12 @@ class ConformerTrainEngine:
         self.ws = None
         self.ws_shape = None
         self.num_blocks = len(enc.encoders)
+        # nn.Dropout at the reference's six sites (css/models/conformer.py:127,249,254,302,317,319): counter-based masks,
+        # a fresh seed per forward (dropout_seed + number of forwards so far); the backward re-derives the same masks
+        self.dropout_p = float(conf.get("dropout_rate", 0.0))
+        self.dropout_seed = int(torch.initial_seed()) & 0x7FFFFFFF
+        self.forward_calls = 0
+        self.last_dropout_seed = None
         self.anchor = torch.zeros(1, device=dev, requires_grad=True)   # makes the native forward's output require grad
         self.exchange = None   # GradientExchange for data-parallel runs
         model.invalidate()     # packed inference weights referenced the old parameter storage
@@ -188,6 +194,11 @@ class ConformerTrainEngine:
         d = self.desc
         y_pred = torch.empty(N, d.num_spk, T, d.num_bins, dtype=torch.float32, device=feat.device)
         head = torch.empty(N * T, d.num_bins * d.num_out, dtype=torch.float32, device=feat.device) if want_masks else None
+        p = self.dropout_p if self.model.training else 0.0
+        self.last_dropout_seed = (self.dropout_seed + self.forward_calls) & 0xFFFFFFFF
+        self.forward_calls += 1
+        nv.check(self.lib.css_trainer_set_dropout(ctypes.c_void_p(self.handle), nv.c_float(p), ctypes.c_uint(self.last_dropout_seed)),
+                 "css_trainer_set_dropout")
         nv.call("css_trainer_forward", ctypes.c_void_p(self.handle), nv.ptr(feat), nv.c_long(N), nv.c_int(T), nv.ptr(y_pred),
                 nv.ptr(head), nv.c_int(0 if head is None else head.stride(0)), nv.ptr(ws), nv.c_size_t(ws.numel()))
         self.bn_tracked += 1

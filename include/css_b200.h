@@ -166,6 +166,13 @@ typedef struct {
 void* css_trainer_create(const css_conformer_train_desc* desc_host, const css_conformer_block_offsets* blocks_host,
                          float* params, float* grads, float* bn_running);
 void css_trainer_destroy(void* trainer);
+/* nn.Dropout(p) at the six sites of css/models/conformer.py:127,249,254,302,317,319 for the following forward/backward
+ * pairs; masks are a pure function of (seed, site, element) -- pass a new seed per step.  p = 0 (default) disables it. */
+int css_trainer_set_dropout(void* trainer, float p, unsigned seed);
+/* the keep-mask (uint8, 1 = kept) the training kernels apply at (p, seed, site) to elements 0..n-1: site 0 = embedding,
+ * block l: 1 + 8 l + k with k = 0 FFN-in hidden, 1 FFN-in output, 2 attention probabilities ([head][n][i][T rounded up to
+ * 32]), 3 attention output, 4 conv module, 5 FFN-out hidden, 6 FFN-out output; 2-D sites index row * cols + col */
+int css_dropout_mask(unsigned char* mask, long n, float p, unsigned seed, unsigned site, css_stream_t stream);
 size_t css_trainer_workspace_bytes(const void* trainer, long N, int T);
 /* Conformer.forward in train mode (css/models/conformer.py:83-104; dropout probability 0): feat (N,T,idim) raw features
  * -> y_pred (N,num_spk,T,num_bins) and optionally the head activations masks_head (N*T, ld_head).  Activations needed by

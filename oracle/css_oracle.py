@@ -102,15 +102,19 @@ def mvn_time(f):
     return (f - f.mean(-2, keepdim=True)) / (f.std(-2, keepdim=True) + EPS)
 
 
-def _conformer_ffn(x, sd, p):
-    """css/models/conformer.py:306-326."""
+def _no_drop(x, block, k):
+    return x
+
+
+def _conformer_ffn(x, sd, p, drop=_no_drop, block=0, k=0):
+    """css/models/conformer.py:306-326 (Linear, ReLU, Dropout, Linear, Dropout)."""
     y = _layer_norm(x, sd, p + ".layer_norm")
-    y = torch.relu(_linear(y, sd, p + ".net.0"))
-    return _linear(y, sd, p + ".net.3")
+    y = drop(torch.relu(_linear(y, sd, p + ".net.0")), block, k)
+    return drop(_linear(y, sd, p + ".net.3"), block, k + 1)
 
 
-def _conformer_mhsa(x, pos_k, sd, p, heads):
-    """css/models/conformer.py:213-254 (mask=None, dropout off)."""
+def _conformer_mhsa(x, pos_k, sd, p, heads, drop=_no_drop, block=0):
+    """css/models/conformer.py:213-254 (mask=None); dropout on the probabilities (:249) and on the output (:254)."""
     n, t, d = x.shape
     dk = d // heads
     y = _layer_norm(x, sd, p + ".layer_norm")
@@ -123,13 +127,13 @@ def _conformer_mhsa(x, pos_k, sd, p, heads):
         qq = q.contiguous().view(n * heads, t, dk).transpose(0, 1)
         b = torch.matmul(qq, pos_k.transpose(-2, -1)).transpose(0, 1).view(n, heads, t, t)
         a = a + b
-    attn = torch.softmax(a / math.sqrt(dk), dim=-1)
+    attn = drop(torch.softmax(a / math.sqrt(dk), dim=-1), block, 2)
     o = torch.matmul(attn, v).transpose(1, 2).contiguous().view(n, t, d)
-    return _linear(o, sd, p + ".linear_out")
+    return drop(_linear(o, sd, p + ".linear_out"), block, 3)
 
 
-def _conformer_conv(x, sd, p, training_stats=False):
-    """css/models/conformer.py:289-303.  The two 'pointwise convs' are scalar affines."""
+def _conformer_conv(x, sd, p, training_stats=False, drop=_no_drop, block=0):
+    """css/models/conformer.py:289-303.  The two 'pointwise convs' are scalar affines; dropout at the end (:302)."""
     y = _layer_norm(x, sd, p + ".layer_norm")
     w1, b1 = sd[p + ".pw_conv_1.weight"].view(2), sd[p + ".pw_conv_1.bias"]
     y = (y * w1[0] + b1[0]) * torch.sigmoid(y * w1[1] + b1[1])
@@ -142,19 +146,22 @@ def _conformer_conv(x, sd, p, training_stats=False):
         training_stats, 0.0 if training_stats else 0.1, 1e-5,
     )
     y = torch.relu(y).transpose(1, 2)
-    return y * sd[p + ".pw_conv_2.weight"].view(()) + sd[p + ".pw_conv_2.bias"].view(())
+    return drop(y * sd[p + ".pw_conv_2.weight"].view(()) + sd[p + ".pw_conv_2.bias"].view(()), block, 4)
 
 
-def conformer_masks(f, sd, heads=4, num_out=3, training=False):
+def conformer_masks(f, sd, heads=4, num_out=3, training=False, drop=None):
     """Reference Conformer forward up to the masks.  css/models/conformer.py:83-101,152-165.
 
     f: (N, T, F) -> list of num_out tensors (N, T, num_bins).  ``training``: BatchNorm uses batch statistics
-    (model.train() with dropout probability 0).
+    (model.train()).  ``drop``: callable (x, block, k) -> x applied at the reference's six nn.Dropout sites (block -1 /
+    k 0 = embedding; per block k = 0 FFN-in hidden, 1 FFN-in output, 2 attention probabilities (n, heads, t, t),
+    3 attention output, 4 conv module, 5 FFN-out hidden, 6 FFN-out output); None = dropout probability 0.
     """
     if f.ndim == 4:
         f = f.squeeze(0)
+    drop = drop or _no_drop
     x = mvn_time(f)
-    x = torch.relu(_layer_norm(_linear(x, sd, "conformer.embed.0"), sd, "conformer.embed.1"))
+    x = torch.relu(drop(_layer_norm(_linear(x, sd, "conformer.embed.0"), sd, "conformer.embed.1"), -1, 0))
     t = x.shape[1]
     pos_k = None
     if "conformer.pos_emb.pe_k.weight" in sd:
@@ -166,10 +173,10 @@ def conformer_masks(f, sd, heads=4, num_out=3, training=False):
     nblk = 1 + max(int(k.split(".")[2]) for k in sd if k.startswith("conformer.encoders."))
     for i in range(nblk):
         p = "conformer.encoders.%d" % i
-        x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_in")
-        x = x + _conformer_mhsa(x, pos_k, sd, p + ".self_attn", heads)
-        x = x + _conformer_conv(x, sd, p + ".conv", training)
-        x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_out")
+        x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_in", drop, i, 0)
+        x = x + _conformer_mhsa(x, pos_k, sd, p + ".self_attn", heads, drop, i)
+        x = x + _conformer_conv(x, sd, p + ".conv", training, drop, i)
+        x = x + 0.5 * _conformer_ffn(x, sd, p + ".feed_forward_out", drop, i, 5)
         x = _layer_norm(x, sd, p + ".layer_norm")
     m = torch.relu(_linear(x, sd, "linear"))
     return list(torch.chunk(m, num_out, 2))
@@ -217,21 +224,21 @@ def _bilstm(x, sd, p):
     return torch.cat([fw, bw], dim=-1)
 
 
-def model_masks(f, sd, heads=4, training=False):
+def model_masks(f, sd, heads=4, training=False, drop=None):
     """Dispatch on the state_dict's own key names (the reference's .mdl interchange contract)."""
     if any(k.startswith("conformer.") for k in sd):
-        return conformer_masks(f, sd, heads, training=training)
+        return conformer_masks(f, sd, heads, training=training, drop=drop)
     return blstm_masks(f, sd)
 
 
-def model_forward(f, sd, num_bins=257, heads=4, training=False):
+def model_forward(f, sd, num_bins=257, heads=4, training=False, drop=None):
     """(y_pred, masks) with the documented patch D3 (``f_orig[..., :num_bins]``).
 
     css/models/conformer.py:103-104, css/models/blstm.py:87-88; SURVEY.md A.9 D3.
     """
     if f.ndim == 4:
         f = f.squeeze(0)
-    masks = model_masks(f, sd, heads, training)
+    masks = model_masks(f, sd, heads, training, drop)
     y_pred = torch.stack([m * f[..., :num_bins] for m in masks[:-1]], dim=1)
     return y_pred, masks
 
@@ -538,16 +545,17 @@ def pit_mse(y_pred, y_true, return_permutation=False):
     return (loss, perms) if return_permutation else loss
 
 
-def mse_objective(sd, sample, heads=4, training=False):
+def mse_objective(sd, sample, heads=4, training=False, drop=None):
     """MeanSquaredError.forward with patches D3/D4.  css/objectives/mse.py:22-37."""
-    y_pred, _ = model_forward(sample["mix"], sd, heads=heads, training=training)
+    y_pred, _ = model_forward(sample["mix"], sd, heads=heads, training=training, drop=drop)
     y_true = torch.stack((sample["source1"], sample["source2"]), dim=1)
     return pit_mse(y_pred, y_true)
 
 
-def train_steps(sd, samples, lr=1e-4, weight_decay=1e-2, grad_thresh=5.0, heads=4):
+def train_steps(sd, samples, lr=1e-4, weight_decay=1e-2, grad_thresh=5.0, heads=4, drops=None):
     """The body of train_one_epoch (css/trainer/iteration_types.py:34-63) with the optimiser of
-    scripts/python/train.py:209-211 (torch.optim.Adam(lr, weight_decay)) and train.sh:16 (clip 5.0), dropout 0.
+    scripts/python/train.py:209-211 (torch.optim.Adam(lr, weight_decay)) and train.sh:16 (clip 5.0).  ``drops``: one
+    dropout hook per step (see conformer_masks) -- the masks are an INPUT here; None = dropout probability 0.
 
     sd: state_dict (modified in place: parameters updated, BatchNorm running stats are NOT tracked here).
     Returns per step: loss, gradient norm (before clipping), and the gradients of the first step.
@@ -559,7 +567,7 @@ def train_steps(sd, samples, lr=1e-4, weight_decay=1e-2, grad_thresh=5.0, heads=
     for step, sample in enumerate(samples):
         live = dict(sd)
         live.update(zip(names, params))
-        loss = mse_objective(live, sample, heads=heads, training=True)
+        loss = mse_objective(live, sample, heads=heads, training=True, drop=drops[step] if drops else None)
         opt.zero_grad()
         loss.backward()
         if step == 0:

@@ -71,11 +71,11 @@ def train_samples(steps, n, t, seed=21, idim=1799):
     return out
 
 
-def train_conformer(num_blocks=2, idim=1799, seed=3):
-    """Case-E model: reference init under `seed`, dropout 0 (the native step's supported setting), train mode."""
+def train_conformer(num_blocks=2, idim=1799, seed=3, dropout=0.0):
+    """Case-E model: reference init under `seed`, train mode (dropout 0 unless asked: the reference-made fixtures use 0)."""
     import css_b200.models as M
 
-    conf = dict(CONF_C7, conformer_num_blocks=num_blocks, idim=idim, conformer_dropout_rate=0.0)
+    conf = dict(CONF_C7, conformer_num_blocks=num_blocks, idim=idim, conformer_dropout_rate=dropout)
     torch.manual_seed(seed)
     return M.build_model("Conformer", conf).train()
 
@@ -115,3 +115,48 @@ def doa_case(seed=77):
         mask[b, :, :, 0] = torch.where(own, 0.9, 0.1) + 0.05 * torch.rand(F, T, generator=g)
         mask[b, :, :, 1] = torch.where(own, 0.1, 0.9) - 0.05 * torch.rand(F, T, generator=g)
     return X, mask, pairs
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# numpy mirror of the counter-based dropout masks of css_b200/csrc/dropout.cu (csrc/dropout.h: css_dropout_mix / keep)
+# ---------------------------------------------------------------------------------------------------------------
+def _mix32(x):
+    import numpy as np
+
+    x = x.astype(np.uint32)
+    x ^= x >> np.uint32(16)
+    x *= np.uint32(0x7FEB352D)
+    x ^= x >> np.uint32(15)
+    x *= np.uint32(0x846CA68B)
+    x ^= x >> np.uint32(16)
+    return x
+
+
+def dropout_mask(n, p, seed, site):
+    """keep-mask (bool, length n) of (p, seed, site): keep = (mix(index ^ mix(seed * 0x9E3779B1 + site)) >> 8) >= floor(p 2^24)."""
+    import numpy as np
+
+    with np.errstate(over="ignore"):
+        key = _mix32(np.array([(seed * 0x9E3779B1 + site) & 0xFFFFFFFF], dtype=np.uint64).astype(np.uint32))[0]
+        h = _mix32(np.arange(n, dtype=np.uint32) ^ key)
+    return torch.from_numpy((h >> np.uint32(8)) >= np.uint32(int(p * 16777216.0)))
+
+
+class DropHook:
+    """The dropout hook of oracle.css_oracle.conformer_masks with the masks the CUDA kernels use for (p, seed)."""
+
+    def __init__(self, p, seed):
+        self.p, self.seed = p, seed
+
+    def __call__(self, x, block, k):
+        if self.p <= 0:
+            return x
+        site = 0 if block < 0 else 1 + 8 * block + k
+        scale = 1.0 / (1.0 - self.p)
+        if k == 2 and block >= 0:                   # probabilities (n, H, t, t): kernel buffer is [H][n][t][t rounded up to 32]
+            n, h, t, _ = x.shape
+            tp = (t + 31) // 32 * 32
+            m = dropout_mask(h * n * t * tp, self.p, self.seed, site).view(h, n, t, tp)[..., :t].permute(1, 0, 2, 3)
+        else:
+            m = dropout_mask(x.numel(), self.p, self.seed, site).view(x.shape)
+        return x * m.to(x.dtype) * scale

@@ -1,5 +1,6 @@
 """Parity of the native training step against the reference-generated golden vectors
 (tests/golden/golden_train.npz, made by tests/golden/make_golden_train.py from /root/reference) and the CPU oracle."""
+import ctypes
 import os
 
 import numpy as np
@@ -101,6 +102,100 @@ def test_all_gradients_vs_oracle_t250(cuda, mode, tol):
         print(f"mode {mode}: worst gradient rel-l2 {worst:.2e}")
     finally:
         nv.set_gemm_mode(1)
+
+
+def test_dropout_masks_match_numpy_mirror(cuda):
+    """css_dropout_mask (the mask the training kernels apply) == tests.helpers.dropout_mask, keep rate ~ 1 - p."""
+    from css_b200 import _native as nv
+    from tests.helpers import dropout_mask
+
+    for p, seed, site in ((0.1, 1234, 0), (0.1, 1234, 19), (0.5, 7, 3), (0.0, 5, 1)):
+        n = 1 << 20
+        m = torch.empty(n, dtype=torch.uint8, device=cuda)
+        nv.call("css_dropout_mask", nv.ptr(m), nv.c_long(n), nv.c_float(p), ctypes.c_uint(seed), ctypes.c_uint(site))
+        ref = dropout_mask(n, p, seed, site)
+        assert torch.equal(m.cpu().bool(), ref)
+        assert abs(float(ref.float().mean()) - (1 - p)) < 3e-3
+    a, b = dropout_mask(1 << 16, 0.3, 1, 5), dropout_mask(1 << 16, 0.3, 2, 5)
+    assert 0.35 < float((a ^ b).float().mean()) < 0.5          # different seeds: independent masks
+
+
+@pytest.mark.parametrize("mode,tol", [(1, 8e-3)])      # the p = 0 path at the same depth (2 blocks, T = 250) measures 5.8e-3
+def test_dropout_gradients_vs_oracle_with_same_masks(cuda, mode, tol):
+    """Training with the reference's dropout rate 0.1 (css/models/conformer.py:40; sites :127,249,254,302,317,319): the
+    native forward/backward against torch autograd over the oracle fed with the SAME counter-based masks -- loss and
+    every gradient tensor.  (PyTorch's own Philox masks are not reproducible outside PyTorch: with identical masks the
+    network function is the reference's.)"""
+    from css_b200 import _native as nv
+    from css_b200.objectives import build_objective
+    from oracle import css_oracle as O
+    from tests.helpers import DropHook
+
+    nv.set_gemm_mode(mode)
+    model = train_conformer(num_blocks=2, dropout=0.1).to(cuda)
+    sd = cpu_state_dict(model)
+    b = train_samples(1, 3, 250, seed=6)[0]
+    engine = model.train_engine()
+    engine.dropout_seed, engine.forward_calls = 4321, 0
+    loss = build_objective("MSE", {})(model, _to(b, cuda), device=cuda)
+    loss.backward()
+    assert engine.last_dropout_seed == 4321
+    ref = O.train_steps(sd, [b], drops=[DropHook(0.1, 4321)])
+    ref0 = O.train_steps(cpu_state_dict(model), [b])
+    assert abs(ref["loss"][0] - ref0["loss"][0]) > 1e-4 * ref0["loss"][0]          # the masks do change the function
+    assert abs(float(loss) - ref["loss"][0]) <= 1e-5 * ref["loss"][0]
+    total = float(torch.sqrt(sum(g.double().pow(2).sum() for g in ref["grads"].values())))
+    worst = 0.0
+    for name, p in model.named_parameters():
+        r = ref["grads"][name]
+        err = float((p.grad.cpu() - r).norm() / max(float(r.norm()), 1e-3 * total))
+        worst = max(worst, err)
+        assert err < tol, f"{name}: rel-l2 {err:.2e}"
+    print(f"dropout 0.1, mode {mode}: worst gradient rel-l2 {worst:.2e}")
+    # eval mode ignores dropout; a second training forward draws new masks
+    model.eval()
+    with torch.no_grad():
+        y0, _ = model(b["mix"].to(cuda))
+        y1, _ = model(b["mix"].to(cuda))
+    assert torch.equal(y0, y1)
+    model.train()
+    l2 = build_objective("MSE", {})(model, _to(b, cuda), device=cuda)
+    assert engine.last_dropout_seed == 4322 and float(l2) != float(loss)
+
+
+def test_bf16_mode_loss_curve_tracks_fp32_class_mode(cuda):
+    """Mode 2 (single-plane bf16 tensor-core GEMMs, BASELINE configs[3]'s compute type) must TRAIN like mode 1 (split-bf16,
+    fp32-class): 200 Adam steps on the same batches from the same initial weights, dropout 0; the loss curves stay together
+    (final loss within 2 %, no step further apart than 5 % of the initial loss) and both fall by > 30 %."""
+    from css_b200 import _native as nv
+    from css_b200.objectives import build_objective
+    from css_b200.trainer import FusedAdam
+
+    batches = [_to(b, cuda) for b in train_samples(8, 4, 60, seed=11, idim=257)]
+    curves = {}
+    try:
+        for mode in (1, 2):
+            nv.set_gemm_mode(mode)
+            model = train_conformer(num_blocks=2, idim=257, seed=4).to(cuda)
+            opt = FusedAdam(model.train_engine(), lr=3e-4, weight_decay=1e-2)
+            objective = build_objective("MSE", {})
+            losses = []
+            for step in range(200):
+                loss = objective(model, batches[step % len(batches)], device=cuda)
+                loss.backward()
+                opt.clip_grad_norm_(5.0)
+                opt.step()
+                opt.zero_grad()
+                losses.append(loss.detach())
+            curves[mode] = torch.stack(losses).cpu()
+    finally:
+        nv.set_gemm_mode(1)
+    a, b = curves[1], curves[2]
+    fa, fb = float(a[-8:].mean()), float(b[-8:].mean())
+    print(f"200 steps: loss {float(a[0]):.5f} -> mode 1 {fa:.5f} / mode 2 {fb:.5f}; max gap {float((a - b).abs().max()):.2e}")
+    assert fa < 0.7 * float(a[0]) and fb < 0.7 * float(b[0])
+    assert abs(fa - fb) <= 0.02 * fa
+    assert float((a - b).abs().max()) <= 0.05 * float(a[0])
 
 
 def test_fused_adam_matches_torch(cuda):
