@@ -193,6 +193,20 @@ int css_adam_step(float* p, const float* g, float* m, float* v, long n, float lr
                   float weight_decay, long step, float gscale, const double* sqnorm, float max_norm, float* norm_out,
                   css_stream_t stream);
 
+/* ---- on-the-fly training mixer: css/datasets/separation.py:163-267 ---- */
+/* One output window: utterance 1 (pool offset/length per channel) starts at mixture sample 0, utterance 2 at start2; the
+ * window covers mixture samples [win_start, win_start + W), zero outside the utterances (lhotse pad + mix + window). */
+typedef struct { long off1, len1, off2, len2, start2, win_start; } css_mix_item;
+/* pool: C channel planes, ch_stride samples apart.  mix (B,C,W); s1, s2 (B,W) = channel 0 of the padded utterances */
+int css_mix_windows(const float* pool, long ch_stride, int C, const void* items, int B, int W, float* mix, float* s1,
+                    float* s2, css_stream_t stream);
+/* x (B,C,W) += g * noise[(off + n) mod noise_len] with g from the channel-0 powers and snr_db[b]; snr_db[b] = NaN: skip */
+int css_mix_add_noise(float* x, int B, int C, int W, const float* noise, long noise_ch_stride, long noise_len,
+                      const long* noise_off, const float* snr_db, css_stream_t stream);
+/* y[b] = energy-normalised FIR(x[b], rirs[rir_idx[b]]) for rir_idx[b] >= 0 (other windows are left unwritten) */
+int css_mix_reverb(const float* x, float* y, int B, int C, int W, const float* rirs, int taps, const int* rir_idx,
+                   double* energy, css_stream_t stream);
+
 /* tcgen05/TMEM GEMM from fp32 operands (same contract as css_gemm_f32): operands are split into `planes` bf16 planes
  * in `scratch` (1 = bf16, 2 = bf16x3, 3 = bf16x6 product terms), accumulation in fp32 */
 size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes);
