@@ -102,7 +102,7 @@ def test_reference_surface_separator_stitcher_beamformer(cuda, case_a, golden):
     p0, _ = Beamformer(c["beamforming"]).continuous_process(wav.to(cuda), plain)
     assert torch.equal(p0, o0)
     with pytest.raises(ValueError):
-        Separator(c["separation"], backend="onnx", model=pipe.separator.model)
+        Separator(c["separation"], backend="tensorrt", model=pipe.separator.model)
     with pytest.raises(ValueError):
         Beamformer(dict(c["beamforming"], type="NoSuchBeamformer"))
     with pytest.raises(RuntimeError):
