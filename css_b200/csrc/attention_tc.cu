@@ -370,6 +370,13 @@ int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_pl
     CSS_REQUIRE(attention_tc_supported(T, dk), "attention_tc: T=%d / dk=%d unsupported", T, dk);
     CSS_REQUIRE(in_planes == 1 || in_planes == 2, "attention_tc: %d input planes unsupported", in_planes);
     CSS_REQUIRE(N > 0 && H > 0 && qkv_planes && (out || (planes && n_planes > 0)), "attention_tc: bad arguments");
+    if (attention_umma_supported(T, dk, in_planes, pe_planes != nullptr, pe_rows)) {
+        css_prof_begin(1, 6.0 * (double)N * H * T * T * DK, st);
+        const int rc = attention_umma_launch(qkv_planes, qkv_plane_stride, pe_planes, pe_plane_stride, pe_rows, out, planes, plane_stride,
+                                             planes ? n_planes : 0, N, H, st);
+        css_prof_end(st);
+        return rc;
+    }
     typedef void (*Kern)(const AttnArgs);
     // score tiles per query tile: 19 covers the executor's 150-frame chunks (and anything up to 152), 20 the rest
     const bool split = in_planes == 2, use_pe = pe_planes != nullptr, nt19 = T <= 152;

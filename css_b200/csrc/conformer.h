@@ -19,6 +19,11 @@ int attention_tc_launch(const void* qkv_planes, long qkv_plane_stride, int in_pl
                         int pe_rows, float* out, void* planes, long plane_stride, int n_planes, long N, int T, int H, int dk,
                         cudaStream_t st);
 
+// tcgen05 / TMEM attention (attention_umma.cu): T == 150, dk == 64, two input planes, relative positions
+bool attention_umma_supported(int T, int dk, int in_planes, bool has_pe, int pe_rows);
+int attention_umma_launch(const void* qkv_planes, long qkv_plane_stride, const void* pe_planes, long pe_plane_stride, int pe_rows,
+                          float* out, void* planes, long plane_stride, int n_planes, long N, int H, cudaStream_t st);
+
 struct ConvModuleParams {
     const float* ln_g;      // (d)
     const float* ln_b;      // (d)

@@ -913,6 +913,12 @@ static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld
     return 0;
 }
 
+// shared with the tcgen05 attention kernel (attention_umma.cu)
+int css_make_plane_map(CUtensorMap* map, const void* base, long rows, int K, int ld, long plane_stride, int planes, int box_rows,
+                       int BK) {
+    return make_map(map, base, rows, K, ld, plane_stride, planes, box_rows, BK);
+}
+
 int sm_count() {
     static int n_dev[CSS_MAX_DEVICES] = {};
     const int dev = css_device();
