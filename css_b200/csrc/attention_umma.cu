@@ -252,7 +252,7 @@ __device__ __forceinline__ void softmax_tile(uint32_t tmem, int q, int lane, flo
     // exchange (max, sum) with the three other key groups of this row
     xch[(G * 128 + row) * 2] = mx;
     xch[(G * 128 + row) * 2 + 1] = sum;
-    asm volatile("bar.sync 1, %0;" ::"n"(NSOFT * 32) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + q), "n"(NSPLIT * 32) : "memory");     // the four warps that share these 32 rows
     float gm = mx, tot = 0.f;
 #pragma unroll
     for (int g2 = 0; g2 < NSPLIT; ++g2) gm = fmaxf(gm, xch[(g2 * 128 + row) * 2]);
@@ -436,23 +436,35 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
             const int h = (int)(it - chunk * H);
 #pragma unroll 1
             for (int tile = 0; tile < 2; ++tile, ++tiles) {
+                // tile 1 holds rows 128..149 only: the warps of lane quadrants 1-3 own no valid row there (their P rows feed
+                // output rows that are never stored) and just keep the barrier counts
+                // (they still wait for the phase's barrier before arriving: an early second arrival would be counted in the
+                // phase of tile 0)
+                const bool live = tile == 0 || q == 0;
+                float inv_sum = 0.f;
                 mbar_wait(sr_full, tiles & 1);
-                tc_fence_after();
-                if (threadIdx.x == 64) DBG(9 + 3 * tile);
-                float inv_sum;
-                if (G == 0) softmax_tile<0>(tmem, q, lane, xch, row, inv_sum);
-                else if (G == 1) softmax_tile<1>(tmem, q, lane, xch, row, inv_sum);
-                else if (G == 2) softmax_tile<2>(tmem, q, lane, xch, row, inv_sum);
-                else softmax_tile<3>(tmem, q, lane, xch, row, inv_sum);
-                tc_fence_before();
+                if (live) {
+                    tc_fence_after();
+                    if (threadIdx.x == 128) DBG(9 + 3 * tile);
+                    if (G == 0) softmax_tile<0>(tmem, q, lane, xch, row, inv_sum);
+                    else if (G == 1) softmax_tile<1>(tmem, q, lane, xch, row, inv_sum);
+                    else if (G == 2) softmax_tile<2>(tmem, q, lane, xch, row, inv_sum);
+                    else softmax_tile<3>(tmem, q, lane, xch, row, inv_sum);
+                    tc_fence_before();
+                }
                 __syncwarp();
                 if (lane == 0) mbar_arrive(p_full);
-                if (threadIdx.x == 64) DBG(10 + 3 * tile);
+                if (threadIdx.x == 128) DBG(10 + 3 * tile);
                 if (G >= 2) continue;
+                if (!live) {
+                    mbar_wait(o_full, tiles & 1);
+                    if (lane == 0) mbar_arrive(o_free);
+                    continue;
+                }
                 // ---- epilogue: key groups 0 and 1 take 32 output columns each
                 mbar_wait(o_full, tiles & 1);
                 tc_fence_after();
-                if (threadIdx.x == 64) DBG(11 + 3 * tile);
+                if (threadIdx.x == 128) DBG(11 + 3 * tile);
                 uint32_t o[32];
                 tld32(tmem + lane_base + TM_O + 32 * G, o);
                 tld_wait();
