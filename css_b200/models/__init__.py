@@ -1,10 +1,9 @@
 """Model registry (reference: css/models/__init__.py:19-27)."""
 from .blstm import BLSTM
 from .conformer import Conformer
+from .conv_tasnet import ConvTasNet
 
-# ConvTasNet is out of scope for the hot path: the STFT-mask executor
-# cannot use it and BASELINE.json's north_star does not name it.
-MODELS = {"Conformer": Conformer, "BLSTM": BLSTM}
+MODELS = {"Conformer": Conformer, "ConvTasNet": ConvTasNet, "BLSTM": BLSTM}
 
 
 def build_model(modelname, conf):

@@ -207,6 +207,24 @@ int css_mix_add_noise(float* x, int B, int C, int W, const float* noise, long no
 int css_mix_reverb(const float* x, float* y, int B, int C, int W, const float* rirs, int taps, const int* rir_idx,
                    double* energy, css_stream_t stream);
 
+/* ---- Conv-TasNet: css/models/conv_tasnet.py:17-330.  Activations time-major (n*T, C); every
+ * Conv1d(kernel 1) is css_gemm_f32; these cover the rest ---- */
+/* encoder Conv1d(1, N, L, stride): x (n, len) -> out (n*T, N), T = (len - L) / stride + 1 */
+int css_ctn_encoder(const float* x, long n, long len, const float* w, const float* b, int N, int L, int stride, float* out,
+                    css_stream_t stream);
+/* nn.LayerNorm over the C channels of every row ("cln") */
+int css_row_layernorm(const float* x, const float* g, const float* b, long M, int C, float eps, float* y, css_stream_t stream);
+/* global layer norm of prelu(x) ("gln"): stats (n, 2) f64 = {sum, sum of squares} per sample; apply; and the dilated
+ * depthwise conv that reads gLN(prelu(x)) on the fly (zero padding on the normalised signal, odd kernel, non-causal) */
+int css_ctn_prelu_stats(const float* x, long n, long per_sample, const float* alpha, double* stats, css_stream_t stream);
+int css_ctn_norm_apply(const float* x, long n, long T, int C, const float* alpha, const double* stats, const float* g,
+                       const float* b, float eps, float* y, css_stream_t stream);
+int css_ctn_dwconv(const float* x, long n, long T, int C, int P, int dil, const float* alpha, const double* stats,
+                   const float* g, const float* b, float eps, const float* w, const float* wb, float* y, css_stream_t stream);
+/* masks x encoder output -> ConvTranspose1d(N, 1, L, stride) -> y (S, n, (T-1) stride + L); frames: S n T L floats scratch */
+int css_ctn_decode(const float* enc, const float* masks, int ldm, long n, long T, int N, int L, int stride, int S,
+                   const float* wd, const float* bias, float* frames, float* y, css_stream_t stream);
+
 /* tcgen05/TMEM GEMM from fp32 operands (same contract as css_gemm_f32): operands are split into `planes` bf16 planes
  * in `scratch` (1 = bf16, 2 = bf16x3, 3 = bf16x6 product terms), accumulation in fp32 */
 size_t css_gemm_tc_scratch_bytes(long M, int N, int K, int planes);

@@ -197,6 +197,42 @@ def blstm_masks(f, sd, num_out=3):
     return list(torch.chunk(m, num_out, -1))
 
 
+def conv_tasnet_forward(x, sd, num_spk=2, num_noise=1):
+    """Reference Conv-TasNet forward (css/models/conv_tasnet.py:127-156, blocks :296-320, gLN :168-202), functional over a
+    reference-named state_dict; separation-block norm "gln", non-causal, ReLU masks.  x (n, L) -> (n, num_spk, L')."""
+    F = torch.nn.functional
+    if x.dim() == 1:
+        x = x.unsqueeze(0)
+    L = sd["encoder.weight"].shape[-1]
+    w = F.conv1d(x.unsqueeze(1), sd["encoder.weight"], sd["encoder.bias"], stride=L // 2)
+    e = F.layer_norm(w.transpose(1, 2), (w.shape[1],), sd["LayerN_S.weight"], sd["LayerN_S.bias"], 1e-5).transpose(1, 2)
+    e = F.conv1d(e, sd["BottleN_S.weight"], sd["BottleN_S.bias"])
+
+    def gln(v, p):
+        mean = v.mean((1, 2), keepdim=True)
+        var = ((v - mean) ** 2).mean((1, 2), keepdim=True)
+        return sd[p + ".weight"] * (v - mean) / torch.sqrt(var + 1e-5) + sd[p + ".bias"]
+
+    r = 0
+    while f"separation.{r}.0.conv1x1.weight" in sd:
+        i = 0
+        while f"separation.{r}.{i}.conv1x1.weight" in sd:
+            p = f"separation.{r}.{i}"
+            c = F.conv1d(e, sd[p + ".conv1x1.weight"], sd[p + ".conv1x1.bias"])
+            c = gln(F.prelu(c, sd[p + ".PReLU_1.weight"]), p + ".norm_1")
+            wd = sd[p + ".dwconv.weight"]
+            dil = 2 ** i
+            c = F.conv1d(c, wd, sd[p + ".dwconv.bias"], padding=dil * (wd.shape[-1] - 1) // 2, dilation=dil, groups=wd.shape[0])
+            c = gln(F.prelu(c, sd[p + ".PReLU_2.weight"]), p + ".norm_2")
+            e = e + F.conv1d(c, sd[p + ".Sc_conv.weight"], sd[p + ".Sc_conv.bias"])
+            i += 1
+        r += 1
+    m = torch.relu(F.conv1d(e, sd["gen_masks.weight"], sd["gen_masks.bias"]))
+    outs = [F.conv_transpose1d(w * mk, sd["decoder.weight"], sd["decoder.bias"], stride=L // 2).squeeze(1)
+            for mk in torch.chunk(m, num_spk + num_noise, dim=1)]
+    return torch.stack(outs[:-1], dim=1)
+
+
 def _lstm_dir(x, w_ih, w_hh, b_ih, b_hh, reverse):
     """One LSTM direction, gate order i,f,g,o (torch.nn.LSTM semantics, css/models/blstm.py:139-145)."""
     n, t, _ = x.shape

@@ -160,3 +160,22 @@ class DropHook:
         else:
             m = dropout_mask(x.numel(), self.p, self.seed, site).view(x.shape)
         return x * m.to(x.dtype) * scale
+
+
+CONF_CTN = dict(num_spk=2, num_noise=1, conv_tasnet_num_filters=64, conv_tasnet_filter_length=16, conv_tasnet_bottleneck_channels=32,
+                conv_tasnet_conv_channels=64, conv_tasnet_kernel_size=3, conv_tasnet_num_blocks=3, conv_tasnet_num_layers=2,
+                conv_tasnet_norm="gln")
+
+
+def randomise_conv_tasnet(model, seed=6):
+    """Non-trivial PReLU slopes / norm affines (their defaults 0.25 / 1 / 0 would hide indexing mistakes)."""
+    g = torch.Generator().manual_seed(seed)
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if "PReLU" in name or "norm_" in name or name.startswith("LayerN_S"):
+                p.add_(0.2 * torch.randn(p.shape, generator=g))
+    return model
+
+
+def conv_tasnet_input(seed=7, n=2, length=4000):
+    return torch.randn(n, length, generator=torch.Generator().manual_seed(seed)) * 0.3
