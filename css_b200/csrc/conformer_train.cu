@@ -15,7 +15,7 @@ namespace {
 
 constexpr int kP = 2;   // planes kept for every operand (the GEMM mode decides how many are used)
 
-struct LinPlanes { PlaneMat w, wT; };   // W (N,K) planes [N][Kp] and W^T planes [K][Np]
+struct LinPlanes { PlaneMat w; };   // W (N,K) planes [N][Kp]; the gradient GEMMs read them MN-major, no W^T copy
 struct BlockLin { LinPlanes ff_in_w1, ff_in_w2, wqkv, wo, ff_out_w1, ff_out_w2; };
 
 struct Trainer {
@@ -48,7 +48,7 @@ struct Ws {
     double* bn_stats;
     float* bstats;
     float *g, *gm, *dwide, *dn, *datt, *att_scratch, *tmp;
-    PlaneMat gP, gT, dwP, dwT, actT;
+    PlaneMat gP, dwP;
     size_t bytes;
 };
 
@@ -90,10 +90,7 @@ void carve(const Trainer* t, long N, int T, char* base, Ws* w) {
     w->tmp = f32((size_t)M * d);
     w->att_scratch = f32(attention_train_scratch_floats(N, T, c.heads));
     w->gP = planes(M, d);
-    w->gT = planes(d, (int)Mp);
     w->dwP = planes(M, wide);
-    w->dwT = planes(wide, (int)Mp);
-    w->actT = planes(std::max(f, t->ldin), (int)Mp);
     w->bytes = off;
 }
 
@@ -117,7 +114,8 @@ int build_planes(Trainer* t, cudaStream_t st) {
     int rc = 0;
     auto mk = [&](LinPlanes& lp, long off, int N, int K, bool need_T) {
         if (rc) return;
-        rc = split_t_launch(t->params + off, N, K, K, &lp.w, need_T ? &lp.wT : nullptr, need_T ? lp.wT.ld : 0, nullptr, 0.f, st);
+        (void)need_T;
+        rc = split_t_launch(t->params + off, N, K, K, &lp.w, nullptr, 0, nullptr, 0.f, st);
     };
     mk(t->embed, c.embed_w, d, c.idim, false);
     mk(t->head, c.head_w, nh, d, true);
@@ -135,6 +133,24 @@ int build_planes(Trainer* t, cudaStream_t st) {
 }
 
 int mode_planes() { return css_get_gemm_mode() == 2 ? 1 : 2; }
+
+// The gradient GEMMs read their operands as they are stored (tcgen05 MN-major smem descriptors, GemmEpilogue::a_mn / b_mn):
+//   dX = dY . W      : W (N_out, K_in) planes are the (K, N) matrix of that product          -> no W^T planes
+//   dW += dY^T . X   : dY (M, N_out) and X (M, K_in) planes are its (K, M) and (K, N) matrices -> no transposed activations
+// (the first version transposed every dY, X and W: 17.6 % of the step's kernel time)
+GemmEpilogue ep_dx(float alpha, long k_valid) {
+    GemmEpilogue e = {nullptr, 0, alpha, nullptr, 0, 0.f};
+    e.b_mn = 1;
+    e.k_valid = k_valid;
+    return e;
+}
+GemmEpilogue ep_dw(float alpha, long rows) {
+    GemmEpilogue e = {nullptr, 0, alpha, nullptr, 0, 0.f};
+    e.a_mn = e.b_mn = 1;
+    e.accumulate = 1;
+    e.k_valid = rows;
+    return e;
+}
 
 // blk / site: block index and the site id of the hidden-activation dropout (the output dropout is site + 1)
 int ffn_fwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const LinPlanes& w2, const float* xin, float* xout,
@@ -164,7 +180,7 @@ int ffn_bwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const Lin
     float* gr = t->grads;
     const float* p = t->params;
     int rc;
-    PlaneMat gT = view(w.gT, d, (int)Mp), dhP = view(w.dwP, M, f), dhT = view(w.dwT, f, (int)Mp);
+    PlaneMat dhP = view(w.dwP, M, f);
     const bool dr = t->drop_p > 0.f;
     const float hs = dr ? 1.f / (1.f - t->drop_p) : 1.f;          // hidden dropout: dh *= 1/(1-p) where kept (dropped h == 0 is masked)
     const float* gb = w.g;                                        // gradient w.r.t. the branch output W2 h + b2 (before the 0.5)
@@ -172,28 +188,19 @@ int ffn_bwd(Trainer* t, const css_ffn_offsets& o, const LinPlanes& w1, const Lin
         if ((rc = dropout_f32_launch(w.gm, w.g, nullptr, M * d, t->drop(blk, site + 1), 1.f, 0, st))) return rc;
         gb = w.gm;
     }
-    if ((rc = split_t_launch(gb, M, d, d, &w.gP, &gT, Mp, gr + o.b2, 0.5f, st))) return rc;
+    if ((rc = split_t_launch(gb, M, d, d, &w.gP, nullptr, 0, gr + o.b2, 0.5f, st))) return rc;
     // dW2 += 0.5 g^T h
-    PlaneMat hT = view(w.actT, f, (int)Mp);
-    if ((rc = transpose_planes_launch(hP, M, f, hT, Mp, st))) return rc;
-    GemmEpilogue ea = {nullptr, 0, 0.5f, nullptr, 0, 0.f};
-    ea.accumulate = 1;
-    if ((rc = tc(gT, hT, P, d, f, (int)Mp, ea, gr + o.w2, f, nullptr, st))) return rc;
+    if ((rc = tc(w.gP, hP, P, d, f, (int)Mp, ep_dw(0.5f, M), gr + o.w2, f, nullptr, st))) return rc;
     // dh = 0.5 g W2, masked by the ReLU
-    GemmEpilogue eh = {nullptr, 0, 0.5f * hs, nullptr, 0, 0.f};
+    GemmEpilogue eh = ep_dx(0.5f * hs, d);
     eh.relu_mask = hP.ptr;
     eh.ldmask = hP.ld;
-    if ((rc = tc(w.gP, w2.wT, P, M, f, d, eh, w.dwide, f, nullptr, st))) return rc;
-    if ((rc = split_t_launch(w.dwide, M, f, f, &dhP, &dhT, Mp, gr + o.b1, 1.f, st))) return rc;
+    if ((rc = tc(w.gP, w2.w, P, M, f, d, eh, w.dwide, f, nullptr, st))) return rc;
+    if ((rc = split_t_launch(w.dwide, M, f, f, &dhP, nullptr, 0, gr + o.b1, 1.f, st))) return rc;
     // dW1 += dh^T n
-    PlaneMat nT = view(w.actT, d, (int)Mp);
-    if ((rc = transpose_planes_launch(nP, M, d, nT, Mp, st))) return rc;
-    GemmEpilogue eb = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-    eb.accumulate = 1;
-    if ((rc = tc(dhT, nT, P, f, d, (int)Mp, eb, gr + o.w1, d, nullptr, st))) return rc;
+    if ((rc = tc(dhP, nP, P, f, d, (int)Mp, ep_dw(1.f, M), gr + o.w1, d, nullptr, st))) return rc;
     // dn = dh W1 ; g += LN'(x_in) dn
-    GemmEpilogue en = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-    if ((rc = tc(dhP, w1.wT, P, M, d, f, en, w.dn, d, nullptr, st))) return rc;
+    if ((rc = tc(dhP, w1.w, P, M, d, f, ep_dx(1.f, f), w.dn, d, nullptr, st))) return rc;
     LnBwdArgs a = {xin, p + o.ln_g, nullptr, w.dn, nullptr, w.g, 1, gr + o.ln_g, gr + o.ln_b, nullptr, nullptr, nullptr, nullptr};
     return ln_bwd_launch(a, M, d, 1e-5f, false, st);
 }
@@ -236,7 +243,7 @@ extern "C" void* css_trainer_create(const css_conformer_train_desc* desc, const 
     // plane memory: W planes [N][pad64(K)] and W^T planes [K][pad64(N)] of every Linear
     size_t total = 0;
     auto bytes = [](long rows, long ld) { return align256((size_t)kP * rows * ld * 2); };
-    auto size_lin = [&](int N, int K, bool T) { total += bytes(N, pad64(K)) + (T ? bytes(K, pad64(N)) : 0); };
+    auto size_lin = [&](int N, int K, bool) { total += bytes(N, pad64(K)); };
     size_lin(d, desc->idim, false);
     size_lin(nh, d, true);
     for (int l = 0; l < desc->num_blocks; ++l) {
@@ -254,7 +261,7 @@ extern "C" void* css_trainer_create(const css_conformer_train_desc* desc, const 
         const long kp = pad64(K), np = pad64(N);
         lp.w = {wp, N * kp, (int)kp, kP};
         wp += bytes(N, kp);
-        if (T) { lp.wT = {wp, K * np, (int)np, kP}; wp += bytes(K, np); }
+        (void)T; (void)np;
         return lp;
     };
     t->embed = mk(d, desc->idim, false);
@@ -373,15 +380,10 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             CSS_REQUIRE(gy, "css_trainer_backward: null gradient");
             float* dhead = w.dwide;   // (M, ldh)
             if ((rc = head_bwd_launch(w.head, t->ldh, feat, c.idim, gy, dhead, N, T, c.num_bins, c.num_spk, st))) return rc;
-            PlaneMat dhP = view(w.dwP, M, t->nhp), dhT = view(w.dwT, nh, (int)Mp);
-            if ((rc = split_t_launch(dhead, M, nh, t->ldh, &dhP, &dhT, Mp, gr + c.head_b, 1.f, st))) return rc;
-            PlaneMat yT = view(w.actT, d, (int)Mp);
-            if ((rc = transpose_planes_launch(w.yP, M, d, yT, Mp, st))) return rc;
-            GemmEpilogue ea = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-            ea.accumulate = 1;
-            if ((rc = tc(dhT, yT, P, nh, d, (int)Mp, ea, gr + c.head_w, d, nullptr, st))) return rc;
-            GemmEpilogue eg = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-            if ((rc = tc(dhP, t->head.wT, P, M, d, t->nhp, eg, w.g, d, nullptr, st))) return rc;
+            PlaneMat dhP = view(w.dwP, M, t->nhp);
+            if ((rc = split_t_launch(dhead, M, nh, t->ldh, &dhP, nullptr, 0, gr + c.head_b, 1.f, st))) return rc;
+            if ((rc = tc(dhP, w.yP, P, nh, d, (int)Mp, ep_dw(1.f, M), gr + c.head_w, d, nullptr, st))) return rc;
+            if ((rc = tc(dhP, t->head.w, P, M, d, t->nhp, ep_dx(1.f, nh), w.g, d, nullptr, st))) return rc;
         } else if (part >= 0) {
             const int l = part;
             const css_conformer_block_offsets& o = t->blk[l];
@@ -399,30 +401,22 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             }
             if ((rc = conv_train_bwd_launch(s.x2, s.cpre, s.bnsave, w.g, gconv, w.dn, w.bstats, N, T, conv_params(t, l), conv_grads(t, l), st))) return rc;
             // ---- self-attention ----
-            PlaneMat gT = view(w.gT, d, (int)Mp);
             const float* gatt = w.g;
             if (dr) {
                 if ((rc = dropout_f32_launch(w.gm, w.g, nullptr, M * d, t->drop(l, 3), 1.f, 0, st))) return rc;
                 gatt = w.gm;
             }
-            if ((rc = split_t_launch(gatt, M, d, d, &w.gP, &gT, Mp, gr + o.bo, 1.f, st))) return rc;
-            PlaneMat aT = view(w.actT, d, (int)Mp);
-            if ((rc = transpose_planes_launch(s.att, M, d, aT, Mp, st))) return rc;
-            GemmEpilogue ea = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-            ea.accumulate = 1;
-            if ((rc = tc(gT, aT, P, d, d, (int)Mp, ea, gr + o.wo, d, nullptr, st))) return rc;
-            GemmEpilogue ed = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-            if ((rc = tc(w.gP, b.wo.wT, P, M, d, d, ed, w.datt, d, nullptr, st))) return rc;
+            if ((rc = split_t_launch(gatt, M, d, d, &w.gP, nullptr, 0, gr + o.bo, 1.f, st))) return rc;
+            if ((rc = tc(w.gP, s.att, P, d, d, (int)Mp, ep_dw(1.f, M), gr + o.wo, d, nullptr, st))) return rc;
+            if ((rc = tc(w.gP, b.wo.w, P, M, d, d, ep_dx(1.f, d), w.datt, d, nullptr, st))) return rc;
             float* dqkv = w.dwide;   // (M, 3d)
             const CssDrop dp = t->drop(l, 2);
             if ((rc = attention_train_bwd_launch(s.qkv, pe, c.pe_rows, s.probs, w.datt, dqkv, pe ? gr + c.pe : nullptr, w.att_scratch,
                                                  N, T, c.heads, d / c.heads, P == 2, dr ? &dp : nullptr, st))) return rc;
-            PlaneMat dqP = view(w.dwP, M, 3 * d), dqT = view(w.dwT, 3 * d, (int)Mp);
-            if ((rc = split_t_launch(dqkv, M, 3 * d, 3 * d, &dqP, &dqT, Mp, gr + o.bqkv, 1.f, st))) return rc;
-            PlaneMat nT = view(w.actT, d, (int)Mp);
-            if ((rc = transpose_planes_launch(s.n2, M, d, nT, Mp, st))) return rc;
-            if ((rc = tc(dqT, nT, P, 3 * d, d, (int)Mp, ea, gr + o.wqkv, d, nullptr, st))) return rc;
-            if ((rc = tc(dqP, b.wqkv.wT, P, M, d, 3 * d, ed, w.dn, d, nullptr, st))) return rc;
+            PlaneMat dqP = view(w.dwP, M, 3 * d);
+            if ((rc = split_t_launch(dqkv, M, 3 * d, 3 * d, &dqP, nullptr, 0, gr + o.bqkv, 1.f, st))) return rc;
+            if ((rc = tc(dqP, s.n2, P, 3 * d, d, (int)Mp, ep_dw(1.f, M), gr + o.wqkv, d, nullptr, st))) return rc;
+            if ((rc = tc(dqP, b.wqkv.w, P, M, d, 3 * d, ep_dx(1.f, 3 * d), w.dn, d, nullptr, st))) return rc;
             LnBwdArgs a1 = {s.x1, p + o.att_ln_g, nullptr, w.dn, nullptr, w.g, 1, gr + o.att_ln_g, gr + o.att_ln_b, nullptr, nullptr, nullptr, nullptr};
             if ((rc = ln_bwd_launch(a1, M, d, 1e-5f, false, st))) return rc;
             if ((rc = ffn_bwd(t, o.ff_in, b.ff_in_w1, b.ff_in_w2, s.x0, s.n1, s.h1, w, P, l, 0, st))) return rc;
@@ -434,13 +428,8 @@ extern "C" int css_trainer_backward_part(void* trainer, const float* feat, const
             }
             LnBwdArgs a = {w.ye, p + c.embed_ln_g, nullptr, w.g, w.xe, w.g, 0, gr + c.embed_ln_g, gr + c.embed_ln_b, nullptr, nullptr, nullptr, nullptr};
             if ((rc = ln_bwd_launch(a, M, d, 1e-5f, false, st))) return rc;
-            PlaneMat gT = view(w.gT, d, (int)Mp);
-            if ((rc = split_t_launch(w.g, M, d, d, nullptr, &gT, Mp, gr + c.embed_b, 1.f, st))) return rc;
-            PlaneMat fT = view(w.actT, t->ldin, (int)Mp);
-            if ((rc = transpose_planes_launch(w.fP, M, t->ldin, fT, Mp, st))) return rc;
-            GemmEpilogue ea = {nullptr, 0, 1.f, nullptr, 0, 0.f};
-            ea.accumulate = 1;
-            if ((rc = tc(gT, fT, P, d, c.idim, (int)Mp, ea, gr + c.embed_w, c.idim, nullptr, st))) return rc;
+            if ((rc = split_t_launch(w.g, M, d, d, &w.gP, nullptr, 0, gr + c.embed_b, 1.f, st))) return rc;
+            if ((rc = tc(w.gP, w.fP, P, d, c.idim, (int)Mp, ep_dw(1.f, M), gr + c.embed_w, c.idim, nullptr, st))) return rc;
         }
     }
     return 0;

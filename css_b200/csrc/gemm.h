@@ -17,6 +17,13 @@ struct GemmEpilogue {
     // LayerNorm(C row; ln_g, ln_b, eps 1e-5) -- see gemm_tc_ln_fusable()
     const float* ln_g = nullptr;
     const float* ln_b = nullptr;
+    // MN-major operands (tcgen05 path, training kernels): the operand is stored with its NON-contracted index contiguous,
+    //   a_mn: A given as planes of A^T, i.e. a (K, M) row-major matrix (pitch A.ld >= M)  -- dW = dY^T X reads dY as it is
+    //   b_mn: W given as planes of W^T, i.e. a (K, N) row-major matrix (pitch W.ld >= N)  -- dX = dY W reads W as it is
+    // so neither gradient GEMM needs a transposed copy of an activation or of a weight.
+    int a_mn = 0;
+    int b_mn = 0;
+    long k_valid = 0;   // rows of the MN-major operands that exist in memory (0: K); rows in [k_valid, K) read as zero (TMA fill)
 };
 
 int gemm_simt_launch(const float* A, int lda, const float* W, int ldw, float* C, int ldc, long M, int N, int K,

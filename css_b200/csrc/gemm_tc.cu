@@ -109,6 +109,18 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr) {
     return d;
 }
 
+// MN-major operand tile: 64-element (128 B) groups along M/N, each group = BK rows (k) of 128 B in the 128-byte swizzle;
+// 8-row k groups are 1024 B apart (stride byte offset), the 64-wide groups BK * 128 B apart (leading byte offset).
+template <int BK>
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t saddr) {
+    uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)((BK * 128) >> 4) << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
 struct TcEpilogue {
     const float* bias;
     int act;
@@ -343,7 +355,8 @@ __device__ __forceinline__ void epilogue_tile(const TcEpilogue& ep, uint32_t tme
 // EM selects the epilogue: 0 generic; 1 bias (+ReLU) -> NPL = P bf16 planes only (FFN-in, QKV); 2 (acc + bias) * alpha
 // + residual -> fp32 only (FFN-out, attention out-projection).  The lean forms need N % 32 == 0 and are chosen on the host;
 // the K = 256 GEMMs are bound by epilogue instruction issue, so every instruction removed there is tile time.
-template <int P, int BN, int BK, bool TRAIN, int EM>
+// MN: 0 both operands K-major; 1 W MN-major (dX = dY W); 3 A and W MN-major (dW = dY^T X).  MN != 0 only with TRAIN.
+template <int P, int BN, int BK, bool TRAIN, int EM, int MN = 0>
 __global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, long M, int N, int K,
                TcEpilogue ep) {
@@ -399,8 +412,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     uint8_t* sb = sa + P * C::A_BYTES;
 #pragma unroll
                     for (int p = 0; p < P; ++p) {
-                        tma_load_3d(sa + p * C::A_BYTES, &tmA, &full[stage], kb * BK, mb * BM, p);
-                        tma_load_3d(sb + p * C::B_BYTES, &tmB, &full[stage], kb * BK, nb * BN, p);
+                        if constexpr ((MN & 2) != 0) {      // A^T planes (K, M): 64-column groups of BK rows
+#pragma unroll
+                            for (int g = 0; g < BM / 64; ++g)
+                                tma_load_3d(sa + p * C::A_BYTES + g * BK * 128, &tmA, &full[stage], mb * BM + g * 64, kb * BK, p);
+                        } else {
+                            tma_load_3d(sa + p * C::A_BYTES, &tmA, &full[stage], kb * BK, mb * BM, p);
+                        }
+                        if constexpr ((MN & 1) != 0) {      // W^T planes (K, N)
+#pragma unroll
+                            for (int g = 0; g < BN / 64; ++g)
+                                tma_load_3d(sb + p * C::B_BYTES + g * BK * 128, &tmB, &full[stage], nb * BN + g * 64, kb * BK, p);
+                        } else {
+                            tma_load_3d(sb + p * C::B_BYTES, &tmB, &full[stage], kb * BK, nb * BN, p);
+                        }
                     }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -409,8 +434,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else if (warp == 1) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            // instruction descriptor: D=f32, A=B=bf16, both K-major, N, M=128
-            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+            // instruction descriptor: D=f32, A=B=bf16, K-major unless MN says otherwise (bits 15 / 16), N, M=128
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)((MN >> 1) & 1) << 15) | ((uint32_t)(MN & 1) << 16) |
+                                   ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
             int stage = 0; uint32_t phase = 0;
             int acc = 0; uint32_t acc_phase = 0;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
@@ -429,8 +455,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                         for (int tm = 0; tm < Terms<P>::N; ++tm) {
                             const int pa = term_a(tm), pb = term_b(tm);
-                            const uint64_t da = make_desc<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
-                            const uint64_t db = make_desc<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
+                            const uint64_t da = (MN & 2) ? make_desc_mn<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 128)
+                                                         : make_desc<BK>(sa + pa * C::A_BYTES + ks * UMMA_K * 2);
+                            const uint64_t db = (MN & 1) ? make_desc_mn<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 128)
+                                                         : make_desc<BK>(sb + pb * C::B_BYTES + ks * UMMA_K * 2);
                             tc_mma(d_tmem, da, db, idesc, ((kb - kb0) | ks | tm) != 0);
                         }
                     }
@@ -996,13 +1024,20 @@ static int launch_cfg2(const PlaneMat& A, const PlaneMat& W, long M, int N, int 
 }
 
 template <int P, int BN, int BK>
-static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st) {
+static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K, const TcEpilogue& ep, cudaStream_t st, int mn = 0,
+                      long k_valid = 0) {
     using C = Cfg<P, BN, BK>;
     CUtensorMap ta, tb;
     int rc;
-    if ((rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK))) return rc;
-    if ((rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK))) return rc;
-    const bool train = ep.mask != nullptr || ep.ksplit > 1;
+    // K-major operand: (rows, K) matrix, box BK x tile rows.  MN-major operand: (K, rows) matrix, box 64 columns x BK rows.
+    const long kv = k_valid > 0 ? k_valid : K;
+    if (mn & 2) rc = make_map(&ta, A.ptr, kv, (int)M, A.ld, A.plane_stride, P, BK, 64);
+    else rc = make_map(&ta, A.ptr, M, K, A.ld, A.plane_stride, P, BM, BK);
+    if (rc) return rc;
+    if (mn & 1) rc = make_map(&tb, W.ptr, kv, N, W.ld, W.plane_stride, P, BK, 64);
+    else rc = make_map(&tb, W.ptr, N, K, W.ld, W.plane_stride, P, BN, BK);
+    if (rc) return rc;
+    const bool train = ep.mask != nullptr || ep.ksplit > 1 || mn != 0;
     const int em = epilogue_mode(ep, P, N, train);
     static CssPerDevice attr;
     if (attr.first()) {
@@ -1010,10 +1045,23 @@ static int launch_cfg(const PlaneMat& A, const PlaneMat& W, long M, int N, int K
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
         if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        if constexpr (P <= 2 && BN == 256) {
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true, 0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(gemm_tc_kernel<P, BN, BK, true, 0, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
+        }
         CSS_REQUIRE(e == cudaSuccess, "gemm_tc: cannot reserve %d B of shared memory: %s", C::SMEM, cudaGetErrorString(e));
     }
     const long tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN) * (ep.ksplit > 1 ? ep.ksplit : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+    if (mn) {
+        if constexpr (P <= 2 && BN == 256) {
+            if (mn == 1) gemm_tc_kernel<P, BN, BK, true, 0, 1><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+            else gemm_tc_kernel<P, BN, BK, true, 0, 3><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
+            return css_check_launch("gemm_tc (MN-major operands)");
+        } else {
+            CSS_REQUIRE(false, "gemm_tc: MN-major operands are built for 1 or 2 planes and 256-column tiles");
+        }
+    }
     if (train) gemm_tc_kernel<P, BN, BK, true, 0><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     else if (em == 1) gemm_tc_kernel<P, BN, BK, false, 1><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
     else if (em == 2) gemm_tc_kernel<P, BN, BK, false, 2><<<grid, 384, C::SMEM, st>>>(ta, tb, M, N, K, ep);
@@ -1035,7 +1083,10 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
                    const PlaneMat* out, cudaStream_t st) {
     CSS_REQUIRE(P >= 1 && P <= 3, "gemm_tc: %d planes unsupported", P);
     CSS_REQUIRE(A.planes >= P && W.planes >= P, "gemm_tc: operands carry %d/%d planes, need %d", A.planes, W.planes, P);
-    CSS_REQUIRE(M > 0 && N > 0 && A.ld >= K && W.ld >= K, "gemm_tc: bad shape M=%ld N=%d K=%d", M, N, K);
+    const int mn = (e.a_mn ? 2 : 0) | (e.b_mn ? 1 : 0);
+    CSS_REQUIRE(mn != 2, "gemm_tc: an MN-major A needs an MN-major W as well (the dW form)");
+    CSS_REQUIRE(M > 0 && N > 0 && A.ld >= (e.a_mn ? M : K) && W.ld >= (e.b_mn ? N : K), "gemm_tc: bad shape M=%ld N=%d K=%d", M, N, K);
+    CSS_REQUIRE(!mn || (P <= 2 && N > 128 && !out && !e.ln_g), "gemm_tc: MN-major operands: 1-2 planes, N > 128, fp32 output");
     CSS_REQUIRE(C || out, "gemm_tc: no output");
     CSS_REQUIRE(K % KPAD == 0 && K > 0, "gemm_tc: K=%d must be a positive multiple of %d", K, KPAD);
     TcEpilogue ep = {e.bias, e.act, e.alpha, e.residual, e.ldr, e.clamp_max, C, ldc,
@@ -1060,6 +1111,10 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     ep.ln_g = e.ln_g;
     ep.ln_b = e.ln_b;
     CSS_REQUIRE(!e.ln_g || (!train && gemm_tc_ln_fusable(M, N, P)), "gemm_tc: fused LayerNorm unsupported for M=%ld N=%d P=%d", M, N, P);
+    if (mn) {
+        if (P == 1) return v == 1 ? launch_cfg<1, 256, 32>(A, W, M, N, K, ep, st, mn, e.k_valid) : launch_cfg<1, 256, 64>(A, W, M, N, K, ep, st, mn, e.k_valid);
+        return v == 1 ? launch_cfg<2, 256, 32>(A, W, M, N, K, ep, st, mn, e.k_valid) : launch_cfg<2, 256, 64>(A, W, M, N, K, ep, st, mn, e.k_valid);
+    }
     if (!train && P <= 2 && N % 256 == 0 && M > 2 * BM && sm_count() >= 2 && two_cta_enabled()) {
         if (P == 1) return v == 1 ? launch_cfg2<1, 32>(A, W, M, N, K, ep, st) : launch_cfg2<1, 64>(A, W, M, N, K, ep, st);
         return v == 1 ? launch_cfg2<2, 32>(A, W, M, N, K, ep, st) : launch_cfg2<2, 64>(A, W, M, N, K, ep, st);
@@ -1131,4 +1186,35 @@ extern "C" int css_gemm_tc(const float* A, int lda, const float* W, int ldw, con
     rc = gemm_tc_planes(a, w, planes, M, N, kp, e, C, ldc, nullptr, st);
     css_prof_end(st);
     return rc;
+}
+
+// Test entry for the MN-major operand forms (training GEMMs): mode 1: C = A . W^T with W handed over as Wt = W^T (K, N);
+// mode 3: additionally A handed over as At = A^T (K, M), result ACCUMULATED into C (split-K + atomics, the dW form).
+// scratch >= 2 * K * (pitch of M + pitch of N) * 2 bytes + 512.
+extern "C" int css_gemm_tc_mn(const float* A, int lda, const float* Wt, int ldw, float* C, int ldc, long M, int N, int K, int mode,
+                              int planes, void* scratch, size_t scratch_bytes, cudaStream_t st) {
+    CSS_REQUIRE((mode == 1 || mode == 3) && planes >= 1 && planes <= 2 && K % KPAD == 0, "css_gemm_tc_mn: bad mode / planes / K");
+    const int mp = (int)((M + 63) / 64 * 64), np = (N + 63) / 64 * 64;
+    char* base = reinterpret_cast<char*>(((uintptr_t)scratch + 255) & ~(uintptr_t)255);
+    PlaneMat a, w;
+    size_t need;
+    int rc;
+    if (mode == 3) {
+        a = {base, (long)K * mp, mp, planes};
+        need = (size_t)planes * K * mp * 2;
+        if ((rc = split_planes_launch(A, K, (int)M, lda, a, st))) return rc;
+    } else {
+        a = {base, M * (long)K, K, planes};
+        need = (size_t)planes * M * K * 2;
+        if ((rc = split_planes_launch(A, M, K, lda, a, st))) return rc;
+    }
+    need = (need + 255) & ~(size_t)255;
+    w = {base + need, (long)K * np, np, planes};
+    CSS_REQUIRE(scratch_bytes >= need + (size_t)planes * K * np * 2 + 512, "css_gemm_tc_mn: scratch too small");
+    if ((rc = split_planes_launch(Wt, K, N, ldw, w, st))) return rc;
+    GemmEpilogue e = {nullptr, 0, 1.f, nullptr, 0, 0.f};
+    e.b_mn = 1;
+    e.a_mn = mode == 3;
+    e.accumulate = mode == 3;
+    return gemm_tc_planes(a, w, planes, M, N, K, e, C, ldc, nullptr, st);
 }

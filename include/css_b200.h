@@ -232,6 +232,12 @@ int css_gemm_tc(const float* A, int lda, const float* W, int ldw, const float* b
                 int K, int act, float alpha, const float* residual, int ldr, float clamp_max, int planes, void* scratch,
                 size_t scratch_bytes, css_stream_t stream);
 
+/* MN-major operand forms of the tcgen05 GEMM (the gradient GEMMs of the training step read dY, X and W as they are stored,
+ * no transposed copies): mode 1: C = A . W^T with W given as Wt = W^T (K, N); mode 3: A given as At = A^T (K, M) as well and
+ * the result ACCUMULATED into C (split-K, fp32 atomics).  Test / tooling entry; K % 64 == 0, N > 128. */
+int css_gemm_tc_mn(const float* A, int lda, const float* Wt, int ldw, float* C, int ldc, long M, int N, int K, int mode,
+                   int planes, void* scratch, size_t scratch_bytes, css_stream_t stream);
+
 /* GEMM engine of the mask networks: 0 = fp32 SIMT, 1 = tcgen05 bf16x3 split (fp32-class accuracy), 2 = tcgen05 bf16 */
 int css_set_gemm_mode(int mode);
 int css_get_gemm_mode(void);
