@@ -460,14 +460,14 @@ def run_b200(args):
                       "ms_per_step": round(ms_c[i] / args.steps, 4), "algorithmic_MB_per_step": round(work_c[i] / args.steps / 1e6, 1)}
            for i in (2, 3, 5, 6, 7, 8, 9, 10) if cnt_c[i] and ms_c[i] > 0}
     traffic = None
-    tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+    tpath = os.path.join(ROOT, "profiles", "r2_traffic.json")
     if os.path.exists(tpath):
         with open(tpath) as f:
             traffic = json.load(f).get("gemm_tc", {}).get("bytes_per_launch")
     roof = {"kernel": {0: "gemm_simt_f32", 1: "gemm_tc_bf16x3 (tcgen05)", 2: "gemm_tc_bf16 (tcgen05)"}[gemm_mode],
             "bound": "tensor", "achieved": achieved, "peak": pk["tensor"], "unit": "TFLOP/s",
             "frac": achieved / pk["tensor"], "peak_source": f"{pk['src']} bf16 sustained (kernel timed inside a long step)",
-            "traffic": traffic, "traffic_note": "ncu dram bytes per launch, mean over the six GEMMs of one block (profiles/r1_traffic.json)",
+            "traffic": traffic, "traffic_note": "ncu dram bytes per launch, mean over the six GEMMs of one block (profiles/r2_traffic.json)",
             "launches": int(g_n), "avg_launch_ms": g_ms / max(1, g_n),
             "algorithmic_flop_per_step": g_flop / args.steps, "share_of_step": shares}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
