@@ -43,7 +43,10 @@ constexpr int OFF_BAR = OFF_V + 2 * PLANE_T;
 constexpr int OFF_XCH = OFF_BAR + 256;
 constexpr int SMEM_BYTES = OFF_XCH + NSPLIT * 128 * 8 + 1024;
 // TMEM columns
-constexpr int TM_S = 0, TM_PLO = 80, TM_R = 160, TM_O = 448;
+// O = P_hi [V_hi | V_lo] (one N = 128 MMA per k-step, the two V planes side by side along N) + P_lo V_hi (N = 64 into the first
+// half): 128 columns that overlay the tail of R, which is dead once the softmax has read it.  (An N = 64 MMA costs the same
+// ~70 cycles as an N = 128 one, so two MMAs per k-step instead of three N = 64 ones.)
+constexpr int TM_S = 0, TM_PLO = 80, TM_R = 160, TM_O = 336;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -105,10 +108,11 @@ __device__ __forceinline__ uint64_t desc_k(uint32_t saddr) {
     return d;
 }
 // MN-major operand (V: [key][dk], dk contiguous, 64 bf16 = one 128-byte swizzle atom row): key groups of 8 are 1024 B apart
-// (stride byte offset); one 64-wide group along N, so the leading byte offset is unused
-__device__ __forceinline__ uint64_t desc_mn(uint32_t saddr) {
+// (stride byte offset); 64-wide groups along N are `lbo_bytes` apart (leading byte offset: the distance between the hi and the lo
+// plane when both are read as one N = 128 operand)
+__device__ __forceinline__ uint64_t desc_mn(uint32_t saddr, uint32_t lbo_bytes = 1024) {
     uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
-    d |= (uint64_t)(1024 >> 4) << 16;
+    d |= (uint64_t)(lbo_bytes >> 4) << 16;
     d |= (uint64_t)(1024 >> 4) << 32;
     d |= (uint64_t)1 << 46;
     d |= (uint64_t)2 << 61;
@@ -366,6 +370,8 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
                                 mma_ss(tmem + TM_S, desc_k(qa + pa * PLANE_T + ks * 32), desc_k(sb + OFF_K + pb * PLANE_T + ks * 32),
                                        idesc_of(160, false), (ks | tm) != 0);
                             }
+                        // R overlays the O columns of the previous tile: its epilogue must have drained them
+                        if (tiles) { mbar_wait(o_free, (tiles - 1) & 1); tc_fence_after(); }
                         // ---- R = Q PE^T, relative columns [0, 288) as two N = 144 halves
 #pragma unroll
                         for (int half = 0; half < 2; ++half)
@@ -389,13 +395,11 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
                     DBG(3 + 4 * tile);
                     tc_fence_after();
 #pragma unroll
-                    for (int ks = 0; ks < KROWS / 16; ++ks)
-#pragma unroll
-                        for (int tm = 0; tm < 3; ++tm) {
-                            const int pa = tm == 2, pb = tm == 1;
-                            mma_ts(tmem + TM_O, tmem + (pa ? TM_PLO : TM_S) + ks * 8, desc_mn(sb + OFF_V + pb * PLANE_T + ks * 16 * 128),
-                                   idesc_of(64, true), (ks | tm) != 0);
-                        }
+                    for (int ks = 0; ks < KROWS / 16; ++ks) {
+                        // P_hi . [V_hi | V_lo]: the two V planes are PLANE_T bytes apart = the operand's leading byte offset
+                        mma_ts(tmem + TM_O, tmem + TM_S + ks * 8, desc_mn(sb + OFF_V + ks * 16 * 128, PLANE_T), idesc_of(128, true), ks != 0);
+                        mma_ts(tmem + TM_O, tmem + TM_PLO + ks * 8, desc_mn(sb + OFF_V + ks * 16 * 128), idesc_of(64, true), 1);
+                    }
                     tc_commit(o_full);
                     if (tile == 0) {
                         // tile 1 (rows 128..149): R needs relative columns [128, 299) -> N = 176 from PE row 128; S behind P V
@@ -465,8 +469,9 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
                 mbar_wait(o_full, tiles & 1);
                 tc_fence_after();
                 if (threadIdx.x == 128) DBG(11 + 3 * tile);
-                uint32_t o[32];
+                uint32_t o[32], o2[32];
                 tld32(tmem + lane_base + TM_O + 32 * G, o);
+                tld32(tmem + lane_base + TM_O + 64 + 32 * G, o2);
                 tld_wait();
                 tc_fence_before();
                 __syncwarp();
@@ -476,7 +481,7 @@ attention_umma_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_co
                     const long eoff = (chunk * T_ + t) * (long)(H * DK) + h * DK + 32 * G;
                     float f[32];
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(o[i]) * inv_sum;
+                    for (int i = 0; i < 32; ++i) f[i] = (__uint_as_float(o[i]) + __uint_as_float(o2[i])) * inv_sum;
                     if (a.out) {
 #pragma unroll
                         for (int i = 0; i < 8; ++i)
