@@ -204,7 +204,7 @@ class ConformerTrainEngine:
         self.bn_tracked += 1
         return y_pred, head
 
-    def enable_data_parallel(self, optim=None, group=None, buckets=4):
+    def enable_data_parallel(self, optim=None, group=None, buckets=8):
         """Data-parallel training over ``torch.distributed``: rank 0's parameters and BatchNorm running
         statistics are broadcast, the flat gradient is sum-all-reduced in ``buckets`` layer groups while the backward is
         still running (``GradientExchange``), and the mean is folded into the optimiser (``grad_scale = 1/world``)."""
