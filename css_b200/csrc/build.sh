@@ -4,6 +4,8 @@ set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC"
+# CSS_B200_CLEAN=1: drop every object and the library first, so the build proves it compiles from source
+if [ -n "$CSS_B200_CLEAN" ]; then rm -rf build libcss_b200.so; fi
 mkdir -p build
 pids=()
 for f in *.cu; do

@@ -88,3 +88,33 @@ def test_long_recording_shard_plan():
                     prefix ^= p
                 s0 = first_state(prefix, sl, c0, e0)
                 assert [s0 ^ v for v in sl] == state[e0:e1]
+
+
+def test_long_recording_sample_ownership():
+    """Host logic of the sharded output: the ranks' sample ranges partition [0, T), every placement of a rank's
+    own chunks lands inside its range plus the spill, and only the `en == T` items (A.6 Q4) reach into the neighbour's range."""
+    import types
+
+    from css_b200.dist import ShardedCssPipeline, chunk_ranges
+    from css_b200.executor.beamformer import Beamformer, placement_plan
+    from css_b200.pipeline import CONFIG_7CH
+
+    sh = ShardedCssPipeline.__new__(ShardedCssPipeline)
+    sh.pipe = types.SimpleNamespace(beamformer=Beamformer(CONFIG_7CH["beamforming"]))
+    assert sh.spill == 6144
+    for T, B in ((960000, 72), (1120000, 85), (9600000, 747)):
+        plan = placement_plan(B, T, 12800, 32000, 38144, 32)
+        for world in (1, 2, 3, 8, 13):
+            ranges = chunk_ranges(B, world)
+            spans = [sh.owned_samples(c0, c1, B, T) for c0, c1 in ranges]
+            live = [s for s in spans if s[1] > s[0]]
+            assert live[0][0] == 0 and live[-1][1] == T and all(a[1] == b[0] for a, b in zip(live, live[1:]))
+            crossings = 0
+            for (c0, c1), (s0, s1) in zip(ranges, spans):
+                for c, a, b, dst in plan:
+                    if c0 <= c < c1:
+                        end = min(T, dst + (b - a))
+                        assert dst >= s0 and end <= min(T, s1 + sh.spill)
+                        crossings += end > s1
+            if T % 12800:
+                assert crossings == 0          # no `en == T` branch without T a multiple of the hop
