@@ -129,3 +129,61 @@ extern "C" int css_peak_normalize(float* x, int rows, long n, float target, unsi
     if (rc) return rc;
     return css_peak_scale(x, rows, n, n, target, scratch, st);
 }
+
+// ---------------------------------------------------------------------------------------------
+// css_peak_normalize without caller scratch and without any allocation (for callers that cannot allocate: CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  The per-row peak bits live in a file-scope device array
+// that every GPU loading the library holds until exit: CSS_PEAK_NOALLOC_MAX_ROWS x 4 B = 256 B.  No counterpart in the
+// reference.
+//
+// In host code `g_peak_bits` is only a stand-in for the symbol, not a device address: the address is looked up once per
+// device (with that device current) by cudaGetSymbolAddress and that pointer is what the kernels get.
+// All calls share the array and it keeps the last call's bits, so it is cleared at the start of every call (stream-ordered);
+// calls that overlap on the GPU (different streams without an ordering between them) race on it.
+// ---------------------------------------------------------------------------------------------
+#define CSS_PEAK_NOALLOC_MAX_ROWS 64
+static __device__ __align__(256) unsigned g_peak_bits[CSS_PEAK_NOALLOC_MAX_ROWS];
+
+static int peak_bits_address(unsigned** out) {
+    static unsigned* addr[CSS_MAX_DEVICES] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        css_set_error("css_peak_normalize_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+        return -2;
+    }
+    CSS_REQUIRE(dev >= 0 && dev < CSS_MAX_DEVICES, "css_peak_normalize_noalloc: device ordinal %d beyond %d", dev, CSS_MAX_DEVICES);
+    if (!addr[dev]) {
+        unsigned* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_peak_bits);
+        if (e != cudaSuccess || !p) {
+            css_set_error("css_peak_normalize_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            return -2;
+        }
+        addr[dev] = p;
+    }
+    *out = addr[dev];
+    return 0;
+}
+
+extern "C" int css_peak_normalize_noalloc_max_rows(void) { return CSS_PEAK_NOALLOC_MAX_ROWS; }
+
+extern "C" int css_peak_normalize_noalloc(float* x, int rows, long n, float target, cudaStream_t st) {
+    CSS_REQUIRE(rows > 0 && n > 0, "css_peak_normalize_noalloc: empty input");
+    CSS_REQUIRE(rows <= CSS_PEAK_NOALLOC_MAX_ROWS, "css_peak_normalize_noalloc: %d rows exceed the built-in scratch of %d rows",
+                rows, CSS_PEAK_NOALLOC_MAX_ROWS);
+    unsigned* bits = nullptr;
+    int rc = peak_bits_address(&bits);
+    if (rc) return rc;
+    cudaError_t e = cudaMemsetAsync(bits, 0, sizeof(unsigned) * rows, st);
+    if (e != cudaSuccess) {
+        css_set_error("css_peak_normalize_noalloc: cudaMemsetAsync: %s", cudaGetErrorString(e));
+        return -2;
+    }
+    // launched directly (not through css_absmax / css_peak_scale): their optional profiling scope creates events
+    absmax_kernel<<<peak_grid(rows, n), 256, 0, st>>>(x, n, n, bits);
+    rc = css_check_launch("css_peak_normalize_noalloc(absmax)");
+    if (rc) return rc;
+    peak_scale_kernel<<<peak_grid(rows, n), 256, 0, st>>>(x, n, n, bits, target);
+    return css_check_launch("css_peak_normalize_noalloc(scale)");
+}

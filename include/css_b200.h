@@ -134,6 +134,13 @@ int css_normalize_scale(const void* result, const void* ref, const float* mask, 
 int css_istft_place(const void* Y, int T, const int* plan, int n_items, float* out, long out_len, css_stream_t stream);
 /* beamformer.py:122-123; scratch: `rows` uint32 */
 int css_peak_normalize(float* x, int rows, long n, float target, unsigned* scratch, css_stream_t stream);
+/* No counterpart in the reference.  css_peak_normalize for callers that
+ * cannot allocate (CUDA graph capture, serving loops): the per-row peak bits live in a 256-byte file-scope device array
+ * inside the library, so there is no scratch argument and the call performs no allocation of any kind.
+ * rows <= css_peak_normalize_noalloc_max_rows() (64), otherwise -1 with a message.  Every call shares that array
+ * (cleared at the start of each call, stream-ordered): calls that overlap on one GPU race. */
+int css_peak_normalize_noalloc(float* x, int rows, long n, float target, css_stream_t stream);
+int css_peak_normalize_noalloc_max_rows(void);
 
 /* The two halves of css_peak_normalize for a recording spread over several GPUs: bits[r] = max(bits[r], bits of
  * max|x[r][:n]|) (caller zeroes bits; combine across ranks with all-reduce MAX), then x[r][:n] = x * target / peak.
