@@ -149,8 +149,17 @@ static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& 
     return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, nullptr, st);
 }
 
-static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_mvn, float clamp_max, float* masks, float* head,
-                      int ld_head, char* wp, int mode, cudaStream_t st) {
+// Input of the fused front end (css_conformer_forward_spec): the chunk spectra instead of a feature matrix.
+struct SpecInput {
+    const void* spec;
+    long stride_d, stride_chunk;
+    const int *ipd_l, *ipd_r;
+    int n_pairs;
+    float* mag;
+};
+
+static int forward_tc(ConformerModel* m, float* feat, const SpecInput* si, long N, int T, int apply_mvn, float clamp_max, float* masks,
+                      float* head, int ld_head, char* wp, int mode, cudaStream_t st) {
     const css_conformer_desc& c = m->d;
     const long M = N * T;
     const int d = c.d_model, dffn = c.d_ffn, nh = c.num_bins * c.num_out, P = (mode == 1) ? 2 : 1;
@@ -166,7 +175,10 @@ static int forward_tc(ConformerModel* m, float* feat, long N, int T, int apply_m
     PlaneMat fP = {wp, M * (long)c.ldin, c.ldin, P};
     int rc;
     if ((rc = build_weight_planes(m, st))) return rc;
-    if (apply_mvn) rc = mvn_time_planes_launch(feat, N, T, c.idim, c.ldin, fP.ptr, fP.plane_stride, c.ldin, P, st);
+    if (si)
+        rc = features_planes_launch(si->spec, si->stride_d, si->stride_chunk, N, T, si->ipd_l, si->ipd_r, si->n_pairs, si->mag, fP.ptr,
+                                    fP.plane_stride, c.ldin, P, nullptr, 0, st);
+    else if (apply_mvn) rc = mvn_time_planes_launch(feat, N, T, c.idim, c.ldin, fP.ptr, fP.plane_stride, c.ldin, P, st);
     else rc = split_planes_launch(feat, M, c.idim, c.ldin, fP, st);
     if (rc) return rc;
     GemmEpilogue ee = {c.embed_b, 0, 1.f, nullptr, 0, 0.f};
@@ -229,7 +241,7 @@ extern "C" int css_conformer_forward(void* model, float* feat, long N, int T, in
     const int d = c.d_model, dffn = c.d_ffn, nh = c.num_bins * c.num_out;
     const size_t wide = (size_t)(dffn > 3 * d ? dffn : 3 * d);
     char* wp = static_cast<char*>(workspace);
-    if (g_gemm_mode != 0) return forward_tc(m, feat, N, T, apply_mvn, clamp_max, masks, head, ld_head, wp, g_gemm_mode, st);
+    if (g_gemm_mode != 0) return forward_tc(m, feat, nullptr, N, T, apply_mvn, clamp_max, masks, head, ld_head, wp, g_gemm_mode, st);
     float* x = (float*)wp;  wp += align256((size_t)M * d * 4);
     float* y = (float*)wp;  wp += align256((size_t)M * d * 4);
     float* a = (float*)wp;  wp += align256((size_t)M * d * 4);
@@ -269,3 +281,25 @@ extern "C" int css_conformer_forward(void* model, float* feat, long N, int T, in
     if ((rc = gemm_dispatch(x, d, c.head_w, d, hd, ldh, M, nh, d, eh, st))) return rc;
     return masks_layout_launch(hd, ldh, masks, N, T, c.num_bins, c.num_out, st);
 }
+
+// The executor's path in one call: chunk spectra -> features -> input MVN -> network -> masks.  spec element
+// (channel d, chunk b, frame t, bin k) lives at spec[(d*stride_d + b*stride_chunk + t) * 264 + k] (complex64), as css_features
+// takes it; mag (N, 257, T) is the second output of css_features.  Tensor-core GEMM modes only (the fp32 SIMT mode keeps
+// the two-call form css_features + css_conformer_forward).
+extern "C" int css_conformer_forward_spec(void* model, const void* spec, long stride_d, long stride_chunk, const int* ipd_l,
+                                          const int* ipd_r, int n_pairs, long N, int T, float clamp_max, float* mag, float* masks,
+                                          float* head, int ld_head, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    ConformerModel* m = static_cast<ConformerModel*>(model);
+    CSS_REQUIRE(m && spec && mag && workspace, "css_conformer_forward_spec: null argument");
+    CSS_REQUIRE(N > 0 && T > 1, "css_conformer_forward_spec: empty input (N=%ld, T=%d)", N, T);
+    CSS_REQUIRE((masks != nullptr) != (head != nullptr), "css_conformer_forward_spec: pass exactly one of masks/head");
+    CSS_REQUIRE(g_gemm_mode != 0, "css_conformer_forward_spec: needs a tensor-core GEMM mode (css_set_gemm_mode 1 or 2)");
+    CSS_REQUIRE(m->d.idim == CSS_NBINS * (n_pairs + 1), "css_conformer_forward_spec: model expects %d input features, %d IPD pairs give %d",
+                m->d.idim, n_pairs, CSS_NBINS * (n_pairs + 1));
+    CSS_REQUIRE(features_planes_supported(T, n_pairs), "css_conformer_forward_spec: T=%d with %d IPD pairs unsupported", T, n_pairs);
+    CSS_REQUIRE(workspace_bytes >= css_conformer_workspace_bytes(model, N, T), "css_conformer_forward_spec: workspace too small");
+    const SpecInput si = {spec, stride_d, stride_chunk, ipd_l, ipd_r, n_pairs, mag};
+    return forward_tc(m, nullptr, &si, N, T, 1, clamp_max, masks, head, ld_head, static_cast<char*>(workspace), g_gemm_mode, st);
+}
+
+extern "C" int css_features_planes_supported(int T, int n_pairs) { return features_planes_supported(T, n_pairs) ? 1 : 0; }

@@ -264,3 +264,290 @@ extern "C" int css_mvn_time(float* x, long n, int T, int F, int ld, cudaStream_t
     mvn_time_kernel<<<grid, 128, 0, st>>>(x, T, F, ld);
     return css_check_launch("css_mvn_time");
 }
+
+// ---------------------------------------------------------------------------------------------
+// Fused front end of the mask network for the executor path (round 2): spectrum -> features (feature.py:105-134,156-175) ->
+// the model's input MVN over time (conformer.py:95 / blstm.py:80) -> bf16 split planes for the embed GEMM, plus the magnitude
+// (B, 257, T).  Replaces css_features + mvn_time_planes on that path: the fp32 feature matrix (832 MB per 10-min session, written
+// once and read once) no longer exists, and every spectrum value is read ONCE per chunk (the two-kernel form read each
+// 2x in features_kernel with no L2 reuse between the passes: 3.8 GB per session against 1.6 GB algorithmic).
+//
+// One CTA per (chunk, FP_BG = 8 bins): thread = (bin, frame slot), 32 frame slots, frames slot, slot + 32, ...  The unit
+// cross-phasors of the chunk (n_pairs x T x 8 float2, 57.6 KB at T = 150) stay in shared memory, so each is formed once instead
+// of twice; they are then overwritten in place by the IPD values, which are normalised over time from shared memory.
+// Four block-wide reductions (shuffle over the 4 frame slots of a warp that share a bin, then the 8 warps through shared
+// memory, fixed order -> deterministic): {sum mag, sum cos, sum sin}, {mag variance, sum IPD}, {sum mag feature, IPD
+// variance}, {mag feature variance}.  257 = 32 x 8 + 1: the last bin group is shifted to bins 249..256 and recomputes seven
+// bins to identical bits.
+// ---------------------------------------------------------------------------------------------
+// unit_cross with its rare cases (purely real bins, vanishing / huge products) out of line: the fused kernel inlines the common
+// path 6x per frame, and with the slow paths inlined as well its code no longer fits the instruction cache
+__device__ __noinline__ float2 unit_cross_rare(float2 a, float2 b) { return unit_cross(a, b); }
+__device__ __forceinline__ float2 unit_cross_fast(float2 a, float2 b) {
+    const float2 p = cmulc(a, b);
+    const float n2 = p.x * p.x + p.y * p.y;
+    if ((a.y == 0.f && b.y == 0.f) || !(n2 >= 1e-30f && n2 <= 1e30f)) return unit_cross_rare(a, b);
+    float r = rsqrtf(n2);
+    r = r * (1.5f - 0.5f * n2 * r * r);
+    return make_float2(p.x * r, p.y * r);
+}
+
+#define FP_BG 8
+#define FP_THREADS 256
+#define FP_SLOTS (FP_THREADS / FP_BG)       // 32 frame slots
+#define FP_WARPS (FP_THREADS / 32)
+#define FP_NV 16                             // reduction slots: 1 + 2 * 6 used by round 1 (up to 1 + 2 * 7 fit)
+
+// Sum over the threads of the CTA that share this thread's bin, v[0..N) in place (every thread gets the result), finished
+// by ONE thread per (value, bin) into what the callers need -- bit i of inv_mask set: 1 / (sqrt(sum / (T-1)) + eps), the
+// reciprocal of the unbiased standard deviation + eps; clear: sum / T, the mean -- so the divisions are not repeated by the 32
+// threads of a bin.
+template <int N>
+__device__ __forceinline__ void fp_reduce(float (&v)[N], float* red, float* stat, int bin, int warp, int lane, int T, unsigned inv_mask) {
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        v[i] += __shfl_xor_sync(0xffffffffu, v[i], 8);
+        v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+    }
+    if (lane < FP_BG) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) red[(i * FP_WARPS + warp) * FP_BG + bin] = v[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < N * FP_BG) {
+        const int i = threadIdx.x / FP_BG, b = threadIdx.x % FP_BG;
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < FP_WARPS; ++w) s += red[(i * FP_WARPS + w) * FP_BG + b];
+        stat[i * FP_BG + b] = ((inv_mask >> i) & 1u) ? 1.f / (sqrtf(s / (T - 1)) + FEAT_EPS) : s / T;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < N; ++i) v[i] = stat[i * FP_BG + bin];
+}
+
+template <int NP, int PL>
+__global__ void __launch_bounds__(FP_THREADS, 3)
+features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T, const int* __restrict__ ipd_l,
+                       const int* __restrict__ ipd_r, float* __restrict__ mag, __nv_bfloat16* __restrict__ planes,
+                       long plane_stride, int ldp, float* __restrict__ feat, int ldf, int n_groups) {
+    extern __shared__ float fp_smem[];
+    float2* U = reinterpret_cast<float2*>(fp_smem);                  // [NP][T][FP_BG] phasors, later .x = IPD value
+    float* MG = fp_smem + (size_t)2 * NP * T * FP_BG;                // [T][FP_BG] magnitude, later the mag feature
+    float* red = MG + (size_t)T * FP_BG;                             // [FP_NV][FP_WARPS][FP_BG]
+    float* stat = red + FP_NV * FP_WARPS * FP_BG;                    // [FP_NV][FP_BG]
+    long* offs = reinterpret_cast<long*>(stat + FP_NV * FP_BG);      // [2][8] channel offsets of the pairs (elements), [16] = shared right channel
+    // bin groups fastest: the CTAs that share a chunk's 128-byte lines (spectrum rows, plane rows) run together
+    const long b = blockIdx.x / n_groups;
+    const int grp = blockIdx.x - (int)b * n_groups;
+    const int k0 = min(grp * FP_BG, CSS_NBINS - FP_BG);
+    const int bin = threadIdx.x & (FP_BG - 1), slot = threadIdx.x / FP_BG;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k = k0 + bin;
+    const float2* base = spec + (b * stride_chunk) * CSS_KP + k;
+    constexpr int NPA = NP > 0 ? NP : 1;
+
+    if (threadIdx.x < NP) {
+        offs[threadIdx.x] = (long)ipd_l[threadIdx.x] * stride_d * CSS_KP;
+        offs[8 + threadIdx.x] = (long)ipd_r[threadIdx.x] * stride_d * CSS_KP;
+    }
+    if (threadIdx.x == 32) {
+        bool sr = true;
+        for (int p = 1; p < NP; ++p) sr &= ipd_r[p] == ipd_r[0];
+        offs[16] = sr;
+    }
+    __syncthreads();
+    long offl[NPA], offr[NPA];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+        offl[p] = offs[p];
+        offr[p] = offs[8 + p];
+    }
+    const bool same_r = offs[16] != 0;
+    struct Frame { float2 x0, xl[NPA], xr[NPA]; };
+    auto fetch = [&](Frame& f, int t) {
+        const float2* q = base + (long)t * CSS_KP;
+        f.x0 = q[0];
+#pragma unroll
+        for (int p = 0; p < NP; ++p) f.xl[p] = q[offl[p]];
+        if (NP > 0) {
+            if (same_r) f.xr[0] = q[offr[0]];
+            else {
+#pragma unroll
+                for (int p = 0; p < NP; ++p) f.xr[p] = q[offr[p]];
+            }
+        }
+    };
+
+    // ---- round 1: magnitudes and unit cross-phasors into shared memory, their sums over time ----
+    float acc[1 + 2 * NP];
+#pragma unroll
+    for (int i = 0; i < 1 + 2 * NP; ++i) acc[i] = 0.f;
+    {
+        Frame cur, nxt;
+        if (slot < T) fetch(cur, slot);
+        for (int t = slot; t < T; t += FP_SLOTS) {
+            if (t + FP_SLOTS < T) fetch(nxt, t + FP_SLOTS);
+            const float m = sqrtf(cur.x0.x * cur.x0.x + cur.x0.y * cur.x0.y);
+            MG[t * FP_BG + bin] = m;
+            acc[0] += fmaxf(m, FEAT_EPS);
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const float2 u = unit_cross_fast(cur.xl[p], same_r ? cur.xr[0] : cur.xr[p]);
+                U[(p * T + t) * FP_BG + bin] = u;
+                acc[1 + 2 * p] += u.x;
+                acc[2 + 2 * p] += u.y;
+            }
+            cur = nxt;
+        }
+    }
+    fp_reduce(acc, red, stat, bin, warp, lane, T, 0u);                 // acc = means over time
+    const float m_mean = acc[0];
+    // mag[b][bin][t]: consecutive threads walk t inside a bin row
+    {
+        float* mrow = mag + (b * CSS_NBINS + k0) * (long)T;
+        for (int i = threadIdx.x; i < FP_BG * T; i += FP_THREADS) {
+            const int bb = i / T, t = i - bb * T;
+            mrow[i] = MG[t * FP_BG + bb];
+        }
+    }
+
+    // ---- round 2: magnitude variance; IPD = atan2(sin - mean sin, cos - mean cos) in place of the phasors, their sums ----
+    float* frow = feat ? feat + (b * T) * (long)ldf + k : nullptr;
+    float a2[1 + NP];
+#pragma unroll
+    for (int i = 0; i < 1 + NP; ++i) a2[i] = 0.f;
+    for (int t = slot; t < T; t += FP_SLOTS) {
+        const float dm = fmaxf(MG[t * FP_BG + bin], FEAT_EPS) - m_mean;
+        a2[0] = fmaf(dm, dm, a2[0]);
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+            float2* up = U + (p * T + t) * FP_BG + bin;
+            const float2 u = *up;
+            const float v = ipd_atan2(u.y - acc[2 + 2 * p], u.x - acc[1 + 2 * p]);
+            up->x = v;
+            if (frow) frow[(long)t * ldf + (p + 1) * CSS_NBINS] = v;
+            a2[1 + p] += v;
+        }
+    }
+    fp_reduce(a2, red, stat, bin, warp, lane, T, 1u);
+    const float m_inv = a2[0];
+
+    // ---- round 3: the magnitude feature (in place of the magnitude) and its sum; IPD variances ----
+    float mean[1 + NP], a3[1 + NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) mean[1 + p] = a2[1 + p];
+#pragma unroll
+    for (int i = 0; i < 1 + NP; ++i) a3[i] = 0.f;
+    for (int t = slot; t < T; t += FP_SLOTS) {
+        const float v0 = (fmaxf(MG[t * FP_BG + bin], FEAT_EPS) - m_mean) * m_inv;
+        MG[t * FP_BG + bin] = v0;
+        if (frow) frow[(long)t * ldf] = v0;
+        a3[0] += v0;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) {
+            const float d = U[(p * T + t) * FP_BG + bin].x - mean[1 + p];
+            a3[1 + p] = fmaf(d, d, a3[1 + p]);
+        }
+    }
+    fp_reduce(a3, red, stat, bin, warp, lane, T, ~1u);
+    mean[0] = a3[0];
+
+    // ---- round 4: variance of the magnitude feature ----
+    float a4[1] = {0.f};
+    for (int t = slot; t < T; t += FP_SLOTS) {
+        const float d = MG[t * FP_BG + bin] - mean[0];
+        a4[0] = fmaf(d, d, a4[0]);
+    }
+    fp_reduce(a4, red, stat, bin, warp, lane, T, 1u);
+    float inv[1 + NP];
+    inv[0] = a4[0];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) inv[1 + p] = a3[1 + p];
+
+    // ---- emit the planes of (v - mean_T) / (std_T + eps) ----
+    __nv_bfloat16* prow = planes + (b * T) * (long)ldp + k;
+    for (int t = slot; t < T; t += FP_SLOTS) {
+        __nv_bfloat16* o = prow + (long)t * ldp;
+#pragma unroll
+        for (int p = 0; p < 1 + NP; ++p) {
+            const float v = p == 0 ? MG[t * FP_BG + bin] : U[((p > 0 ? p - 1 : 0) * T + t) * FP_BG + bin].x;
+            float r = (v - mean[p]) * inv[p];
+#pragma unroll
+            for (int q = 0; q < PL; ++q) {
+                const __nv_bfloat16 h = __float2bfloat16_rn(r);
+                r -= __bfloat162float(h);
+                o[q * plane_stride + p * CSS_NBINS] = h;
+            }
+        }
+    }
+    // zero the K padding of the rows (planes, and the fp32 features when they are written)
+    if (grp == 0) {
+        const int F = CSS_NBINS * (NP + 1), padp = ldp - F;
+        for (int i = threadIdx.x; i < T * padp; i += FP_THREADS) {
+            const int t = i / padp, c = i - t * padp;
+            for (int q = 0; q < PL; ++q) planes[q * plane_stride + (b * T + t) * (long)ldp + F + c] = __float2bfloat16_rn(0.f);
+        }
+        if (feat) {
+            const int padf = ldf - F;
+            for (int i = threadIdx.x; i < T * padf; i += FP_THREADS) {
+                const int t = i / padf, c = i - t * padf;
+                feat[(b * T + t) * (long)ldf + F + c] = 0.f;
+            }
+        }
+    }
+}
+
+static size_t fp_smem_bytes(int np, int T) {
+    return sizeof(float) * ((size_t)2 * np * T * FP_BG + (size_t)T * FP_BG + FP_NV * FP_WARPS * FP_BG + FP_NV * FP_BG) + 17 * sizeof(long);
+}
+bool features_planes_supported(int T, int n_pairs) {
+    return T > 1 && n_pairs >= 0 && n_pairs <= 7 && fp_smem_bytes(n_pairs, T) <= 200 * 1024;
+}
+
+template <int NP, int PL>
+static int features_planes_go(const float2* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
+                              const int* ipd_r, float* mag, void* planes, long plane_stride, int ldp, float* feat, int ldf,
+                              cudaStream_t st) {
+    const size_t smem = fp_smem_bytes(NP, T);
+    static CssPerDevice attr_set;
+    if (attr_set.first()) cudaFuncSetAttribute(features_planes_kernel<NP, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    const int n_groups = (CSS_NBINS + FP_BG - 1) / FP_BG;
+    CSS_REQUIRE(n_chunks * n_groups < (1L << 31), "css_features_planes: too many chunks (%ld)", n_chunks);
+    features_planes_kernel<NP, PL><<<(unsigned)(n_chunks * n_groups), FP_THREADS, smem, st>>>(
+        spec, stride_d, stride_chunk, T, ipd_l, ipd_r, mag, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, feat, ldf, n_groups);
+    return css_check_launch("css_features_planes");
+}
+
+// mag (B, 257, T); planes: n_planes x (B*T, ldp) bf16, ldp >= 257 (n_pairs + 1), padding zeroed; feat (B*T, ldf) fp32 or NULL.
+int features_planes_launch(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
+                           const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
+                           float* feat, int ldf, cudaStream_t st) {
+    CSS_REQUIRE(n_chunks > 0 && T > 1, "css_features_planes: empty input (chunks=%ld T=%d)", n_chunks, T);
+    CSS_REQUIRE(features_planes_supported(T, n_pairs), "css_features_planes: T=%d with %d IPD pairs does not fit shared memory", T, n_pairs);
+    CSS_REQUIRE(ldp >= CSS_NBINS * (n_pairs + 1) && (!feat || ldf >= CSS_NBINS * (n_pairs + 1)), "css_features_planes: pitch too small");
+    CSS_REQUIRE(n_planes >= 1 && n_planes <= 3, "css_features_planes: 1..3 planes");
+    // algorithmic bytes: spectrum read once per chunk, magnitude + planes written
+    CssProfScope prof(6, (double)n_chunks * T * (CSS_NBINS * ((n_pairs ? 7 : 1) * 8.0 + 4.0) + (double)ldp * 2.0 * n_planes), st);
+    const float2* s = static_cast<const float2*>(spec);
+#define FP_ARGS s, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, mag, planes, plane_stride, ldp, feat, ldf, st
+#define FP_CASE(NP)                                                          \
+    case NP:                                                                 \
+        if (n_planes == 1) return features_planes_go<NP, 1>(FP_ARGS);        \
+        if (n_planes == 2) return features_planes_go<NP, 2>(FP_ARGS);        \
+        return features_planes_go<NP, 3>(FP_ARGS)
+    switch (n_pairs) {
+        FP_CASE(0); FP_CASE(1); FP_CASE(2); FP_CASE(3); FP_CASE(4); FP_CASE(5); FP_CASE(6); FP_CASE(7);
+    }
+#undef FP_CASE
+#undef FP_ARGS
+    return -1;
+}
+
+// Stand-alone C-ABI form (tests, other callers): same outputs as css_features followed by the model-side MVN + plane split.
+extern "C" int css_features_planes(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
+                                   const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp,
+                                   int n_planes, float* feat, int ldf, cudaStream_t st) {
+    return features_planes_launch(spec, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, n_pairs, mag, planes, plane_stride, ldp,
+                                  n_planes, feat, ldf, st);
+}

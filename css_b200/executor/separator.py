@@ -12,6 +12,7 @@ imported into the native model (css_b200/utils/onnx_import.py), no onnxruntime i
 backend asserts ``batch_size == 1`` (separator.py:21-24).
 """
 import math
+import os
 
 import torch
 
@@ -66,6 +67,9 @@ class Separator:
         self.chunk_frames = (self.chunk_len - self.frame_length) // self.frame_shift + 1
         self.hop_frames = self.eval_hop // self.frame_shift
         self.max_chunks = max_chunks_per_launch
+        # spectrum -> features -> MVN -> planes fused in front of the network (css_conformer_forward_spec); off = the two-call
+        # form css_features + css_conformer_forward (A/B switch, and what models without the fused entry point use)
+        self.fused_front_end = os.environ.get("CSS_B200_FUSED_FRONT", "1") != "0"
         # a pinned host recording is copied in pieces: a small first one, whose chunks keep the GPU busy while the rest
         # arrives (the mask network of 1/8 of the chunks takes about as long as the copy of the other 7/8)
         self.stream_first_fraction = float(stream_first_fraction)
@@ -109,8 +113,13 @@ class Separator:
             if before_batch is not None:
                 before_batch(i, b0, nb)
             sub = spec.reshape(-1)[b0 * stride_chunk * nv.KP * 2:]
-            mag, feat = features(sub, stride_d, stride_chunk, nb, T, il, ir, ldin)
-            m = self.model.masks_layout(feat, nb, T, clamp_max=1.0)
+            fused = self.model.masks_from_spec(sub, stride_d, stride_chunk, nb, T, il, ir, clamp_max=1.0) \
+                if self.fused_front_end and hasattr(self.model, "masks_from_spec") else None
+            if fused is not None:
+                m, mag = fused
+            else:
+                mag, feat = features(sub, stride_d, stride_chunk, nb, T, il, ir, ldin)
+                m = self.model.masks_layout(feat, nb, T, clamp_max=1.0)
             if self.merge:
                 like = torch.empty(nb, 2, 30, dtype=torch.float32, device=spec.device)
                 idx = torch.empty(nb, 3, dtype=torch.int32, device=spec.device)

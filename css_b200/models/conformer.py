@@ -233,6 +233,22 @@ class Conformer(nn.Module):
                 nv.c_int(1 if apply_mvn else 0), nv.c_float(clamp_max), nv.ptr(masks), nv.ptr(head), nv.c_int(ld_head),
                 nv.ptr(ws), nv.c_size_t(ws.numel()))
 
+    def masks_from_spec(self, spec, stride_d, stride_chunk, N, T, ipd_l, ipd_r, clamp_max=1.0):
+        """Executor fast path with the fused front end: chunk spectra -> (masks (N, num_bins, T, 3), mag (N, num_bins, T)),
+        or None when the shape / GEMM mode is not covered (the caller then uses features() + masks_layout())."""
+        n_pairs = int(ipd_l.numel())
+        if nv.get_gemm_mode() == 0 or self.in_features != self.num_bins * (n_pairs + 1) or self.num_bins != 257 \
+                or not nv.lib().css_features_planes_supported(nv.c_int(T), nv.c_int(n_pairs)):
+            return None
+        eng = self.engine()
+        ws = self._workspace(eng, N, T)
+        out = torch.empty(N, self.num_bins, T, self.num_spk + self.num_noise, dtype=torch.float32, device=spec.device)
+        mag = torch.empty(N, self.num_bins, T, dtype=torch.float32, device=spec.device)
+        nv.call("css_conformer_forward_spec", ctypes.c_void_p(eng["handle"]), nv.ptr(spec), nv.c_long(stride_d),
+                nv.c_long(stride_chunk), nv.ptr(ipd_l), nv.ptr(ipd_r), nv.c_int(n_pairs), nv.c_long(N), nv.c_int(T),
+                nv.c_float(clamp_max), nv.ptr(mag), nv.ptr(out), nv.ptr(None), nv.c_int(0), nv.ptr(ws), nv.c_size_t(ws.numel()))
+        return out, mag
+
     def masks_layout(self, feat, N, T, clamp_max=1.0):
         """Executor fast path: padded features -> masks (N, num_bins, T, 3) (separator.py:100-104)."""
         out = torch.empty(N, self.num_bins, T, self.num_spk + self.num_noise, dtype=torch.float32, device=feat.device)

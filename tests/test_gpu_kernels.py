@@ -103,6 +103,58 @@ def test_feature_extractor_single_channel(cuda):
     assert rel_inf(mag, mag_o) < 1e-5 and rel_inf(f, f_o) < 1e-4
 
 
+@pytest.mark.parametrize("ipd,chunks,T", [("1,0;2,0;3,0;4,0;5,0;6,0", 3, 150), ("", 2, 150), ("1,0;2,1;0,3", 2, 37)])
+def test_fused_front_end_matches_oracle_features_and_mvn(cuda, ipd, chunks, T):
+    """css_features_planes (spectrum -> features -> input MVN -> bf16 split planes, one kernel) against the oracle's
+    feature_extract (css/executor/feature.py:156-175) followed by the model's MVN over time (conformer.py:95): the fp32
+    feature output within the tolerances of the two-kernel path above, the planes' sum within 2e-4 of the normalised
+    features (bf16 hi + lo carries 16 mantissa bits: 1.5e-5 relative; the MVN of an angle feature inherits the IPD's
+    ill-conditioning, so cut-adjacent elements are excluded as above)."""
+    from css_b200.executor.feature import parse_ipd, stft
+
+    nv = _nv()
+    D = 7 if ipd else 1
+    g = torch.Generator().manual_seed(5)
+    n = 256 * (T - 1) + 512
+    x = torch.randn(chunks, D, n, generator=g) * 0.05
+    x[:, 1:] = 0.6 * x[:, 1:] + 0.4 * x[:, :1]                         # correlated channels: IPDs away from uniform noise
+    spec = stft(x.reshape(chunks * D, n).to(cuda))                      # (chunks*D, T, KP, 2), uncentred frames
+    assert spec.shape[1] == T
+    il, ir = parse_ipd(ipd) if ipd else ([], [])
+    ilt = torch.tensor(il, dtype=torch.int32, device=cuda)
+    irt = torch.tensor(ir, dtype=torch.int32, device=cuda)
+    npairs = len(il)
+    F = 257 * (npairs + 1)
+    ldp = (F + 63) // 64 * 64
+    mag = torch.empty(chunks, 257, T, device=cuda)
+    planes = torch.full((2, chunks * T, ldp), 7.0, dtype=torch.bfloat16, device=cuda)
+    feat = torch.full((chunks * T, ldp), 7.0, device=cuda)
+    nv.call("css_features_planes", nv.ptr(spec), nv.c_long(T), nv.c_long(D * T), nv.c_long(chunks), nv.c_int(T), nv.ptr(ilt),
+            nv.ptr(irt), nv.c_int(npairs), nv.ptr(mag), nv.ptr(planes), nv.c_long(planes.stride(0)), nv.c_int(ldp), nv.c_int(2),
+            nv.ptr(feat), nv.c_int(ldp))
+    # the two-kernel path on the same spectrum: same magnitude, same features up to summation order
+    from css_b200.executor.feature import features
+    mag2, feat2 = features(spec, T, D * T, chunks, T, ilt, irt, ldp)
+    assert torch.equal(mag, mag2)
+    assert float(feat[:, F:].abs().max()) == 0 and float(planes[:, :, F:].float().abs().max()) == 0
+    d = (feat[:, :F] - feat2[:, :F]).abs()
+    d = torch.minimum(d, 2 * math.pi - d)
+    assert float(d[:, :257].max()) < 1e-5 and float(d.mean()) < 1e-6 and float(d.max()) < 2e-2
+    # oracle: the same windows -> features -> MVN over time
+    _, f_o, _, _ = O.feature_extract(x if ipd else x[:, 0], ipd_index=ipd or None)                # (B, F_total, T)
+    fo = f_o.permute(0, 2, 1).contiguous()
+    mvn = O.mvn_time(fo)
+    got = planes.float().sum(0)[:, :F].reshape(chunks, T, F).cpu()
+    fg = feat[:, :F].reshape(chunks, T, F).cpu()
+    df = (fg - fo).abs()
+    df = torch.minimum(df, 2 * math.pi - df)
+    assert float(df[..., :257].max()) < 1e-4 and float(df.mean()) < 1e-5
+    ok = df < 1e-4                                   # elements whose IPD agrees: columns with a cut-adjacent element are skipped
+    col_ok = ok.all(dim=1, keepdim=True).expand_as(ok)
+    assert float(col_ok.float().mean()) > 0.97
+    assert float(((got - mvn).abs() * col_ok).max()) < 2e-4
+
+
 @pytest.mark.parametrize("M,N,K,act,alpha,res,clamp", [
     (300, 256, 1856, 0, 1.0, False, 0.0),
     (150, 1024, 256, 1, 1.0, False, 0.0),
