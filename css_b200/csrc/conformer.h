@@ -49,5 +49,5 @@ int mvn_time_planes_launch(const float* x, long n, int T, int F, int ld, void* p
 // spectrum -> features -> input MVN -> bf16 planes + magnitude in one kernel (features.cu); feat may be NULL
 bool features_planes_supported(int T, int n_pairs);
 int features_planes_launch(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
-                           const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
+                           const int* ipd_r, int n_pairs, int shared_right, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
                            float* feat, int ldf, cudaStream_t st);

@@ -154,7 +154,7 @@ struct SpecInput {
     const void* spec;
     long stride_d, stride_chunk;
     const int *ipd_l, *ipd_r;
-    int n_pairs;
+    int n_pairs, shared_right;
     float* mag;
 };
 
@@ -176,7 +176,8 @@ static int forward_tc(ConformerModel* m, float* feat, const SpecInput* si, long 
     int rc;
     if ((rc = build_weight_planes(m, st))) return rc;
     if (si)
-        rc = features_planes_launch(si->spec, si->stride_d, si->stride_chunk, N, T, si->ipd_l, si->ipd_r, si->n_pairs, si->mag, fP.ptr,
+        rc = features_planes_launch(si->spec, si->stride_d, si->stride_chunk, N, T, si->ipd_l, si->ipd_r, si->n_pairs, si->shared_right, si->mag,
+                                    fP.ptr,
                                     fP.plane_stride, c.ldin, P, nullptr, 0, st);
     else if (apply_mvn) rc = mvn_time_planes_launch(feat, N, T, c.idim, c.ldin, fP.ptr, fP.plane_stride, c.ldin, P, st);
     else rc = split_planes_launch(feat, M, c.idim, c.ldin, fP, st);
@@ -287,7 +288,7 @@ extern "C" int css_conformer_forward(void* model, float* feat, long N, int T, in
 // takes it; mag (N, 257, T) is the second output of css_features.  Tensor-core GEMM modes only (the fp32 SIMT mode keeps
 // the two-call form css_features + css_conformer_forward).
 extern "C" int css_conformer_forward_spec(void* model, const void* spec, long stride_d, long stride_chunk, const int* ipd_l,
-                                          const int* ipd_r, int n_pairs, long N, int T, float clamp_max, float* mag, float* masks,
+                                          const int* ipd_r, int n_pairs, int shared_right, long N, int T, float clamp_max, float* mag, float* masks,
                                           float* head, int ld_head, void* workspace, size_t workspace_bytes, cudaStream_t st) {
     ConformerModel* m = static_cast<ConformerModel*>(model);
     CSS_REQUIRE(m && spec && mag && workspace, "css_conformer_forward_spec: null argument");
@@ -298,7 +299,7 @@ extern "C" int css_conformer_forward_spec(void* model, const void* spec, long st
                 m->d.idim, n_pairs, CSS_NBINS * (n_pairs + 1));
     CSS_REQUIRE(features_planes_supported(T, n_pairs), "css_conformer_forward_spec: T=%d with %d IPD pairs unsupported", T, n_pairs);
     CSS_REQUIRE(workspace_bytes >= css_conformer_workspace_bytes(model, N, T), "css_conformer_forward_spec: workspace too small");
-    const SpecInput si = {spec, stride_d, stride_chunk, ipd_l, ipd_r, n_pairs, mag};
+    const SpecInput si = {spec, stride_d, stride_chunk, ipd_l, ipd_r, n_pairs, shared_right, mag};
     return forward_tc(m, nullptr, &si, N, T, 1, clamp_max, masks, head, ld_head, static_cast<char*>(workspace), g_gemm_mode, st);
 }
 

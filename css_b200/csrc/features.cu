@@ -280,18 +280,6 @@ extern "C" int css_mvn_time(float* x, long n, int T, int F, int ld, cudaStream_t
 // variance}, {mag feature variance}.  257 = 32 x 8 + 1: the last bin group is shifted to bins 249..256 and recomputes seven
 // bins to identical bits.
 // ---------------------------------------------------------------------------------------------
-// unit_cross with its rare cases (purely real bins, vanishing / huge products) out of line: the fused kernel inlines the common
-// path 6x per frame, and with the slow paths inlined as well its code no longer fits the instruction cache
-__device__ __noinline__ float2 unit_cross_rare(float2 a, float2 b) { return unit_cross(a, b); }
-__device__ __forceinline__ float2 unit_cross_fast(float2 a, float2 b) {
-    const float2 p = cmulc(a, b);
-    const float n2 = p.x * p.x + p.y * p.y;
-    if ((a.y == 0.f && b.y == 0.f) || !(n2 >= 1e-30f && n2 <= 1e30f)) return unit_cross_rare(a, b);
-    float r = rsqrtf(n2);
-    r = r * (1.5f - 0.5f * n2 * r * r);
-    return make_float2(p.x * r, p.y * r);
-}
-
 #define FP_BG 8
 #define FP_THREADS 256
 #define FP_SLOTS (FP_THREADS / FP_BG)       // 32 frame slots
@@ -326,8 +314,11 @@ __device__ __forceinline__ void fp_reduce(float (&v)[N], float* red, float* stat
     for (int i = 0; i < N; ++i) v[i] = stat[i * FP_BG + bin];
 }
 
-template <int NP, int PL>
-__global__ void __launch_bounds__(FP_THREADS, 3)
+// SAME_R: every pair has the same right channel ("1,0;2,0;..."), loaded once per frame -- the caller's claim (`shared_right`; the
+// tables live in device memory and the host does not read them); the kernel checks it and traps on a false claim.  Without the claim
+// the general variant runs (right and for any tables, 120 registers -> 2 CTAs per SM).
+template <int NP, int PL, bool SAME_R>
+__global__ void __launch_bounds__(FP_THREADS, SAME_R ? 3 : 2)
 features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T, const int* __restrict__ ipd_l,
                        const int* __restrict__ ipd_r, float* __restrict__ mag, __nv_bfloat16* __restrict__ planes,
                        long plane_stride, int ldp, float* __restrict__ feat, int ldf, int n_groups) {
@@ -336,7 +327,7 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
     float* MG = fp_smem + (size_t)2 * NP * T * FP_BG;                // [T][FP_BG] magnitude, later the mag feature
     float* red = MG + (size_t)T * FP_BG;                             // [FP_NV][FP_WARPS][FP_BG]
     float* stat = red + FP_NV * FP_WARPS * FP_BG;                    // [FP_NV][FP_BG]
-    long* offs = reinterpret_cast<long*>(stat + FP_NV * FP_BG);      // [2][8] channel offsets of the pairs (elements), [16] = shared right channel
+    int* offs = reinterpret_cast<int*>(stat + FP_NV * FP_BG);        // [2][8] channel offsets of the pairs (elements < 2^31, checked by the host), [16] = shared right channel
     // bin groups fastest: the CTAs that share a chunk's 128-byte lines (spectrum rows, plane rows) run together
     const long b = blockIdx.x / n_groups;
     const int grp = blockIdx.x - (int)b * n_groups;
@@ -347,35 +338,34 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
     const float2* base = spec + (b * stride_chunk) * CSS_KP + k;
     constexpr int NPA = NP > 0 ? NP : 1;
 
-    if (threadIdx.x < NP) {
-        offs[threadIdx.x] = (long)ipd_l[threadIdx.x] * stride_d * CSS_KP;
-        offs[8 + threadIdx.x] = (long)ipd_r[threadIdx.x] * stride_d * CSS_KP;
-    }
-    if (threadIdx.x == 32) {
+    constexpr bool same_r = SAME_R;
+    constexpr int NR = SAME_R ? 1 : NPA;
+    if (SAME_R) {
         bool sr = true;
         for (int p = 1; p < NP; ++p) sr &= ipd_r[p] == ipd_r[0];
-        offs[16] = sr;
+        if (!sr) __trap();
+    }
+    if (threadIdx.x < NP) {
+        const long ol = (long)ipd_l[threadIdx.x] * stride_d * CSS_KP, orr = (long)ipd_r[threadIdx.x] * stride_d * CSS_KP;
+        if ((ol | orr) >> 31) __trap();                 // 32-bit element offsets (the host checks 8 channels' worth)
+        offs[threadIdx.x] = (int)ol;
+        offs[8 + threadIdx.x] = (int)orr;
     }
     __syncthreads();
-    long offl[NPA], offr[NPA];
+    int offl[NPA], offr[NR];
 #pragma unroll
-    for (int p = 0; p < NP; ++p) {
-        offl[p] = offs[p];
-        offr[p] = offs[8 + p];
-    }
-    const bool same_r = offs[16] != 0;
-    struct Frame { float2 x0, xl[NPA], xr[NPA]; };
+    for (int p = 0; p < NP; ++p) offl[p] = offs[p];
+#pragma unroll
+    for (int p = 0; p < (NP > 0 ? NR : 0); ++p) offr[p] = offs[8 + p];
+    struct Frame { float2 x0, xl[NPA], xr[NR]; };
     auto fetch = [&](Frame& f, int t) {
         const float2* q = base + (long)t * CSS_KP;
         f.x0 = q[0];
 #pragma unroll
         for (int p = 0; p < NP; ++p) f.xl[p] = q[offl[p]];
-        if (NP > 0) {
-            if (same_r) f.xr[0] = q[offr[0]];
-            else {
+        if constexpr (NP > 0) {
 #pragma unroll
-                for (int p = 0; p < NP; ++p) f.xr[p] = q[offr[p]];
-            }
+            for (int p = 0; p < NR; ++p) f.xr[p] = q[offr[p]];
         }
     };
 
@@ -391,12 +381,36 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
             const float m = sqrtf(cur.x0.x * cur.x0.x + cur.x0.y * cur.x0.y);
             MG[t * FP_BG + bin] = m;
             acc[0] += fmaxf(m, FEAT_EPS);
+            // common path for every pair, branch-free; the rare cases (purely real bins, vanishing / huge products: digital
+            // silence) are flagged, contribute zero here and are redone below by the full unit_cross, one pair at a time in a
+            // loop that is not unrolled (no calls, no spills, one copy of the slow code)
+            unsigned rare = 0;
 #pragma unroll
             for (int p = 0; p < NP; ++p) {
-                const float2 u = unit_cross_fast(cur.xl[p], same_r ? cur.xr[0] : cur.xr[p]);
+                const float2 a = cur.xl[p], c = cur.xr[same_r ? 0 : p];
+                const float2 w = cmulc(a, c);
+                const float n2 = w.x * w.x + w.y * w.y;
+                const bool odd = (a.y == 0.f && c.y == 0.f) || !(n2 >= 1e-30f && n2 <= 1e30f);
+                rare |= (odd ? 1u : 0u) << p;
+                float r = rsqrtf(n2);
+                r = r * (1.5f - 0.5f * n2 * r * r);
+                const float2 u = odd ? make_float2(0.f, 0.f) : make_float2(w.x * r, w.y * r);
                 U[(p * T + t) * FP_BG + bin] = u;
                 acc[1 + 2 * p] += u.x;
                 acc[2 + 2 * p] += u.y;
+            }
+            if (rare) {
+                const float2* q = base + (long)t * CSS_KP;
+#pragma unroll 1
+                for (int p = 0; p < NP; ++p)
+                    if ((rare >> p) & 1u) U[(p * T + t) * FP_BG + bin] = unit_cross(q[offs[p]], q[offs[8 + p]]);
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+                    if ((rare >> p) & 1u) {
+                        const float2 u = U[(p * T + t) * FP_BG + bin];
+                        acc[1 + 2 * p] += u.x;
+                        acc[2 + 2 * p] += u.y;
+                    }
             }
             cur = nxt;
         }
@@ -499,7 +513,7 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
 }
 
 static size_t fp_smem_bytes(int np, int T) {
-    return sizeof(float) * ((size_t)2 * np * T * FP_BG + (size_t)T * FP_BG + FP_NV * FP_WARPS * FP_BG + FP_NV * FP_BG) + 17 * sizeof(long);
+    return sizeof(float) * ((size_t)2 * np * T * FP_BG + (size_t)T * FP_BG + FP_NV * FP_WARPS * FP_BG + FP_NV * FP_BG) + 17 * sizeof(int);
 }
 bool features_planes_supported(int T, int n_pairs) {
     return T > 1 && n_pairs >= 0 && n_pairs <= 7 && fp_smem_bytes(n_pairs, T) <= 200 * 1024;
@@ -507,30 +521,40 @@ bool features_planes_supported(int T, int n_pairs) {
 
 template <int NP, int PL>
 static int features_planes_go(const float2* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
-                              const int* ipd_r, float* mag, void* planes, long plane_stride, int ldp, float* feat, int ldf,
-                              cudaStream_t st) {
+                              const int* ipd_r, bool shared_right, float* mag, void* planes, long plane_stride, int ldp,
+                              float* feat, int ldf, cudaStream_t st) {
     const size_t smem = fp_smem_bytes(NP, T);
     static CssPerDevice attr_set;
-    if (attr_set.first()) cudaFuncSetAttribute(features_planes_kernel<NP, PL>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (attr_set.first()) {
+        cudaFuncSetAttribute(features_planes_kernel<NP, PL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(features_planes_kernel<NP, PL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    }
     const int n_groups = (CSS_NBINS + FP_BG - 1) / FP_BG;
     CSS_REQUIRE(n_chunks * n_groups < (1L << 31), "css_features_planes: too many chunks (%ld)", n_chunks);
-    features_planes_kernel<NP, PL><<<(unsigned)(n_chunks * n_groups), FP_THREADS, smem, st>>>(
-        spec, stride_d, stride_chunk, T, ipd_l, ipd_r, mag, static_cast<__nv_bfloat16*>(planes), plane_stride, ldp, feat, ldf, n_groups);
+    const unsigned grid = (unsigned)(n_chunks * n_groups);
+    __nv_bfloat16* pp = static_cast<__nv_bfloat16*>(planes);
+    if (shared_right || NP <= 1)
+        features_planes_kernel<NP, PL, true><<<grid, FP_THREADS, smem, st>>>(spec, stride_d, stride_chunk, T, ipd_l, ipd_r, mag, pp,
+                                                                           plane_stride, ldp, feat, ldf, n_groups);
+    else
+        features_planes_kernel<NP, PL, false><<<grid, FP_THREADS, smem, st>>>(spec, stride_d, stride_chunk, T, ipd_l, ipd_r, mag, pp,
+                                                                            plane_stride, ldp, feat, ldf, n_groups);
     return css_check_launch("css_features_planes");
 }
 
 // mag (B, 257, T); planes: n_planes x (B*T, ldp) bf16, ldp >= 257 (n_pairs + 1), padding zeroed; feat (B*T, ldf) fp32 or NULL.
 int features_planes_launch(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
-                           const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
+                           const int* ipd_r, int n_pairs, int shared_right, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
                            float* feat, int ldf, cudaStream_t st) {
     CSS_REQUIRE(n_chunks > 0 && T > 1, "css_features_planes: empty input (chunks=%ld T=%d)", n_chunks, T);
     CSS_REQUIRE(features_planes_supported(T, n_pairs), "css_features_planes: T=%d with %d IPD pairs does not fit shared memory", T, n_pairs);
     CSS_REQUIRE(ldp >= CSS_NBINS * (n_pairs + 1) && (!feat || ldf >= CSS_NBINS * (n_pairs + 1)), "css_features_planes: pitch too small");
     CSS_REQUIRE(n_planes >= 1 && n_planes <= 3, "css_features_planes: 1..3 planes");
+    CSS_REQUIRE(n_pairs == 0 || 8 * stride_d * CSS_KP < (1L << 31), "css_features_planes: channel stride %ld too large for 32-bit offsets", stride_d);
     // algorithmic bytes: spectrum read once per chunk, magnitude + planes written
     CssProfScope prof(6, (double)n_chunks * T * (CSS_NBINS * ((n_pairs ? 7 : 1) * 8.0 + 4.0) + (double)ldp * 2.0 * n_planes), st);
     const float2* s = static_cast<const float2*>(spec);
-#define FP_ARGS s, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, mag, planes, plane_stride, ldp, feat, ldf, st
+#define FP_ARGS s, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, shared_right != 0, mag, planes, plane_stride, ldp, feat, ldf, st
 #define FP_CASE(NP)                                                          \
     case NP:                                                                 \
         if (n_planes == 1) return features_planes_go<NP, 1>(FP_ARGS);        \
@@ -546,8 +570,8 @@ int features_planes_launch(const void* spec, long stride_d, long stride_chunk, l
 
 // Stand-alone C-ABI form (tests, other callers): same outputs as css_features followed by the model-side MVN + plane split.
 extern "C" int css_features_planes(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
-                                   const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp,
+                                   const int* ipd_r, int n_pairs, int shared_right, float* mag, void* planes, long plane_stride, int ldp,
                                    int n_planes, float* feat, int ldf, cudaStream_t st) {
-    return features_planes_launch(spec, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, n_pairs, mag, planes, plane_stride, ldp,
+    return features_planes_launch(spec, stride_d, stride_chunk, n_chunks, T, ipd_l, ipd_r, n_pairs, shared_right, mag, planes, plane_stride, ldp,
                                   n_planes, feat, ldf, st);
 }

@@ -113,7 +113,8 @@ class Separator:
             if before_batch is not None:
                 before_batch(i, b0, nb)
             sub = spec.reshape(-1)[b0 * stride_chunk * nv.KP * 2:]
-            fused = self.model.masks_from_spec(sub, stride_d, stride_chunk, nb, T, il, ir, clamp_max=1.0) \
+            fused = self.model.masks_from_spec(sub, stride_d, stride_chunk, nb, T, il, ir, clamp_max=1.0,
+                                               shared_right=len(set(self.feature.ipd_r)) <= 1) \
                 if self.fused_front_end and hasattr(self.model, "masks_from_spec") else None
             if fused is not None:
                 m, mag = fused

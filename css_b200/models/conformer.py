@@ -233,7 +233,7 @@ class Conformer(nn.Module):
                 nv.c_int(1 if apply_mvn else 0), nv.c_float(clamp_max), nv.ptr(masks), nv.ptr(head), nv.c_int(ld_head),
                 nv.ptr(ws), nv.c_size_t(ws.numel()))
 
-    def masks_from_spec(self, spec, stride_d, stride_chunk, N, T, ipd_l, ipd_r, clamp_max=1.0):
+    def masks_from_spec(self, spec, stride_d, stride_chunk, N, T, ipd_l, ipd_r, clamp_max=1.0, shared_right=False):
         """Executor fast path with the fused front end: chunk spectra -> (masks (N, num_bins, T, 3), mag (N, num_bins, T)),
         or None when the shape / GEMM mode is not covered (the caller then uses features() + masks_layout())."""
         n_pairs = int(ipd_l.numel())
@@ -245,8 +245,8 @@ class Conformer(nn.Module):
         out = torch.empty(N, self.num_bins, T, self.num_spk + self.num_noise, dtype=torch.float32, device=spec.device)
         mag = torch.empty(N, self.num_bins, T, dtype=torch.float32, device=spec.device)
         nv.call("css_conformer_forward_spec", ctypes.c_void_p(eng["handle"]), nv.ptr(spec), nv.c_long(stride_d),
-                nv.c_long(stride_chunk), nv.ptr(ipd_l), nv.ptr(ipd_r), nv.c_int(n_pairs), nv.c_long(N), nv.c_int(T),
-                nv.c_float(clamp_max), nv.ptr(mag), nv.ptr(out), nv.ptr(None), nv.c_int(0), nv.ptr(ws), nv.c_size_t(ws.numel()))
+                nv.c_long(stride_chunk), nv.ptr(ipd_l), nv.ptr(ipd_r), nv.c_int(n_pairs), nv.c_int(1 if shared_right else 0), nv.c_long(N),
+                nv.c_int(T), nv.c_float(clamp_max), nv.ptr(mag), nv.ptr(out), nv.ptr(None), nv.c_int(0), nv.ptr(ws), nv.c_size_t(ws.numel()))
         return out, mag
 
     def masks_layout(self, feat, N, T, clamp_max=1.0):

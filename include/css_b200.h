@@ -86,16 +86,19 @@ int css_conformer_forward(void* model, float* feat, long N, int T, int apply_mvn
 /* FeatureExtractor.forward (css/executor/feature.py:156-175) + the model's input MVN (conformer.py:95) + Conformer.forward
  * (conformer.py:83-104) in one call, as css/executor/separator.py:86-104 chains them: the fp32 feature matrix is never
  * materialised.  spec/strides/ipd tables as css_features; mag (N,257,T) is css_features' magnitude output.  Tensor-core
- * GEMM modes only; css_features_planes_supported(T, n_pairs) says whether the fused front end takes the shape. */
+ * GEMM modes only; css_features_planes_supported(T, n_pairs) says whether the fused front end takes the shape.
+ * shared_right != 0 is the caller's claim that every pair has the same right channel (ipd_r[p] == ipd_r[0], as in
+ * conf/config_7ch.yaml "1,0;2,0;..."): that channel is then loaded once per frame; the kernel checks the claim and traps
+ * if it is false.  0 is always correct. */
 int css_conformer_forward_spec(void* model, const void* spec, long stride_d, long stride_chunk, const int* ipd_l,
-                               const int* ipd_r, int n_pairs, long N, int T, float clamp_max, float* mag, float* masks,
+                               const int* ipd_r, int n_pairs, int shared_right, long N, int T, float clamp_max, float* mag, float* masks,
                                float* head, int ld_head, void* workspace, size_t workspace_bytes, css_stream_t stream);
 int css_features_planes_supported(int T, int n_pairs);
 /* The front end of that call on its own: magnitude (N,257,T) + the n_planes bf16 split planes (n_planes x (N*T, ldp),
  * plane_stride elements apart, K padding zeroed) of the time-normalised features; feat (N*T, ldf) fp32 = css_features'
  * feature output, or NULL. */
 int css_features_planes(const void* spec, long stride_d, long stride_chunk, long n_chunks, int T, const int* ipd_l,
-                        const int* ipd_r, int n_pairs, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
+                        const int* ipd_r, int n_pairs, int shared_right, float* mag, void* planes, long plane_stride, int ldp, int n_planes,
                         float* feat, int ldf, css_stream_t stream);
 
 /* ---- BLSTM mask estimator: css/models/blstm.py:68-88 (BLSTM.forward) ---- */

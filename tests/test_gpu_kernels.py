@@ -130,8 +130,16 @@ def test_fused_front_end_matches_oracle_features_and_mvn(cuda, ipd, chunks, T):
     planes = torch.full((2, chunks * T, ldp), 7.0, dtype=torch.bfloat16, device=cuda)
     feat = torch.full((chunks * T, ldp), 7.0, device=cuda)
     nv.call("css_features_planes", nv.ptr(spec), nv.c_long(T), nv.c_long(D * T), nv.c_long(chunks), nv.c_int(T), nv.ptr(ilt),
-            nv.ptr(irt), nv.c_int(npairs), nv.ptr(mag), nv.ptr(planes), nv.c_long(planes.stride(0)), nv.c_int(ldp), nv.c_int(2),
+            nv.ptr(irt), nv.c_int(npairs), nv.c_int(1 if len(set(ir)) <= 1 else 0), nv.ptr(mag), nv.ptr(planes), nv.c_long(planes.stride(0)), nv.c_int(ldp), nv.c_int(2),
             nv.ptr(feat), nv.c_int(ldp))
+    if npairs > 1 and len(set(ir)) == 1:
+        # without the shared-right-channel claim the general variant runs: same bits
+        planes_g = torch.empty_like(planes)
+        mag_g = torch.empty_like(mag)
+        nv.call("css_features_planes", nv.ptr(spec), nv.c_long(T), nv.c_long(D * T), nv.c_long(chunks), nv.c_int(T), nv.ptr(ilt),
+                nv.ptr(irt), nv.c_int(npairs), nv.c_int(0), nv.ptr(mag_g), nv.ptr(planes_g), nv.c_long(planes.stride(0)),
+                nv.c_int(ldp), nv.c_int(2), nv.ptr(None), nv.c_int(0))
+        assert torch.equal(planes_g, planes) and torch.equal(mag_g, mag)
     # the two-kernel path on the same spectrum: same magnitude, same features up to summation order
     from css_b200.executor.feature import features
     mag2, feat2 = features(spec, T, D * T, chunks, T, ilt, irt, ldp)
