@@ -271,7 +271,8 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 #define CM_HALO 16
 #define CM_TAPS (2 * CM_HALO + 1)
 #define CM_THREADS 512
-#define CM_MAX_ROWS 220          // (tile + 2*halo) rows of 1 KB each must fit in shared memory
+#define CM_MAX_ROWS 192          // (tile + 2*halo) rows of 1 KB each + the tap table must fit in shared memory
+#define CM_WPITCH (CM_D + 1)     // tap table in shared memory: [tap][channel], pitch 257 floats
 #define CM_OUT 8                 // outputs per register pass of the depthwise filter
 
 // One CTA per (sequence, time tile); a 150-frame chunk is one tile, so nothing is recomputed.
@@ -281,11 +282,11 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 // fp32 FMA (FFMA2) -- the kernel is bound by the FMA pipe, not by memory.
 // Tiling (ConvPlan): the first n_full sequences get `full_tiles` tiles each; what is left -- less than one wave of CTAs,
 // which would otherwise cost a whole extra wave -- is cut into `tail_tiles` short tiles spread over the idle SMs.
-struct ConvPlan { int n_full, full_tiles, full_len, tail_tiles, tail_len; };
+struct ConvPlan { int n_full, full_tiles, full_len, tail_tiles, tail_len, smem_rows; };
 
 __global__ void __launch_bounds__(CM_THREADS, 1)
 conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, ConvPlan pl, ConvModuleParams p) {
-    extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D]
+    extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D], then the tap table [CM_TAPS][CM_WPITCH]
     long n;
     int t0, tile;
     {
@@ -304,6 +305,15 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
     const int rows = tile + 2 * CM_HALO;
     const float* xs = x + n * (long)T * CM_D;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // The depthwise taps (d, 33) go to shared memory transposed, by 4-byte async copies that run under phase 1: read in
+    // place by thread = channel they were 66 loads with a 132-byte stride between lanes, a fifth of the kernel's stall samples.
+    float* Wt = U + (size_t)pl.smem_rows * CM_D;
+    for (int i = threadIdx.x; i < CM_D * CM_TAPS; i += CM_THREADS) {
+        const int ch = i / CM_TAPS, k = i - ch * CM_TAPS;
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Wt + k * CM_WPITCH + ch);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.dw_w + i) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
     // four rows per pass: their eight loads are in flight together (the phase is latency-bound otherwise)
     constexpr int NW = CM_THREADS / 32, RB = 4;
     for (int rb = warp; rb < rows; rb += NW * RB) {
@@ -357,20 +367,25 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
             }
         }
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
     const int c = 2 * (threadIdx.x & (CM_D / 2 - 1)), part = threadIdx.x >> 7;     // channels c, c+1
     float2 w[CM_TAPS];
 #pragma unroll
-    for (int k = 0; k < CM_TAPS; ++k) w[k] = make_float2(p.dw_w[c * CM_TAPS + k], p.dw_w[(c + 1) * CM_TAPS + k]);
+    for (int k = 0; k < CM_TAPS; ++k) w[k] = make_float2(Wt[k * CM_WPITCH + c], Wt[k * CM_WPITCH + c + 1]);
     const float2 bias = *reinterpret_cast<const float2*>(p.dw_b + c);
     const float2 sc = *reinterpret_cast<const float2*>(p.bn_scale + c), sh = *reinterpret_cast<const float2*>(p.bn_shift + c);
     float* os = out + n * (long)T * CM_D;
     const int per = ((tile + 4 * CM_OUT - 1) / (4 * CM_OUT)) * CM_OUT;       // multiple of CM_OUT
     const int t_end = min(tile, (part + 1) * per);
     for (int tt = part * per; tt < t_end; tt += CM_OUT) {
-        float2 acc[CM_OUT];
+        float2 acc[CM_OUT], xv[CM_OUT];
 #pragma unroll
-        for (int j = 0; j < CM_OUT; ++j) acc[j] = bias;
+        for (int j = 0; j < CM_OUT; ++j) {
+            acc[j] = bias;
+            // the residual rows are requested before the filter pass and consumed after it
+            xv[j] = (tt + j < t_end) ? *reinterpret_cast<const float2*>(xs + (long)(t0 + tt + j) * CM_D + c) : make_float2(0.f, 0.f);
+        }
 #pragma unroll
         for (int kk = 0; kk < CM_TAPS + CM_OUT - 1; ++kk) {
             const int r = tt + kk;
@@ -383,10 +398,9 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
         for (int j = 0; j < CM_OUT; ++j) {
             if (tt + j < t_end) {
                 const long idx = (long)(t0 + tt + j) * CM_D + c;
-                const float2 xv = *reinterpret_cast<const float2*>(xs + idx);
                 float2 o;
-                o.x = xv.x + (fmaxf(acc[j].x * sc.x + sh.x, 0.f) * p.pw2_w + p.pw2_b);
-                o.y = xv.y + (fmaxf(acc[j].y * sc.y + sh.y, 0.f) * p.pw2_w + p.pw2_b);
+                o.x = xv[j].x + (fmaxf(acc[j].x * sc.x + sh.x, 0.f) * p.pw2_w + p.pw2_b);
+                o.y = xv[j].y + (fmaxf(acc[j].y * sc.y + sh.y, 0.f) * p.pw2_w + p.pw2_b);
                 *reinterpret_cast<float2*>(os + idx) = o;
             }
         }
@@ -418,10 +432,12 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
     }
     const long ctas = (long)pl.n_full * pl.full_tiles + (N - pl.n_full) * pl.tail_tiles;
     CSS_REQUIRE(ctas < (1L << 31), "conv_module: too many sequences (%ld)", N);
-    const size_t smem = sizeof(float) * (size_t)(pl.full_len + 2 * CM_HALO) * CM_D;
+    pl.smem_rows = pl.full_len + 2 * CM_HALO;
+    const size_t smem = sizeof(float) * ((size_t)pl.smem_rows * CM_D + CM_TAPS * CM_WPITCH);
     static CssPerDevice attr_set;
     if (attr_set.first()) {
-        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_MAX_ROWS * CM_D * 4);
+        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (CM_MAX_ROWS * CM_D + CM_TAPS * CM_WPITCH) * 4);
     }
     css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
     conv_module_kernel<<<(unsigned)ctas, CM_THREADS, smem, st>>>(x, out, T, pl, p);
