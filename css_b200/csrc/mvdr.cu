@@ -40,44 +40,80 @@ __device__ __forceinline__ void scm_row(const float2 (&x)[MV_M], const float (&w
     }
 }
 
+// Frames reach the four warps through a ring of SC_ST stages of SC_F frames in shared memory, filled by 16-byte async copies
+// (7 channels x 32 bins complex + 3 masks x 32 bins per frame = 2,176 B): the first version had every warp load its own
+// operands one frame ahead and spent its time waiting for one round trip per frame (15 % of the DRAM rate at 20 warps per SM);
+// now SC_ST - 1 stages are in flight per CTA and the four warps share one copy of the frame.
+#define SC_F 5
+#define SC_ST 4
+#define SC_XF (MV_M * MV_BINS)            // float2 per frame
+#define SC_WF (3 * MV_BINS)               // float per frame
+#define SC_PIECES (SC_XF / 2 + SC_WF / 4) // 16-byte pieces per frame: 112 + 24
+
+__device__ __forceinline__ void sc_copy16(void* dst, const void* src, bool valid) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+    const int n = valid ? 16 : 0;                         // 0 source bytes: the 16 bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+}
+
 template <int G>
 __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
                                           long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
-                                          float* __restrict__ scm, float* __restrict__ energy) {
+                                          float* __restrict__ scm, float* __restrict__ energy, float2* Xs, float* Ws) {
     constexpr int R0 = G, R1 = (G == 0) ? -1 : MV_M - G;
     const long b = blockIdx.y;
-    const int lane = threadIdx.x;
-    const int k = blockIdx.x * MV_BINS + lane;
+    const int lane = threadIdx.x, tid = threadIdx.y * MV_BINS + threadIdx.x;
+    const int k0 = blockIdx.x * MV_BINS, k = k0 + lane;
     float2 acc[3][7];                        // (re, im) of the thread's 7 pairs, per mask: one packed FMA (FFMA2) each
 #pragma unroll
     for (int m = 0; m < 3; ++m)
 #pragma unroll
         for (int i = 0; i < 7; ++i) acc[m][i] = make_float2(0.f, 0.f);
     float msum[3] = {0.f, 0.f, 0.f}, e_mask[2] = {0.f, 0.f};
-    if (k < CSS_NBINS) {
-        const float* mrow = stitched + (b * hop_frames) * (long)CSS_KP + k;
-        const float2* sp = spec + (b * hop_frames - 1) * (long)CSS_KP + k;      // frame t >= 1 of the chunk at sp + t * KP
-        const long mstride = L * CSS_KP, cstride = frames * CSS_KP;
-        float2 xn[MV_M];
-        float wn[3];
+    const float* mrow = stitched + (b * hop_frames) * (long)CSS_KP + k0;
+    const float2* sp = spec + (b * hop_frames - 1) * (long)CSS_KP + k0;      // frame t >= 1 of the chunk at sp + t * KP
+    const long mstride = L * CSS_KP, cstride = frames * CSS_KP;
+    const int kmax = CSS_KP - k0;                                            // elements of a row from k0 on (8 in the last tile)
+
+    auto load_stage = [&](int st) {
+        const int f0 = st * SC_F, buf = st % SC_ST;
+        for (int i = tid; i < SC_F * SC_PIECES; i += 4 * MV_BINS) {
+            const int f = i / SC_PIECES, r = i - f * SC_PIECES, t = f0 + f;
+            if (r < SC_XF / 2) {
+                const int d = r / (MV_BINS / 2), j = 2 * (r - d * (MV_BINS / 2));
+                const bool ok = t < T && j < kmax;
+                const float2* src = (t == 0) ? edge + ((long)d * n_chunks + b) * CSS_KP + k0 + j : sp + d * cstride + (long)t * CSS_KP + j;
+                sc_copy16(Xs + (buf * SC_F + f) * SC_XF + d * MV_BINS + j, ok ? src : spec, ok);
+            } else {
+                const int q = r - SC_XF / 2, m = q / (MV_BINS / 4), j = 4 * (q - m * (MV_BINS / 4));
+                const bool ok = t < T && j < kmax;
+                sc_copy16(Ws + (buf * SC_F + f) * SC_WF + m * MV_BINS + j, ok ? (const void*)(mrow + m * mstride + (long)t * CSS_KP + j) : (const void*)spec, ok);
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    const int n_st = (T + SC_F - 1) / SC_F;
 #pragma unroll
-        for (int d = 0; d < MV_M; ++d) xn[d] = edge[((long)d * n_chunks + b) * CSS_KP + k];
-#pragma unroll
-        for (int m = 0; m < 3; ++m) wn[m] = mrow[m * mstride];
-#pragma unroll 2
-        for (int t = 0; t < T; ++t) {
+    for (int s0 = 0; s0 < SC_ST - 1; ++s0) {
+        if (s0 < n_st) load_stage(s0);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+    for (int st = 0; st < n_st; ++st) {
+        asm volatile("cp.async.wait_group %0;" ::"n"(SC_ST - 2) : "memory");
+        __syncthreads();                     // stage st has landed for everyone; stage st - 1 has been consumed by everyone
+        if (st + SC_ST - 1 < n_st) load_stage(st + SC_ST - 1);
+        else asm volatile("cp.async.commit_group;" ::: "memory");
+        const int buf = st % SC_ST, nf = min(SC_F, T - st * SC_F);
+        for (int f = 0; f < nf; ++f) {
             float2 x[MV_M];
             float w[3];
+            const float2* xf = Xs + (buf * SC_F + f) * SC_XF + lane;
+            const float* wf = Ws + (buf * SC_F + f) * SC_WF + lane;
 #pragma unroll
-            for (int d = 0; d < MV_M; ++d) x[d] = xn[d];
+            for (int d = 0; d < MV_M; ++d) x[d] = xf[d * MV_BINS];
 #pragma unroll
-            for (int m = 0; m < 3; ++m) w[m] = wn[m];
-            if (t + 1 < T) {
-#pragma unroll
-                for (int d = 0; d < MV_M; ++d) xn[d] = sp[d * cstride + (long)(t + 1) * CSS_KP];
-#pragma unroll
-                for (int m = 0; m < 3; ++m) wn[m] = mrow[m * mstride + (long)(t + 1) * CSS_KP];
-            }
+            for (int m = 0; m < 3; ++m) w[m] = wf[m * MV_BINS];
 #pragma unroll
             for (int m = 0; m < 3; ++m) msum[m] += w[m];
             if (G == 0) {
@@ -90,6 +126,8 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
             scm_row<R0, 0>(x, w, acc);
             if (R1 >= 0) scm_row<(R1 >= 0 ? R1 : 0), MV_M - R0>(x, w, acc);
         }
+    }
+    if (k < CSS_NBINS) {
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
             float* dst = scm + ((b * 3 + m) * (long)MV_E) * CSS_KP + k;
@@ -112,7 +150,7 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
     if (G == 0) {
 #pragma unroll
         for (int m = 0; m < 2; ++m) {
-            const float e = warp_sum(e_mask[m]);
+            const float e = warp_sum(k < CSS_NBINS ? e_mask[m] : 0.f);
             if (lane == 0) energy[((b * 2 + m) * gridDim.x + blockIdx.x) * 2 + 1] = e;
         }
     }
@@ -122,11 +160,13 @@ __global__ void __launch_bounds__(128)
 mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
                 const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
                 float* __restrict__ energy) {
-    switch (threadIdx.y) {      // warp-uniform
-        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
-        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
-        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
-        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy); break;
+    __shared__ __align__(16) float2 Xs[SC_ST * SC_F * SC_XF];
+    __shared__ __align__(16) float Ws[SC_ST * SC_F * SC_WF];
+    switch (threadIdx.y) {      // warp-uniform; every arm runs the same copy / barrier sequence
+        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
+        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
+        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
+        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
     }
 }
 
