@@ -4,6 +4,7 @@
 #include "conformer.h"
 #include "gemm.h"
 #include "../../include/css_b200.h"
+#include <cstdlib>
 #include <new>
 #include <vector>
 
@@ -132,8 +133,11 @@ static int tc_gemm(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
 // ln_done: yP already holds the planes of LN(x) (written by the previous block's output norm).
 // next_g/next_b: LayerNorm that follows this FFN (the attention-in norm after the first FFN of a block); when the GEMM can
 // take it in its epilogue, yP leaves holding the planes of LN(x_new) and *fused is set -- the caller then skips that launch.
+// norm_x (the block's second FFN): next_g/next_b is the block's OUTPUT norm -- x itself leaves normalised (conformer.py:356) -- and
+// yP holds the planes of that x, or of LN(x; next2_g, next2_b), the following block's FFN-in norm, when next2_g is given.
 static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& w2, float* x, const PlaneMat& yP, const PlaneMat& hP,
-                  int P, long M, int d, int dffn, bool ln_done, const float* next_g, const float* next_b, bool* fused, cudaStream_t st) {
+                  int P, long M, int d, int dffn, bool ln_done, const float* next_g, const float* next_b, bool* fused, cudaStream_t st,
+                  bool norm_x = false, const float* next2_g = nullptr, const float* next2_b = nullptr) {
     int rc = ln_done ? 0 : layernorm_planes_launch(x, w.ln_g, w.ln_b, nullptr, M, d, 1e-5f, 0, yP.ptr, yP.plane_stride, P, st);
     if (rc) return rc;
     GemmEpilogue e1 = {w.b1, 1, 1.f, nullptr, 0, 0.f};
@@ -144,6 +148,9 @@ static int ffn_tc(const css_ffn_weights& w, const PlaneMat& w1, const PlaneMat& 
     if (fuse) {
         e2.ln_g = next_g;
         e2.ln_b = next_b;
+        e2.ln_to_c = norm_x ? 1 : 0;
+        e2.ln2_g = norm_x ? next2_g : nullptr;
+        e2.ln2_b = norm_x ? next2_b : nullptr;
         return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, &yP, st);
     }
     return tc_gemm(hP, w2, P, M, d, dffn, e2, x, d, nullptr, st);
@@ -210,13 +217,17 @@ static int forward_tc(ConformerModel* m, float* feat, const SpecInput* si, long 
                                b.bn_scale, b.bn_shift, b.pw2_w, b.pw2_b, 33};
         if ((rc = conv_module_launch(x, a, N, T, d, cp, st))) return rc;
         { float* t = x; x = a; a = t; }
-        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, false, nullptr, nullptr, nullptr, st))) return rc;
-        // block output LN: fp32 for the residual stream, and in the same pass the planes the next GEMM reads -- the next
-        // block's FFN-in norm of that output, or the output itself for the head GEMM after the last block
+        // block output LN: fp32 for the residual stream, and with it the planes the next GEMM reads -- the next block's FFN-in
+        // norm of that output, or the output itself for the head GEMM after the last block.  Both norms ride in the epilogue
+        // of the FFN's second GEMM when the shape allows it (css_gemm_tc_ln_fusion(0) / CSS_B200_GEMM_LN=0: separate launch).
         const bool last = l == c.num_blocks - 1;
         const css_ffn_weights* nf = last ? nullptr : &m->blk[l + 1].ff_in;
-        if ((rc = layernorm2_planes_launch(x, b.out_ln_g, b.out_ln_b, x, nf ? nf->ln_g : nullptr, nf ? nf->ln_b : nullptr, M, d, 1e-5f,
-                                           0, yP.ptr, yP.plane_stride, P, st))) return rc;
+        bool out_ln_done = false;
+        if ((rc = ffn_tc(b.ff_out, q.ff_out_w1, q.ff_out_w2, x, yP, hP, P, M, d, dffn, false, b.out_ln_g,
+                         b.out_ln_b, &out_ln_done, st, true, nf ? nf->ln_g : nullptr, nf ? nf->ln_b : nullptr))) return rc;
+        if (!out_ln_done && (rc = layernorm2_planes_launch(x, b.out_ln_g, b.out_ln_b, x, nf ? nf->ln_g : nullptr, nf ? nf->ln_b : nullptr, M, d, 1e-5f,
+                                           0, yP.ptr, yP.plane_stride, P, st)))
+            return rc;
     }
     if (c.num_blocks == 0 && (rc = split_planes_launch(x, M, d, d, yP, st))) return rc;
     if (head) {

@@ -345,7 +345,7 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
         for (int p = 1; p < NP; ++p) sr &= ipd_r[p] == ipd_r[0];
         if (!sr) __trap();
     }
-    if (threadIdx.x < NP) {
+    if ((int)threadIdx.x < NP) {
         const long ol = (long)ipd_l[threadIdx.x] * stride_d * CSS_KP, orr = (long)ipd_r[threadIdx.x] * stride_d * CSS_KP;
         if ((ol | orr) >> 31) __trap();                 // 32-bit element offsets (the host checks 8 channels' worth)
         offs[threadIdx.x] = (int)ol;

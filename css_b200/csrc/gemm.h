@@ -17,6 +17,11 @@ struct GemmEpilogue {
     // LayerNorm(C row; ln_g, ln_b, eps 1e-5) -- see gemm_tc_ln_fusable()
     const float* ln_g = nullptr;
     const float* ln_b = nullptr;
+    // ln_to_c != 0: C gets LayerNorm(result row; ln_g, ln_b) instead of the raw result (a block's output norm, conformer.py:356),
+    // and `out` the split planes of that C -- or, with ln2_g / ln2_b set, of a SECOND LayerNorm of it (the next block's FFN-in norm)
+    int ln_to_c = 0;
+    const float* ln2_g = nullptr;
+    const float* ln2_b = nullptr;
     // MN-major operands (tcgen05 path, training kernels): the operand is stored with its NON-contracted index contiguous,
     //   a_mn: A given as planes of A^T, i.e. a (K, M) row-major matrix (pitch A.ld >= M)  -- dW = dY^T X reads dY as it is
     //   b_mn: W given as planes of W^T, i.e. a (K, N) row-major matrix (pitch W.ld >= N)  -- dX = dY W reads W as it is

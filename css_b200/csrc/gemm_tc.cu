@@ -141,6 +141,9 @@ struct TcEpilogue {
     // EM 4: planes = split planes of LayerNorm(c row; ln_g, ln_b)
     const float* ln_g;
     const float* ln_b;
+    int ln_to_c;                 // c = LayerNorm(result) and planes = split(c) or split(LayerNorm(c; ln2_g, ln2_b))
+    const float* ln2_g;
+    const float* ln2_b;
 };
 
 template <int P> struct Terms;
@@ -571,7 +574,9 @@ __device__ __forceinline__ void epilogue_tile_tma(const TcEpilogue& ep, const CU
             bb[j] = ep.bias ? __ldg(reinterpret_cast<const float4*>(ep.bias + col0) + j) : make_float4(0.f, 0.f, 0.f, 0.f);
         uint32_t r[32];
         tc_ld32(tmem_acc + ((uint32_t)(q * 32) << 16) + c0, r);
-        // the previous chunk's stores must have read the staging tile before it is overwritten
+        // the previous chunk's stores must have read the staging tile before it is overwritten (a second staging tile per
+        // warp, so that a chunk need not wait for the previous chunk's store, was measured: no change)
+        const uint32_t stb = stg;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
 #pragma unroll
@@ -595,14 +600,14 @@ __device__ __forceinline__ void epilogue_tile_tma(const TcEpilogue& ep, const CU
                         v[2 * i + 1] -= __uint_as_float(w[i] & 0xffff0000u);
                     }
                 }
-                sts128u(stg + p * 2048 + lane * 64 + (((uint32_t)j ^ sw) << 4), w[0], w[1], w[2], w[3]);
+                sts128u(stb + p * 2048 + lane * 64 + (((uint32_t)j ^ sw) << 4), w[0], w[1], w[2], w[3]);
             }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         __syncwarp();
         if (lane == 0) {
 #pragma unroll
-            for (int p = 0; p < P; ++p) tma_store_3d(tmC, stg + p * 2048, col0, (int)row_base, p);
+            for (int p = 0; p < P; ++p) tma_store_3d(tmC, stb + p * 2048, col0, (int)row_base, p);
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
     }
@@ -695,16 +700,213 @@ __device__ __forceinline__ void epilogue_ln_pass1(const TcEpilogue& ep, uint32_t
     asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");      // both warps have read before the staging tiles are reused
 }
 
+// ---- ln_to_c form: C = LayerNorm(result; ln_g, ln_b) and planes = split(C) or split(LayerNorm(C; ln2_g, ln2_b)) ----
+// The raw result is needed three times (row statistics, statistics of the normalised row, the stores) and never leaves the SM:
+// pass 1 adds bias and residual in the row-major layout (coalesced residual reads through the staging tile, as above) and puts
+// the values BACK into the accumulator's TMEM columns (tcgen05.st); the second norm's statistics are then thread-local sums in
+// the TMEM layout (lane = row) and the last pass goes through the staging tile once more for coalesced stores.  L2 traffic per
+// 128 x 256 tile: residual in, C and the planes out -- the unfused epilogue plus the planes -- instead of two more round trips of C.
+__device__ __forceinline__ void tc_st32(uint32_t taddr, const uint32_t* r) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+          "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]),
+          "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]),
+          "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+        : "memory");
+}
+__device__ __forceinline__ void tc_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 template <int P>
-__device__ __forceinline__ void epilogue_ln_pass2(const TcEpilogue& ep, long row_base, long M, int chalf, int lane, const LnRowStats& st) {
+__device__ __forceinline__ void epilogue_lnc(const TcEpilogue& ep, uint32_t tmem_acc, uint32_t stg, uint32_t stg_partner, long row_base,
+                                             long M, int q, int chalf, int lane, const float4 (&bbv)[4]) {
+    constexpr int BN = 256;
+    const int cg = lane & 7, rsub = lane >> 3;
+    const long row0 = row_base + rsub;
+    const uint32_t tq = tmem_acc + ((uint32_t)(q * 32) << 16);
+    float s1[8], s2[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) s1[it] = s2[it] = 0.f;
+    // ---- pass 1: c = (acc + bias) * alpha + residual, back into TMEM; row sums ----
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c0 = chalf * (BN / 2) + cc * 32;
+        const int col = c0 + cg * 4;
+        float4 res4[8];
+        if (ep.residual) {
+            const float* rp = ep.residual + row0 * ep.ldr + col;
+#pragma unroll
+            for (int it = 0; it < 8; ++it)
+                res4[it] = (row0 + it * 4 < M) ? *reinterpret_cast<const float4*>(rp + (long)(it * 4) * ep.ldr) : make_float4(0.f, 0.f, 0.f, 0.f);
+        } else {
+#pragma unroll
+            for (int it = 0; it < 8; ++it) res4[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        uint32_t r[32];
+        tc_ld32(tq + c0, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            sts128(stg + (lane * 8 + (j ^ (lane & 7))) * 16, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        float4 bb = bbv[0];
+#pragma unroll
+        for (int i = 1; i < 4; ++i) if (cc == i) bb = bbv[i];
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            const uint32_t sa = stg + (rr * 8 + (cg ^ (rr & 7))) * 16;
+            const float4 xs = lds128(sa);
+            float4 o;
+            o.x = fmaf(xs.x + bb.x, ep.alpha, res4[it].x);
+            o.y = fmaf(xs.y + bb.y, ep.alpha, res4[it].y);
+            o.z = fmaf(xs.z + bb.z, ep.alpha, res4[it].z);
+            o.w = fmaf(xs.w + bb.w, ep.alpha, res4[it].w);
+            s1[it] += (o.x + o.y) + (o.z + o.w);
+            s2[it] += (o.x * o.x + o.y * o.y) + (o.z * o.z + o.w * o.w);
+            sts128(sa, o.x, o.y, o.z, o.w);           // the same thread read this piece: no hazard inside the pass
+        }
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 v = lds128(stg + (lane * 8 + (j ^ (lane & 7))) * 16);
+            r[4 * j] = __float_as_uint(v.x); r[4 * j + 1] = __float_as_uint(v.y);
+            r[4 * j + 2] = __float_as_uint(v.z); r[4 * j + 3] = __float_as_uint(v.w);
+        }
+        tc_st32(tq + c0, r);
+        __syncwarp();
+    }
+    tc_st_wait();
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+            s1[it] += __shfl_xor_sync(0xffffffffu, s1[it], o);
+            s2[it] += __shfl_xor_sync(0xffffffffu, s2[it], o);
+        }
+    }
+    if (cg == 0) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it)
+            asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stg + (it * 4 + rsub) * 8), "f"(s1[it]), "f"(s2[it]) : "memory");
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+    // statistics of the thread's OWN row (TMEM layout: lane = row) -- both warps of the pair compute the same numbers
+    float mean1, rstd1;
+    {
+        float a0, b0, a1, b1;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a0), "=f"(b0) : "r"(stg + lane * 8) : "memory");
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a1), "=f"(b1) : "r"(stg_partner + lane * 8) : "memory");
+        const float sa = chalf ? a1 + a0 : a0 + a1, sb = chalf ? b1 + b0 : b0 + b1;      // same order in both warps
+        mean1 = sa * (1.f / BN);
+        rstd1 = rsqrtf(fmaxf(sb * (1.f / BN) - mean1 * mean1, 0.f) + 1e-5f);
+    }
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");      // both warps have read before the staging tiles are reused
+    // ---- pass 2a: statistics of y = LayerNorm(c) for the second norm, thread-local in the TMEM layout ----
+    float mean2 = 0.f, rstd2 = 1.f;
+    const bool second = ep.ln2_g != nullptr;
+    if (second) {
+        float t1 = 0.f, t2 = 0.f;
+#pragma unroll 1
+        for (int cc = 0; cc < BN / 64; ++cc) {
+            const int c0 = chalf * (BN / 2) + cc * 32;
+            uint32_t r[32];
+            tc_ld32(tq + c0, r);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 g4 = __ldg(reinterpret_cast<const float4*>(ep.ln_g + c0) + j);
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.ln_b + c0) + j);
+                const float y0 = (__uint_as_float(r[4 * j]) - mean1) * rstd1 * g4.x + b4.x;
+                const float y1 = (__uint_as_float(r[4 * j + 1]) - mean1) * rstd1 * g4.y + b4.y;
+                const float y2 = (__uint_as_float(r[4 * j + 2]) - mean1) * rstd1 * g4.z + b4.z;
+                const float y3 = (__uint_as_float(r[4 * j + 3]) - mean1) * rstd1 * g4.w + b4.w;
+                t1 += (y0 + y1) + (y2 + y3);
+                t2 += (y0 * y0 + y1 * y1) + (y2 * y2 + y3 * y3);
+            }
+        }
+        asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(stg + lane * 8), "f"(t1), "f"(t2) : "memory");
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+        float a1, b1;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(a1), "=f"(b1) : "r"(stg_partner + lane * 8) : "memory");
+        const float sa = chalf ? a1 + t1 : t1 + a1, sb = chalf ? b1 + t2 : t2 + b1;
+        mean2 = sa * (1.f / BN);
+        rstd2 = rsqrtf(fmaxf(sb * (1.f / BN) - mean2 * mean2, 0.f) + 1e-5f);
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+    }
+    // the four per-row numbers, from the TMEM layout to the row-major layout of the stores (8 rows per lane)
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(stg + lane * 16), "f"(mean1), "f"(rstd1), "f"(mean2), "f"(rstd2) : "memory");
+    __syncwarp();
+    float4 rs[8];
+#pragma unroll
+    for (int it = 0; it < 8; ++it) rs[it] = lds128(stg + (it * 4 + rsub) * 16);
+    __syncwarp();
+    // ---- pass 2b: C = y, planes = split(y) or split(LayerNorm(y; ln2)) ----
+#pragma unroll 1
+    for (int cc = 0; cc < BN / 64; ++cc) {
+        const int c0 = chalf * (BN / 2) + cc * 32;
+        const int col = c0 + cg * 4;
+        uint32_t r[32];
+        tc_ld32(tq + c0, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+            sts128(stg + (lane * 8 + (j ^ (lane & 7))) * 16, __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                   __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        const float4 g4 = __ldg(reinterpret_cast<const float4*>(ep.ln_g + col));
+        const float4 b4 = __ldg(reinterpret_cast<const float4*>(ep.ln_b + col));
+        float4 h4 = make_float4(1.f, 1.f, 1.f, 1.f), k4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (second) {
+            h4 = __ldg(reinterpret_cast<const float4*>(ep.ln2_g + col));
+            k4 = __ldg(reinterpret_cast<const float4*>(ep.ln2_b + col));
+        }
+        float* cp = ep.c + row0 * ep.ldc + col;
+        __nv_bfloat16* pp = ep.planes + row0 * ep.ldp + col;
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+            const int rr = it * 4 + rsub;
+            const float4 x = lds128(stg + (rr * 8 + (cg ^ (rr & 7))) * 16);
+            if (row0 + it * 4 >= M) continue;
+            const float m = rs[it].x, rd = rs[it].y;
+            float v0 = (x.x - m) * rd * g4.x + b4.x, v1 = (x.y - m) * rd * g4.y + b4.y;
+            float v2 = (x.z - m) * rd * g4.z + b4.z, v3 = (x.w - m) * rd * g4.w + b4.w;
+            *reinterpret_cast<float4*>(cp + (long)(it * 4) * ep.ldc) = make_float4(v0, v1, v2, v3);
+            if (second) {
+                const float m2 = rs[it].z, rd2 = rs[it].w;
+                v0 = (v0 - m2) * rd2 * h4.x + k4.x; v1 = (v1 - m2) * rd2 * h4.y + k4.y;
+                v2 = (v2 - m2) * rd2 * h4.z + k4.z; v3 = (v3 - m2) * rd2 * h4.w + k4.w;
+            }
+            __nv_bfloat16* dst = pp + (long)(it * 4) * ep.ldp;
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+                const __nv_bfloat162 h01 = __floats2bfloat162_rn(v0, v1);
+                const __nv_bfloat162 h23 = __floats2bfloat162_rn(v2, v3);
+                uint2 w;
+                w.x = *reinterpret_cast<const uint32_t*>(&h01);
+                w.y = *reinterpret_cast<const uint32_t*>(&h23);
+                *reinterpret_cast<uint2*>(dst + p * ep.plane_stride) = w;
+                if (p + 1 < P) {
+                    v0 -= __uint_as_float(w.x << 16); v1 -= __uint_as_float(w.x & 0xffff0000u);
+                    v2 -= __uint_as_float(w.y << 16); v3 -= __uint_as_float(w.y & 0xffff0000u);
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+template <int P>
+__device__ __forceinline__ void epilogue_ln_pass2(const TcEpilogue& ep, const float* __restrict__ ln_g, const float* __restrict__ ln_b,
+                                                  long row_base, long M, int chalf, int lane, const LnRowStats& st) {
     constexpr int BN = 256;
     const int cg = lane & 7, rsub = lane >> 3;
     const long row0 = row_base + rsub;
 #pragma unroll 1
     for (int cc = 0; cc < BN / 64; ++cc) {
         const int col = chalf * (BN / 2) + cc * 32 + cg * 4;
-        const float4 g4 = make_float4(__ldg(ep.ln_g + col), __ldg(ep.ln_g + col + 1), __ldg(ep.ln_g + col + 2), __ldg(ep.ln_g + col + 3));
-        const float4 b4 = make_float4(__ldg(ep.ln_b + col), __ldg(ep.ln_b + col + 1), __ldg(ep.ln_b + col + 2), __ldg(ep.ln_b + col + 3));
+        const float4 g4 = make_float4(__ldg(ln_g + col), __ldg(ln_g + col + 1), __ldg(ln_g + col + 2), __ldg(ln_g + col + 3));
+        const float4 b4 = make_float4(__ldg(ln_b + col), __ldg(ln_b + col + 1), __ldg(ln_b + col + 2), __ldg(ln_b + col + 3));
         const float* cp = ep.c + row0 * ep.ldc + col;
         float4 x[8];
 #pragma unroll
@@ -869,13 +1071,21 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
                 epilogue_bias<BN, EM>(ep, nb, N, chalf, lane, bbv);
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
-                LnRowStats st;
-                epilogue_ln_pass1<P>(ep, tmem_base + acc * BN, stg, stg_partner, row_base, M, q, chalf, lane, bbv, st);
-                // the accumulator goes back to the MMA warp before the normalisation pass
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
-                epilogue_ln_pass2<P>(ep, row_base, M, chalf, lane, st);
+                if (ep.ln_to_c) {
+                    // normalised C: the values stay in the accumulator's columns until the last pass has read them
+                    epilogue_lnc<P>(ep, tmem_base + acc * BN, stg, stg_partner, row_base, M, q, chalf, lane, bbv);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
+                } else {
+                    LnRowStats st;
+                    epilogue_ln_pass1<P>(ep, tmem_base + acc * BN, stg, stg_partner, row_base, M, q, chalf, lane, bbv, st);
+                    // the accumulator goes back to the MMA warp before the normalisation pass
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(mapa_rank(smem_u32(&tempty[acc]), 0));
+                    epilogue_ln_pass2<P>(ep, ep.ln_g, ep.ln_b, row_base, M, chalf, lane, st);
+                }
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
                 continue;
@@ -1076,7 +1286,7 @@ bool gemm_tc_ln_fusable(long M, int N, int P) {
     return g_ln_fusion && env && N == 256 && P <= 2 && M > 2 * BM && sm_count() >= 2 && two_cta_enabled();
 }
 
-static int g_tc_variant = 1;   // 0: BK=64 / 128B swizzle, 1: BK=32 / 64B swizzle (deeper ring)
+static int g_tc_variant = 0;   // 0: BK=64 / 128B swizzle (default: 5-7 % faster over the 16-block network since the round-2 epilogues), 1: BK=32 / 64B swizzle (deeper ring)
 extern "C" void css_gemm_tc_variant(int v) { g_tc_variant = v; }
 
 int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, int K, const GemmEpilogue& e, float* C, int ldc,
@@ -1110,6 +1320,11 @@ int gemm_tc_planes(const PlaneMat& A, const PlaneMat& W, int P, long M, int N, i
     const bool train = ep.mask != nullptr || ep.ksplit > 1;
     ep.ln_g = e.ln_g;
     ep.ln_b = e.ln_b;
+    ep.ln_to_c = e.ln_g ? e.ln_to_c : 0;
+    ep.ln2_g = (e.ln_g && e.ln_to_c) ? e.ln2_g : nullptr;
+    ep.ln2_b = ep.ln2_g ? e.ln2_b : nullptr;
+    CSS_REQUIRE(!ep.ln2_g || ep.ln2_b, "gemm_tc: ln2_g without ln2_b");
+    CSS_REQUIRE(!ep.ln_to_c || (((uintptr_t)e.ln_g | (uintptr_t)e.ln_b) & 15) == 0, "gemm_tc: LayerNorm parameters must be 16-byte aligned");
     CSS_REQUIRE(!e.ln_g || (!train && gemm_tc_ln_fusable(M, N, P)), "gemm_tc: fused LayerNorm unsupported for M=%ld N=%d P=%d", M, N, P);
     if (mn) {
         if (P == 1) return v == 1 ? launch_cfg<1, 256, 32>(A, W, M, N, K, ep, st, mn, e.k_valid) : launch_cfg<1, 256, 64>(A, W, M, N, K, ep, st, mn, e.k_valid);
