@@ -42,6 +42,20 @@ __device__ __forceinline__ float2* warp_fft256(float2* a, float2* b, const float
             float2 s13 = make_float2(v1.x + v3.x, v1.y + v3.y);
             float2 d13 = make_float2(v1.y - v3.y, v3.x - v1.x);   // -i * (v1 - v3)
             const int j0 = ((j - k) << 2) + k;
+            if (pass == 0) {
+                // Ns = 1: the four outputs of a butterfly are neighbours -> two 16-byte stores, 32 contiguous bytes per lane
+                // (four 8-byte stores with a 32-byte stride between lanes were an 8-way bank conflict each; the kernel sits on
+                // the shared-memory pipe)
+                // (lanes 4-7, 12-15, ... store their halves in the opposite order, so that one store instruction covers all 32
+                // banks with eight lanes: 4 wavefronts per instruction, the minimum for 512 bytes)
+                float4* o4 = reinterpret_cast<float4*>(out + 4 * j);
+                const float4 lo = make_float4(s02.x + s13.x, s02.y + s13.y, d02.x + d13.x, d02.y + d13.y);
+                const float4 hi = make_float4(s02.x - s13.x, s02.y - s13.y, d02.x - d13.x, d02.y - d13.y);
+                const int flip = (lane >> 2) & 1;
+                o4[flip] = flip ? hi : lo;
+                o4[flip ^ 1] = flip ? lo : hi;
+                continue;
+            }
             out[j0] = make_float2(s02.x + s13.x, s02.y + s13.y);
             out[j0 + Ns] = make_float2(d02.x + d13.x, d02.y + d13.y);
             out[j0 + 2 * Ns] = make_float2(s02.x - s13.x, s02.y - s13.y);

@@ -14,7 +14,7 @@ __global__ void __launch_bounds__(IS_WARPS * 32)
 istft_place_kernel(const float2* __restrict__ Y, int T, const int4* __restrict__ plan, float* __restrict__ out,
                    long out_len) {
     __shared__ FftTables tab;
-    __shared__ float2 buf[IS_WARPS][2][256];
+    __shared__ __align__(16) float2 buf[IS_WARPS][2][256];
     fft_tables_init(&tab);
     __syncthreads();
     const int4 it = plan[blockIdx.x];

@@ -290,27 +290,32 @@ mvdr_apply_kernel(const float2* __restrict__ spec, const float2* __restrict__ ed
             wx[i] = make_float2(w.x, w.x);
             wy[i] = make_float2(w.y, w.y);
         }
-        float2 xn[MV_M];
+        // frames in groups of AP_G: the group's 7 x AP_G loads are issued together (one frame ahead was one round trip per
+        // frame: ncu long_scoreboard = 23 of 27 warp-cycles per issue)
+        constexpr int AP_G = 4;
+        for (int t0 = 0; t0 < T; t0 += AP_G) {
+            float2 x[AP_G][MV_M];
 #pragma unroll
-        for (int d = 0; d < MV_M; ++d) xn[d] = load_x(spec, edge, frames, n_chunks, b, hop_frames, d, 0, k);
-#pragma unroll 2
-        for (int t = 0; t < T; ++t) {
-            float2 x[MV_M];
+            for (int g = 0; g < AP_G; ++g) {
+                const int t = t0 + g;
 #pragma unroll
-            for (int d = 0; d < MV_M; ++d) x[d] = xn[d];
-            if (t + 1 < T) {
-#pragma unroll
-                for (int d = 0; d < MV_M; ++d) xn[d] = spec[((long)d * frames + b * hop_frames + t) * CSS_KP + k];
+                for (int d = 0; d < MV_M; ++d)
+                    x[g][d] = (t < T) ? load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k) : make_float2(0.f, 0.f);
             }
-            float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
 #pragma unroll
-            for (int d = 0; d < MV_M; ++d) {
-                P = __ffma2_rn(wx[d], x[d], P);
-                Q = __ffma2_rn(wy[d], x[d], Q);
+            for (int g = 0; g < AP_G; ++g) {
+                const int t = t0 + g;
+                if (t >= T) break;
+                float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int d = 0; d < MV_M; ++d) {
+                    P = __ffma2_rn(wx[d], x[g][d], P);
+                    Q = __ffma2_rn(wy[d], x[g][d], Q);
+                }
+                const float yr = P.x + Q.y, yi = P.y - Q.x;
+                yrow[(long)t * CSS_KP] = make_float2(yr, yi);
+                e_y += yr * yr + yi * yi;
             }
-            const float yr = P.x + Q.y, yi = P.y - Q.x;
-            yrow[(long)t * CSS_KP] = make_float2(yr, yi);
-            e_y += yr * yr + yi * yi;
         }
     } else if (k < CSS_KP) {   // zero the bin padding of Y so later stages can read whole rows
         for (int t = 0; t < T; ++t) yrow[(long)t * CSS_KP] = make_float2(0.f, 0.f);

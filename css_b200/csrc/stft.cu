@@ -11,7 +11,7 @@
 __global__ void __launch_bounds__(STFT_WARPS * 32)
 stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_frames, float2* __restrict__ spec, long spec_stride) {
     __shared__ FftTables tab;
-    __shared__ float2 buf[STFT_WARPS][2][256];
+    __shared__ __align__(16) float2 buf[STFT_WARPS][2][256];
     fft_tables_init(&tab);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -40,7 +40,7 @@ __global__ void __launch_bounds__(STFT_WARPS * 32)
 stft_edge_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_chunks, long chunk_hop,
                  float2* __restrict__ edge) {
     __shared__ FftTables tab;
-    __shared__ float2 buf[STFT_WARPS][2][256];
+    __shared__ __align__(16) float2 buf[STFT_WARPS][2][256];
     fft_tables_init(&tab);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
