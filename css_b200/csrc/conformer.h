@@ -35,7 +35,10 @@ struct ConvModuleParams {
     const float* bn_shift;  // (d) beta - running_mean * scale
     float pw2_w, pw2_b;     // pw_conv_2 scalar affine
     int ksize;
+    const float* dw_wt = nullptr;   // optional: the taps transposed to (ksize = 33, d) by conv_taps_transpose_launch -> the
+                                    // two-CTAs-per-SM shape of the kernel
 };
+int conv_taps_transpose_launch(const float* w /* (256, 33) */, float* wt /* (33, 256) */, cudaStream_t st);
 // out = x + ConvModule(x).  x, out: (N, T, 256), out must not alias x.  ksize odd, <= 33.
 int conv_module_launch(const float* x, float* out, long N, int T, int d, const ConvModuleParams& p, cudaStream_t st);
 

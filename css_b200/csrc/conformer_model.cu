@@ -32,6 +32,7 @@ struct ConformerModel {
     void* plane_mem = nullptr;
     PlaneMat embed_w{}, head_w{}, pe{};
     std::vector<BlockPlanes> bp;
+    float* taps_t = nullptr;     // [num_blocks][33][256]: depthwise taps transposed for the conv module (inside plane_mem)
 };
 constexpr int kWeightPlanes = 2;
 
@@ -41,7 +42,8 @@ static int build_weight_planes(ConformerModel* m, cudaStream_t st) {
     const size_t d = c.d_model, f = c.d_ffn, nh = (size_t)c.num_bins * c.num_out;
     auto bytes = [](size_t rows, size_t k) { return (kWeightPlanes * rows * k * 2 + 255) & ~(size_t)255; };
     const size_t dk = d / c.heads;
-    size_t total = bytes(d, c.ldin) + bytes(nh, d) + (c.pe ? bytes(c.pe_rows, dk) : 0) + c.num_blocks * (2 * bytes(f, d) + 2 * bytes(d, f) + bytes(3 * d, d) + bytes(d, d));
+    const size_t taps_bytes = ((size_t)c.num_blocks * 33 * d * 4 + 255) & ~(size_t)255;
+    size_t total = bytes(d, c.ldin) + bytes(nh, d) + (c.pe ? bytes(c.pe_rows, dk) : 0) + c.num_blocks * (2 * bytes(f, d) + 2 * bytes(d, f) + bytes(3 * d, d) + bytes(d, d)) + taps_bytes;
     cudaError_t e = cudaMalloc(&m->plane_mem, total);
     CSS_REQUIRE(e == cudaSuccess, "conformer: cannot allocate %zu B for the bf16 weight planes: %s", total, cudaGetErrorString(e));
     char* wp = static_cast<char*>(m->plane_mem);
@@ -66,7 +68,9 @@ static int build_weight_planes(ConformerModel* m, cudaStream_t st) {
         q.ff_out_w1 = mk(b.ff_out.w1, f, d);
         q.ff_out_w2 = mk(b.ff_out.w2, d, f);
     }
-    if (rc) { cudaFree(m->plane_mem); m->plane_mem = nullptr; }
+    m->taps_t = reinterpret_cast<float*>(wp);
+    for (int l = 0; l < c.num_blocks && !rc; ++l) rc = conv_taps_transpose_launch(m->blk[l].dw_w, m->taps_t + (size_t)l * 33 * d, st);
+    if (rc) { cudaFree(m->plane_mem); m->plane_mem = nullptr; m->taps_t = nullptr; }
     return rc;
 }
 
@@ -215,6 +219,7 @@ static int forward_tc(ConformerModel* m, float* feat, const SpecInput* si, long 
         if ((rc = tc_gemm(aP, q.wo, P, M, d, d, eo, x, d, nullptr, st))) return rc;
         ConvModuleParams cp = {b.conv_ln_g, b.conv_ln_b, b.pw1_w0, b.pw1_b0, b.pw1_w1, b.pw1_b1, b.dw_w, b.dw_b,
                                b.bn_scale, b.bn_shift, b.pw2_w, b.pw2_b, 33};
+        cp.dw_wt = m->taps_t + (size_t)l * 33 * d;
         if ((rc = conv_module_launch(x, a, N, T, d, cp, st))) return rc;
         { float* t = x; x = a; a = t; }
         // block output LN: fp32 for the residual stream, and with it the planes the next GEMM reads -- the next block's FFN-in

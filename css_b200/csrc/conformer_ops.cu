@@ -1,6 +1,7 @@
 // Warp-level kernels of the Conformer block: LayerNorm, relative-position MHSA, conv module,
 // and the mask-head layout transform.  (css/models/conformer.py:188-303, css/executor/separator.py:100-104)
 #include "common.cuh"
+#include <cstdlib>
 #include "conformer.h"
 #include "gemm.h"
 #include <cuda_bf16.h>
@@ -273,6 +274,7 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 #define CM_THREADS 512
 #define CM_MAX_ROWS 192          // (tile + 2*halo) rows of 1 KB each + the tap table must fit in shared memory
 #define CM_WPITCH (CM_D + 1)     // tap table in shared memory: [tap][channel], pitch 257 floats
+#define CM_SPLIT_ROWS 112        // two-CTAs-per-SM shape: 112 KB per CTA
 #define CM_OUT 8                 // outputs per register pass of the depthwise filter
 
 // One CTA per (sequence, time tile); a 150-frame chunk is one tile, so nothing is recomputed.
@@ -284,9 +286,15 @@ extern "C" int css_relpos_attention(const float* qkv, const float* pe, int pe_ro
 // which would otherwise cost a whole extra wave -- is cut into `tail_tiles` short tiles spread over the idle SMs.
 struct ConvPlan { int n_full, full_tiles, full_len, tail_tiles, tail_len, smem_rows; };
 
-__global__ void __launch_bounds__(CM_THREADS, 1)
+// Two shapes: THREADS = 512, one CTA per SM, a whole 150-frame chunk per tile and the taps transposed into shared memory by the
+// kernel; THREADS = 256, TWO CTAs per SM on half-chunk tiles (75 + 32 halo rows, 107 KB) with the taps read from a table the
+// caller has transposed once (ConvModuleParams::dw_wt) -- one CTA's LayerNorm phase (loads) then runs under the other's filter
+// phase (FMA pipe), at the price of normalising the 32 halo rows twice.
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS, THREADS == 512 ? 1 : 2)
 conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, ConvPlan pl, ConvModuleParams p) {
-    extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D], then the tap table [CM_TAPS][CM_WPITCH]
+    constexpr bool WSMEM = THREADS == 512;
+    extern __shared__ float U[];   // [(tile + 2*CM_HALO)][CM_D], then (WSMEM) the tap table [CM_TAPS][CM_WPITCH]
     long n;
     int t0, tile;
     {
@@ -308,14 +316,16 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
     // The depthwise taps (d, 33) go to shared memory transposed, by 4-byte async copies that run under phase 1: read in
     // place by thread = channel they were 66 loads with a 132-byte stride between lanes, a fifth of the kernel's stall samples.
     float* Wt = U + (size_t)pl.smem_rows * CM_D;
-    for (int i = threadIdx.x; i < CM_D * CM_TAPS; i += CM_THREADS) {
-        const int ch = i / CM_TAPS, k = i - ch * CM_TAPS;
-        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Wt + k * CM_WPITCH + ch);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.dw_w + i) : "memory");
+    if (WSMEM) {
+        for (int i = threadIdx.x; i < CM_D * CM_TAPS; i += THREADS) {
+            const int ch = i / CM_TAPS, k = i - ch * CM_TAPS;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(Wt + k * CM_WPITCH + ch);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(p.dw_w + i) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
     // four rows per pass: their eight loads are in flight together (the phase is latency-bound otherwise)
-    constexpr int NW = CM_THREADS / 32, RB = 4;
+    constexpr int NW = THREADS / 32, RB = 4;
     for (int rb = warp; rb < rows; rb += NW * RB) {
         float4 v[RB][2];
 #pragma unroll
@@ -367,16 +377,22 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
             }
         }
     }
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();
     const int c = 2 * (threadIdx.x & (CM_D / 2 - 1)), part = threadIdx.x >> 7;     // channels c, c+1
+    constexpr int NPART = THREADS / 128;
     float2 w[CM_TAPS];
+    if (WSMEM) asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
+    if (WSMEM) {
 #pragma unroll
-    for (int k = 0; k < CM_TAPS; ++k) w[k] = make_float2(Wt[k * CM_WPITCH + c], Wt[k * CM_WPITCH + c + 1]);
+        for (int k = 0; k < CM_TAPS; ++k) w[k] = make_float2(Wt[k * CM_WPITCH + c], Wt[k * CM_WPITCH + c + 1]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < CM_TAPS; ++k) w[k] = __ldg(reinterpret_cast<const float2*>(p.dw_wt + k * CM_D + c));
+    }
     const float2 bias = *reinterpret_cast<const float2*>(p.dw_b + c);
     const float2 sc = *reinterpret_cast<const float2*>(p.bn_scale + c), sh = *reinterpret_cast<const float2*>(p.bn_shift + c);
     float* os = out + n * (long)T * CM_D;
-    const int per = ((tile + 4 * CM_OUT - 1) / (4 * CM_OUT)) * CM_OUT;       // multiple of CM_OUT
+    const int per = ((tile + NPART * CM_OUT - 1) / (NPART * CM_OUT)) * CM_OUT;       // multiple of CM_OUT
     const int t_end = min(tile, (part + 1) * per);
     for (int tt = part * per; tt < t_end; tt += CM_OUT) {
         float2 acc[CM_OUT], xv[CM_OUT];
@@ -389,7 +405,8 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
 #pragma unroll
         for (int kk = 0; kk < CM_TAPS + CM_OUT - 1; ++kk) {
             const int r = tt + kk;
-            const float2 u = (r < rows) ? *reinterpret_cast<const float2*>(U + r * CM_D + c) : make_float2(0.f, 0.f);
+            // rows past the tile's halo (last, partial pass) exist in the allocation and feed only outputs that are not stored
+            const float2 u = *reinterpret_cast<const float2*>(U + r * CM_D + c);
 #pragma unroll
             for (int j = 0; j < CM_OUT; ++j)
                 if (kk - j >= 0 && kk - j < CM_TAPS) acc[j] = __ffma2_rn(w[kk - j], u, acc[j]);
@@ -407,24 +424,39 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
     }
 }
 
+// taps (d, 33) -> (33, d), once per model
+__global__ void conv_taps_transpose_kernel(const float* __restrict__ w, float* __restrict__ wt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < CM_D * CM_TAPS) wt[(i % CM_TAPS) * CM_D + i / CM_TAPS] = w[i];
+}
+int conv_taps_transpose_launch(const float* w, float* wt, cudaStream_t st) {
+    conv_taps_transpose_kernel<<<(CM_D * CM_TAPS + 255) / 256, 256, 0, st>>>(w, wt);
+    return css_check_launch("conv_taps_transpose");
+}
+
 int conv_module_launch(const float* x, float* out, long N, int T, int d, const ConvModuleParams& p, cudaStream_t st) {
     CSS_REQUIRE(d == CM_D, "conv_module: d=%d unsupported (kernel is built for 256)", d);
     CSS_REQUIRE(p.ksize == CM_TAPS, "conv_module: taps must be centre-padded to %d (got %d)", CM_TAPS, p.ksize);
     CSS_REQUIRE(N > 0 && T > 0 && x != out, "conv_module: bad arguments");
-    const int max_tile = CM_MAX_ROWS - 2 * CM_HALO;
+    // two CTAs per SM on half-size tiles when the caller supplies the transposed taps (A/B: CSS_B200_CONV_SPLIT=0)
+    static const bool split_env = !(getenv("CSS_B200_CONV_SPLIT") && getenv("CSS_B200_CONV_SPLIT")[0] == '0');
+    const bool split = p.dw_wt != nullptr && split_env;
+    const int max_rows = split ? CM_SPLIT_ROWS : CM_MAX_ROWS;
+    const int max_tile = max_rows - 2 * CM_HALO;
     ConvPlan pl;
     pl.full_tiles = (T + max_tile - 1) / max_tile;
     pl.full_len = (T + pl.full_tiles - 1) / pl.full_tiles;
     pl.n_full = (int)N;
-    pl.tail_tiles = 1;
+    pl.tail_tiles = pl.full_tiles;
     pl.tail_len = pl.full_len;
-    const int sms = sm_count();
-    const int rem = (int)(N % sms);
-    if (pl.full_tiles == 1 && N > sms && rem > 0 && T >= 16) {
+    const int slots = sm_count() * (split ? 2 : 1);            // CTAs per wave
+    const int seq_slots = slots / pl.full_tiles;               // sequences per wave
+    const int rem = seq_slots > 0 ? (int)(N % seq_slots) : 0;
+    if (seq_slots > 0 && N > seq_slots && rem > 0 && T >= 16) {
         // cut the sequences of the last, partial wave into short tiles (at least 8 frames) that fill the idle SMs
-        int tiles = sms / rem;
+        int tiles = slots / rem;
         if (tiles > T / 8) tiles = T / 8;
-        if (tiles > 1) {
+        if (tiles > pl.full_tiles) {
             pl.tail_len = (T + tiles - 1) / tiles;
             pl.tail_tiles = (T + pl.tail_len - 1) / pl.tail_len;
             pl.n_full = (int)N - rem;
@@ -432,15 +464,24 @@ int conv_module_launch(const float* x, float* out, long N, int T, int d, const C
     }
     const long ctas = (long)pl.n_full * pl.full_tiles + (N - pl.n_full) * pl.tail_tiles;
     CSS_REQUIRE(ctas < (1L << 31), "conv_module: too many sequences (%ld)", N);
-    pl.smem_rows = pl.full_len + 2 * CM_HALO;
-    const size_t smem = sizeof(float) * ((size_t)pl.smem_rows * CM_D + CM_TAPS * CM_WPITCH);
+    {
+        // the filter passes of a part read CM_OUT + 2 * CM_HALO rows from their first output row on: the last pass of the last
+        // part ends at per * parts + 2 * CM_HALO
+        const int parts = split ? 2 : 4;
+        const int per = ((pl.full_len + parts * CM_OUT - 1) / (parts * CM_OUT)) * CM_OUT;
+        pl.smem_rows = per * parts + 2 * CM_HALO;
+        CSS_REQUIRE(pl.smem_rows <= max_rows, "conv_module: tile of %d frames does not fit shared memory", pl.full_len);
+    }
+    const size_t smem = sizeof(float) * ((size_t)pl.smem_rows * CM_D + (split ? 0 : CM_TAPS * CM_WPITCH));
     static CssPerDevice attr_set;
     if (attr_set.first()) {
-        cudaFuncSetAttribute(conv_module_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(conv_module_kernel<512>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (CM_MAX_ROWS * CM_D + CM_TAPS * CM_WPITCH) * 4);
+        cudaFuncSetAttribute(conv_module_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, CM_SPLIT_ROWS * CM_D * 4);
     }
     css_prof_begin(2, 2.0 * (double)N * T * CM_D * 4, st);         // read x + write out
-    conv_module_kernel<<<(unsigned)ctas, CM_THREADS, smem, st>>>(x, out, T, pl, p);
+    if (split) conv_module_kernel<256><<<(unsigned)ctas, 256, smem, st>>>(x, out, T, pl, p);
+    else conv_module_kernel<512><<<(unsigned)ctas, 512, smem, st>>>(x, out, T, pl, p);
     css_prof_end(st);
     return css_check_launch("conv_module");
 }
