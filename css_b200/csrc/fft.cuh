@@ -56,10 +56,25 @@ __device__ __forceinline__ float2* warp_fft256(float2* a, float2* b, const float
                 o4[flip ^ 1] = flip ? lo : hi;
                 continue;
             }
-            out[j0] = make_float2(s02.x + s13.x, s02.y + s13.y);
-            out[j0 + Ns] = make_float2(d02.x + d13.x, d02.y + d13.y);
-            out[j0 + 2 * Ns] = make_float2(s02.x - s13.x, s02.y - s13.y);
-            out[j0 + 3 * Ns] = make_float2(d02.x - d13.x, d02.y - d13.y);
+            float2 o0 = make_float2(s02.x + s13.x, s02.y + s13.y), o1 = make_float2(d02.x + d13.x, d02.y + d13.y);
+            float2 o2 = make_float2(s02.x - s13.x, s02.y - s13.y), o3 = make_float2(d02.x - d13.x, d02.y - d13.y);
+            if (pass == 1) {
+                // Ns = 4: a group of four lanes writes 32 contiguous bytes and the eight groups of a warp sit 128 bytes apart
+                // -- the same banks for every output index.  Group g therefore stores output (s + g) mod 4 in store s (the
+                // four outputs are rotated by g in registers): four groups cover the 32 banks, 2 wavefronts instead of 8.
+                const int g = (lane >> 2) & 3;
+                if (g & 1) { const float2 t = o0; o0 = o1; o1 = o2; o2 = o3; o3 = t; }
+                if (g & 2) { float2 t = o0; o0 = o2; o2 = t; t = o1; o1 = o3; o3 = t; }
+                out[j0 + ((g) & 3) * Ns] = o0;
+                out[j0 + ((g + 1) & 3) * Ns] = o1;
+                out[j0 + ((g + 2) & 3) * Ns] = o2;
+                out[j0 + ((g + 3) & 3) * Ns] = o3;
+                continue;
+            }
+            out[j0] = o0;
+            out[j0 + Ns] = o1;
+            out[j0 + 2 * Ns] = o2;
+            out[j0 + 3 * Ns] = o3;
         }
         __syncwarp();
         float2* tmp = in; in = out; out = tmp;
