@@ -20,23 +20,41 @@ __device__ __forceinline__ void fft_tables_init(FftTables* t) {
     }
 }
 
+// The twiddles of a lane's butterflies do not depend on the frame: passes 1-3 x two butterflies x three factors, kept in
+// registers by the persistent warps (read from the shared table they were 4- to 8-way bank conflicts -- 4, 16 or 32 distinct
+// addresses on a 256 / 64 / 16-byte stride -- and about a third of the kernel's shared-memory wavefronts).
+struct FftLaneTw { float2 w[3][2][3]; };
+__device__ __forceinline__ void fft_lane_twiddles(FftLaneTw& t, const float2* __restrict__ tw, int lane) {
+#pragma unroll
+    for (int pass = 1; pass < 4; ++pass) {
+        const int Ns = 1 << (2 * pass), twstep = 128 >> (2 * pass);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int k = (lane + 32 * h) & (Ns - 1);
+#pragma unroll
+            for (int q = 0; q < 3; ++q) t.w[pass - 1][h][q] = tw[(q + 1) * k * twstep];
+        }
+    }
+}
+
 // Forward 256-point complex FFT of `a` (natural order in, natural order out).
 // Result pointer is returned (it is `a` again after 4 passes).  Warp-synchronous.
-__device__ __forceinline__ float2* warp_fft256(float2* a, float2* b, const float2* __restrict__ tw, int lane) {
+__device__ __forceinline__ float2* warp_fft256(float2* a, float2* b, const FftLaneTw& ltw, int lane) {
     float2* in = a;
     float2* out = b;
 #pragma unroll
     for (int pass = 0; pass < 4; ++pass) {
         const int Ns = 1 << (2 * pass);          // 1,4,16,64
-        const int twstep = 128 >> (2 * pass);    // 512/(4*Ns)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int j = lane + 32 * h;         // butterfly index 0..63
             const int k = j & (Ns - 1);
-            float2 v0 = in[j];
-            float2 v1 = cmul(in[j + 64], tw[k * twstep]);
-            float2 v2 = cmul(in[j + 128], tw[2 * k * twstep]);
-            float2 v3 = cmul(in[j + 192], tw[3 * k * twstep]);
+            float2 v0 = in[j], v1 = in[j + 64], v2 = in[j + 128], v3 = in[j + 192];
+            if (pass > 0) {                       // pass 0: k = 0, all three factors are 1
+                v1 = cmul(v1, ltw.w[pass > 0 ? pass - 1 : 0][h][0]);
+                v2 = cmul(v2, ltw.w[pass > 0 ? pass - 1 : 0][h][1]);
+                v3 = cmul(v3, ltw.w[pass > 0 ? pass - 1 : 0][h][2]);
+            }
             float2 s02 = make_float2(v0.x + v2.x, v0.y + v2.y);
             float2 d02 = make_float2(v0.x - v2.x, v0.y - v2.y);
             float2 s13 = make_float2(v1.x + v3.x, v1.y + v3.y);

@@ -22,6 +22,8 @@ istft_place_kernel(const float2* __restrict__ Y, int T, const int4* __restrict__
     const int j0 = it.y >> 8;                          // first output block
     const int nb = ((it.z - 1) >> 8) - j0 + 1;         // blocks touched (<= 8)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    FftLaneTw ltw;
+    fft_lane_twiddles(ltw, tab.tw, lane);
     float* fw = reinterpret_cast<float*>(buf[warp][1]);   // windowed time-domain frame of this warp
     if (warp <= nb && j0 + warp < T) {
         const float2* X = Y + (((long)it.x * 2 + spk) * T + (j0 + warp)) * CSS_KP;
@@ -34,7 +36,7 @@ istft_place_kernel(const float2* __restrict__ Y, int T, const int4* __restrict__
             a[k] = irfft_pack(xk, xc, tab.tw, k);
         }
         __syncwarp();
-        const float2* z = warp_fft256(a, buf[warp][1], tab.tw, lane);   // == a after 4 passes
+        const float2* z = warp_fft256(a, buf[warp][1], ltw, lane);   // == a after 4 passes
         __syncwarp();
 #pragma unroll
         for (int i = 0; i < 8; ++i) {

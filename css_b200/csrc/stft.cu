@@ -15,6 +15,8 @@ stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_fra
     fft_tables_init(&tab);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    FftLaneTw ltw;
+    fft_lane_twiddles(ltw, tab.tw, lane);
     const long total = n_sig * n_frames;
     for (long w = (long)blockIdx.x * STFT_WARPS + warp; w < total; w += (long)gridDim.x * STFT_WARPS) {
         const long s = w / n_frames, g = w - s * n_frames;
@@ -26,7 +28,7 @@ stft_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long n_fra
             a[n] = make_float2(__ldg(src + 2 * n) * tab.win[2 * n], __ldg(src + 2 * n + 1) * tab.win[2 * n + 1]);
         }
         __syncwarp();
-        const float2* Z = warp_fft256(a, buf[warp][1], tab.tw, lane);
+        const float2* Z = warp_fft256(a, buf[warp][1], ltw, lane);
         float2* dst = spec + (s * spec_stride + g) * CSS_KP;
         for (int k = lane; k < CSS_KP; k += 32)
             dst[k] = (k < CSS_NBINS) ? rfft_bin(Z, tab.tw, k) : make_float2(0.f, 0.f);
@@ -44,6 +46,8 @@ stft_edge_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long 
     fft_tables_init(&tab);
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    FftLaneTw ltw;
+    fft_lane_twiddles(ltw, tab.tw, lane);
     const long total = n_sig * n_chunks;
     for (long w = (long)blockIdx.x * STFT_WARPS + warp; w < total; w += (long)gridDim.x * STFT_WARPS) {
         const long s = w / n_chunks, c = w - s * n_chunks;
@@ -58,7 +62,7 @@ stft_edge_kernel(const float* __restrict__ x, long n_sig, long sig_stride, long 
             a[n] = make_float2(__ldg(src + i0) * tab.win[p0], __ldg(src + i1) * tab.win[p1]);
         }
         __syncwarp();
-        const float2* Z = warp_fft256(a, buf[warp][1], tab.tw, lane);
+        const float2* Z = warp_fft256(a, buf[warp][1], ltw, lane);
         float2* dst = edge + (s * n_chunks + c) * CSS_KP;
         for (int k = lane; k < CSS_KP; k += 32)
             dst[k] = (k < CSS_NBINS) ? rfft_bin(Z, tab.tw, k) : make_float2(0.f, 0.f);
