@@ -36,7 +36,11 @@ __device__ __forceinline__ float pymod360(float x) {
     return (r < 0.f) ? r + 360.f : r;
 }
 
-__global__ void __launch_bounds__(256, 2)      // two CTAs per SM: the 104 KB steering table of the usual band fits twice
+// PITCH: row pitch of the steering table in shared memory -- 64 when the band has at most 64 bins (the usual 80-2000 Hz band: 61), so
+// that the 210 table reads of a point are one base register + immediates (with the runtime pitch nf every read carried its own
+// address arithmetic: an eighth of the kernel's instructions); 0: pitch = nf.
+template <int PITCH>
+__global__ void __launch_bounds__(256, 2)      // two CTAs per SM: the 105 KB steering table of the usual band fits twice
 doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chunk, int T,
                  const float2* __restrict__ svT, const float* __restrict__ angles, int lo, int nf, float thresh,
                  float binarize, float* masks, int C, float* __restrict__ like_out, int* __restrict__ idx_out) {
@@ -45,7 +49,11 @@ doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chu
     __shared__ double tot[2 * DOA_A];
     __shared__ int hit_s;
     const long b = blockIdx.x;
-    for (int i = threadIdx.x; i < DOA_A * DOA_M * nf; i += blockDim.x) sv[i] = svT[i];
+    const int pitch = PITCH ? PITCH : nf;
+    for (int i = threadIdx.x; i < DOA_A * DOA_M * nf; i += blockDim.x) {
+        const int row = i / nf;
+        sv[row * pitch + (i - row * nf)] = svT[i];
+    }
     __syncthreads();
     float acc[2][DOA_A];
 #pragma unroll
@@ -72,12 +80,16 @@ doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chu
             float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
 #pragma unroll
             for (int m = 0; m < DOA_M; ++m) {
-                const float2 sm = sv[(a * DOA_M + m) * nf + fi];
+                const float2 sm = sv[(a * DOA_M + m) * pitch + fi];
                 P = __ffma2_rn(xx[m], sm, P);
                 Q = __ffma2_rn(xy[m], sm, Q);
             }
             const float re = P.x + Q.y, im = P.y - Q.x;
-            const float l = -sqrtf(xpow - (re * re + im * im));   // NaN when the radicand rounds < 0 (Q7)
+            // NaN when the radicand rounds < 0 (Q7): sqrt.approx keeps that, and its 1-2 ulp are below what the order of the
+            // 9,150-term sums already differs from torch's by (IEEE sqrtf was six more instructions per angle and point)
+            float l;
+            asm("sqrt.approx.f32 %0, %1;" : "=f"(l) : "f"(xpow - (re * re + im * im)));
+            l = -l;
             acc[0][a] += b0 * l;
             acc[1][a] += b1 * l;
         }
@@ -127,16 +139,21 @@ extern "C" int css_doa_merge(const void* spec, long stride_d, long stride_chunk,
     const int nf = hi - lo;
     CSS_REQUIRE(n_chunks > 0 && T > 0 && C >= 2, "css_doa_merge: bad shape");
     CSS_REQUIRE(lo >= 0 && hi <= CSS_NBINS && nf > 0, "css_doa_merge: bad band [%d,%d)", lo, hi);
-    const size_t smem = sizeof(float2) * DOA_A * DOA_M * nf;
+    const int pitch = nf <= 64 ? 64 : nf;
+    const size_t smem = sizeof(float2) * DOA_A * DOA_M * pitch;
     CSS_REQUIRE(smem <= 200 * 1024, "css_doa_merge: band of %d bins needs too much shared memory", nf);
     static CssPerDevice attr_set;
     if (attr_set.first()) {
-        cudaFuncSetAttribute(doa_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(doa_merge_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(doa_merge_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     }
     CssProfScope prof(7, (double)n_chunks * T * (CSS_NBINS * C * 4.0 + 7.0 * (hi - lo) * 8.0), st);
-    doa_merge_kernel<<<(unsigned)n_chunks, 256, smem, st>>>((const float2*)spec, stride_d, stride_chunk, T,
-                                                            (const float2*)svT, angles, lo, nf, thresh, 0.5f, masks, C,
-                                                            like, idx);
+    if (pitch == 64)
+        doa_merge_kernel<64><<<(unsigned)n_chunks, 256, smem, st>>>((const float2*)spec, stride_d, stride_chunk, T, (const float2*)svT,
+                                                                    angles, lo, nf, thresh, 0.5f, masks, C, like, idx);
+    else
+        doa_merge_kernel<0><<<(unsigned)n_chunks, 256, smem, st>>>((const float2*)spec, stride_d, stride_chunk, T, (const float2*)svT,
+                                                                   angles, lo, nf, thresh, 0.5f, masks, C, like, idx);
     return css_check_launch("css_doa_merge");
 }
 
