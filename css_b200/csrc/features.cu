@@ -44,7 +44,10 @@ __device__ __forceinline__ float ipd_atan2(float y, float x) {
     const float ax = fabsf(x), ay = fabsf(y);
     float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
     if (mx < 1e-20f) { mx *= 1.8446744e19f; mn *= 1.8446744e19f; }      // keep the reciprocal in range
-    const float a = mx > 0.f ? __fdividef(mn, mx) : 0.f;
+    // mx is in [1e-20, ~2] here: one MUFU.RCP (div.approx adds a range-scaling sequence for denominators beyond 2^126)
+    float rmx;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rmx) : "f"(mx));
+    const float a = mx > 0.f ? mn * rmx : 0.f;
     const float s = a * a;
     float r = 0.0028340641874819994f;
     r = fmaf(r, s, -0.016005029901862144f);
