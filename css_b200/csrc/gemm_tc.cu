@@ -1151,6 +1151,21 @@ static int make_map(CUtensorMap* map, const void* base, long rows, int K, int ld
     return 0;
 }
 
+int css_make_f32_map3(CUtensorMap* map, const void* base, const unsigned long long dims[3], const unsigned long long strides[2],
+                      const unsigned box[3]) {
+    EncodeTiledFn fn = encode_fn();
+    CSS_REQUIRE(fn, "cuTensorMapEncodeTiled is not available from the driver");
+    CSS_REQUIRE(((uintptr_t)base & 15) == 0 && strides[0] % 16 == 0 && strides[1] % 16 == 0, "tensor map: base / strides must be 16-byte aligned");
+    cuuint64_t d[3] = {dims[0], dims[1], dims[2]};
+    cuuint64_t st[2] = {strides[0], strides[1]};
+    cuuint32_t bx[3] = {box[0], box[1], box[2]};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(base), d, st, bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CSS_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (fp32, 3-D) failed (%d)", (int)r);
+    return 0;
+}
+
 // shared with the tcgen05 attention kernel (attention_umma.cu)
 int css_make_plane_map(CUtensorMap* map, const void* base, long rows, int K, int ld, long plane_stride, int planes, int box_rows,
                        int BK) {

@@ -40,26 +40,40 @@ __device__ __forceinline__ void scm_row(const float2 (&x)[MV_M], const float (&w
     }
 }
 
-// Frames reach the four warps through a ring of SC_ST stages of SC_F frames in shared memory, filled by 16-byte async copies
-// (7 channels x 32 bins complex + 3 masks x 32 bins per frame = 2,176 B): the first version had every warp load its own
+// Frames reach the four warps through a ring of SC_ST stages of SC_F frames in shared memory, filled by the bulk-copy engine
+// (cp.async.bulk, one copy per row piece, completion on the stage's mbarrier; 7 channels x 32 bins complex + 3 masks x 32 bins per
+// frame = 2,176 B): the first version had every warp load its own
 // operands one frame ahead and spent its time waiting for one round trip per frame (15 % of the DRAM rate at 20 warps per SM);
 // now SC_ST - 1 stages are in flight per CTA and the four warps share one copy of the frame.
 #define SC_F 5
 #define SC_ST 4
 #define SC_XF (MV_M * MV_BINS)            // float2 per frame
 #define SC_WF (3 * MV_BINS)               // float per frame
-#define SC_PIECES (SC_XF / 2 + SC_WF / 4) // 16-byte pieces per frame: 112 + 24
 
-__device__ __forceinline__ void sc_copy16(void* dst, const void* src, bool valid) {
-    const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
-    const int n = valid ? 16 : 0;                         // 0 source bytes: the 16 bytes are zero-filled
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(d), "l"(src), "r"(n) : "memory");
+__device__ __forceinline__ uint32_t sc_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sc_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(sc_smem(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void sc_mbar_expect(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(sc_smem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void sc_mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.b32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(sc_smem(bar)), "r"(parity) : "memory");
+    } while (!done);
+}
+// one row piece (a multiple of 16 bytes) global -> shared by the bulk-copy engine, completion counted on the stage's mbarrier
+__device__ __forceinline__ void sc_bulk(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(sc_smem(dst)), "l"(src), "r"(bytes), "r"(sc_smem(bar)) : "memory");
 }
 
 template <int G>
 __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
                                           long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
-                                          float* __restrict__ scm, float* __restrict__ energy, float2* Xs, float* Ws) {
+                                          float* __restrict__ scm, float* __restrict__ energy, float2* Xs, float* Ws, uint64_t* full) {
     constexpr int R0 = G, R1 = (G == 0) ? -1 : MV_M - G;
     const long b = blockIdx.y;
     const int lane = threadIdx.x, tid = threadIdx.y * MV_BINS + threadIdx.x;
@@ -75,36 +89,43 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
     const long mstride = L * CSS_KP, cstride = frames * CSS_KP;
     const int kmax = CSS_KP - k0;                                            // elements of a row from k0 on (8 in the last tile)
 
+    // Stage st = frames [st * SC_F, +SC_F): 7 spectrum row pieces + 3 mask row pieces per frame, one bulk copy each, issued by
+    // the lanes of warp 0 (a first version copied 16-byte pieces with cp.async from all threads: the piece arithmetic was 40 % of
+    // the kernel's instructions).
+    const uint32_t xbytes = (uint32_t)min(MV_BINS, kmax) * 8u, wbytes = (uint32_t)min(MV_BINS, kmax) * 4u;
     auto load_stage = [&](int st) {
-        const int f0 = st * SC_F, buf = st % SC_ST;
-        for (int i = tid; i < SC_F * SC_PIECES; i += 4 * MV_BINS) {
-            const int f = i / SC_PIECES, r = i - f * SC_PIECES, t = f0 + f;
-            if (r < SC_XF / 2) {
-                const int d = r / (MV_BINS / 2), j = 2 * (r - d * (MV_BINS / 2));
-                const bool ok = t < T && j < kmax;
-                const float2* src = (t == 0) ? edge + ((long)d * n_chunks + b) * CSS_KP + k0 + j : sp + d * cstride + (long)t * CSS_KP + j;
-                sc_copy16(Xs + (buf * SC_F + f) * SC_XF + d * MV_BINS + j, ok ? src : spec, ok);
+        const int f0 = st * SC_F, buf = st % SC_ST, nf = min(SC_F, T - f0);
+        if (lane == 0) sc_mbar_expect(&full[buf], (uint32_t)nf * (MV_M * xbytes + 3 * wbytes));
+        __syncwarp();
+        for (int i = lane; i < nf * (MV_M + 3); i += 32) {
+            const int f = i / (MV_M + 3), r = i - f * (MV_M + 3), t = f0 + f;
+            if (r < MV_M) {
+                const float2* src = (t == 0) ? edge + ((long)r * n_chunks + b) * CSS_KP + k0 : sp + r * cstride + (long)t * CSS_KP;
+                sc_bulk(Xs + (buf * SC_F + f) * SC_XF + r * MV_BINS, src, xbytes, &full[buf]);
             } else {
-                const int q = r - SC_XF / 2, m = q / (MV_BINS / 4), j = 4 * (q - m * (MV_BINS / 4));
-                const bool ok = t < T && j < kmax;
-                sc_copy16(Ws + (buf * SC_F + f) * SC_WF + m * MV_BINS + j, ok ? (const void*)(mrow + m * mstride + (long)t * CSS_KP + j) : (const void*)spec, ok);
+                const int m = r - MV_M;
+                sc_bulk(Ws + (buf * SC_F + f) * SC_WF + m * MV_BINS, mrow + m * mstride + (long)t * CSS_KP, wbytes, &full[buf]);
             }
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     const int n_st = (T + SC_F - 1) / SC_F;
+    if (tid == 0) {
 #pragma unroll
-    for (int s0 = 0; s0 < SC_ST - 1; ++s0) {
-        if (s0 < n_st) load_stage(s0);
-        else asm volatile("cp.async.commit_group;" ::: "memory");
+        for (int i = 0; i < SC_ST; ++i) sc_mbar_init(&full[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (G == 0) {
+#pragma unroll
+        for (int s0 = 0; s0 < SC_ST - 1; ++s0)
+            if (s0 < n_st) load_stage(s0);
     }
     for (int st = 0; st < n_st; ++st) {
-        asm volatile("cp.async.wait_group %0;" ::"n"(SC_ST - 2) : "memory");
-        __syncthreads();                     // stage st has landed for everyone; stage st - 1 has been consumed by everyone
-        if (st + SC_ST - 1 < n_st) load_stage(st + SC_ST - 1);
-        else asm volatile("cp.async.commit_group;" ::: "memory");
         const int buf = st % SC_ST, nf = min(SC_F, T - st * SC_F);
+        sc_mbar_wait(&full[buf], (uint32_t)(st / SC_ST) & 1u);
+        __syncthreads();                     // stage st - 1 has been consumed by everyone: its buffer takes stage st + SC_ST - 1
+        if (G == 0 && st + SC_ST - 1 < n_st) load_stage(st + SC_ST - 1);
         for (int f = 0; f < nf; ++f) {
             float2 x[MV_M];
             float w[3];
@@ -162,11 +183,12 @@ mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge
                 float* __restrict__ energy) {
     __shared__ __align__(16) float2 Xs[SC_ST * SC_F * SC_XF];
     __shared__ __align__(16) float Ws[SC_ST * SC_F * SC_WF];
+    __shared__ __align__(8) uint64_t full[SC_ST];
     switch (threadIdx.y) {      // warp-uniform; every arm runs the same copy / barrier sequence
-        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
-        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
-        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
-        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws); break;
+        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
     }
 }
 
