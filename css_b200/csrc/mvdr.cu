@@ -9,6 +9,7 @@
 // stitched: [3][L][KP] (speech0, speech1, noise), chunk b uses frames [b*hop_frames, +T).
 // Y: [B][2][T][KP] complex64.
 #include "common.cuh"
+#include "tma_map.h"
 
 #define MV_M 7
 #define MV_TRI 28          // upper triangle incl. diagonal
@@ -70,8 +71,20 @@ __device__ __forceinline__ void sc_bulk(void* dst, const void* src, uint32_t byt
                  ::"r"(sc_smem(dst)), "l"(src), "r"(bytes), "r"(sc_smem(bar)) : "memory");
 }
 
+// one box of a 3-D tensor map global -> shared (TMA), completion counted on the stage's mbarrier
+__device__ __forceinline__ void sc_tma3(void* dst, const CUtensorMap* map, int c0, int c1, int c2, uint64_t* bar) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(sc_smem(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(sc_smem(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+// Tensor maps of the covariance kernel (fp32 views; a complex bin = two floats):
+//   x5 / x1: spectrum (2 KP, channels, frames), boxes of 32 bins x 7 channels x SC_F frames / x 1 frame
+//   e1:      chunk-start edge frames (2 KP, channels, chunks), box 32 bins x 7 channels x 1
+//   w5:      stitched masks (KP, 3, L), box 32 bins x 3 masks x SC_F frames
+// A box lands in shared memory frame-major, [frame][channel or mask][bin]: the layout of the stage buffers.
+struct ScmMaps { CUtensorMap x5, x1, e1, w5; };
+
 template <int G>
-__device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
+__device__ __forceinline__ void scm_group(const ScmMaps& maps, const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
                                           long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
                                           float* __restrict__ scm, float* __restrict__ energy, float2* Xs, float* Ws, uint64_t* full) {
     constexpr int R0 = G, R1 = (G == 0) ? -1 : MV_M - G;
@@ -84,29 +97,28 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
 #pragma unroll
         for (int i = 0; i < 7; ++i) acc[m][i] = make_float2(0.f, 0.f);
     float msum[3] = {0.f, 0.f, 0.f}, e_mask[2] = {0.f, 0.f};
-    const float* mrow = stitched + (b * hop_frames) * (long)CSS_KP + k0;
-    const float2* sp = spec + (b * hop_frames - 1) * (long)CSS_KP + k0;      // frame t >= 1 of the chunk at sp + t * KP
-    const long mstride = L * CSS_KP, cstride = frames * CSS_KP;
-    const int kmax = CSS_KP - k0;                                            // elements of a row from k0 on (8 in the last tile)
 
-    // Stage st = frames [st * SC_F, +SC_F): 7 spectrum row pieces + 3 mask row pieces per frame, one bulk copy each, issued by
-    // the lanes of warp 0 (a first version copied 16-byte pieces with cp.async from all threads: the piece arithmetic was 40 % of
-    // the kernel's instructions).
-    const uint32_t xbytes = (uint32_t)min(MV_BINS, kmax) * 8u, wbytes = (uint32_t)min(MV_BINS, kmax) * 4u;
+    // Stage st = frames [st * SC_F, +SC_F) of the chunk.  Frame t >= 1 is global frame b * hop + t - 1, frame 0 the reflect-padded
+    // edge frame of the chunk, so stage 0 is one edge box + SC_F - 1 single-frame boxes and every other stage ONE spectrum box;
+    // the masks are one box per stage.  (Earlier forms: 16-byte cp.async pieces from all threads -- their address arithmetic was
+    // 40 % of the kernel's instructions; then one bulk copy per 256-byte row piece, 50 per stage -- the copy engine then took
+    // ~20 cycles per small copy and the warps waited at the stage barrier.)  Bins past the row (last bin tile) and frames past the
+    // spectrogram are out-of-bounds box elements: they read as zero and are never used.
+    constexpr uint32_t kStageBytes = SC_F * (SC_XF * 8 + SC_WF * 4);
     auto load_stage = [&](int st) {
-        const int f0 = st * SC_F, buf = st % SC_ST, nf = min(SC_F, T - f0);
-        if (lane == 0) sc_mbar_expect(&full[buf], (uint32_t)nf * (MV_M * xbytes + 3 * wbytes));
-        __syncwarp();
-        for (int i = lane; i < nf * (MV_M + 3); i += 32) {
-            const int f = i / (MV_M + 3), r = i - f * (MV_M + 3), t = f0 + f;
-            if (r < MV_M) {
-                const float2* src = (t == 0) ? edge + ((long)r * n_chunks + b) * CSS_KP + k0 : sp + r * cstride + (long)t * CSS_KP;
-                sc_bulk(Xs + (buf * SC_F + f) * SC_XF + r * MV_BINS, src, xbytes, &full[buf]);
-            } else {
-                const int m = r - MV_M;
-                sc_bulk(Ws + (buf * SC_F + f) * SC_WF + m * MV_BINS, mrow + m * mstride + (long)t * CSS_KP, wbytes, &full[buf]);
-            }
+        if (lane != 0) return;
+        const int buf = st % SC_ST;
+        const int g0 = (int)(b * hop_frames) + st * SC_F;              // global mask frame of the stage's first frame
+        sc_mbar_expect(&full[buf], kStageBytes);
+        float2* xd = Xs + (buf * SC_F) * SC_XF;
+        if (st == 0) {
+            sc_tma3(xd, &maps.e1, 2 * k0, 0, (int)b, &full[buf]);
+#pragma unroll
+            for (int f = 1; f < SC_F; ++f) sc_tma3(xd + f * SC_XF, &maps.x1, 2 * k0, 0, g0 + f - 1, &full[buf]);
+        } else {
+            sc_tma3(xd, &maps.x5, 2 * k0, 0, g0 - 1, &full[buf]);
         }
+        sc_tma3(Ws + (buf * SC_F) * SC_WF, &maps.w5, k0, 0, g0, &full[buf]);
     };
 
     const int n_st = (T + SC_F - 1) / SC_F;
@@ -178,17 +190,17 @@ __device__ __forceinline__ void scm_group(const float2* __restrict__ spec, const
 }
 
 __global__ void __launch_bounds__(128)
-mvdr_scm_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
+mvdr_scm_kernel(const __grid_constant__ ScmMaps maps, const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
                 const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
                 float* __restrict__ energy) {
-    __shared__ __align__(16) float2 Xs[SC_ST * SC_F * SC_XF];
-    __shared__ __align__(16) float Ws[SC_ST * SC_F * SC_WF];
+    __shared__ __align__(128) float2 Xs[SC_ST * SC_F * SC_XF];
+    __shared__ __align__(128) float Ws[SC_ST * SC_F * SC_WF];
     __shared__ __align__(8) uint64_t full[SC_ST];
     switch (threadIdx.y) {      // warp-uniform; every arm runs the same copy / barrier sequence
-        case 0: scm_group<0>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        case 1: scm_group<1>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        case 2: scm_group<2>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        default: scm_group<3>(spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 0: scm_group<0>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 1: scm_group<1>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 2: scm_group<2>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        default: scm_group<3>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
     }
 }
 
@@ -361,8 +373,22 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
     float2* wv = reinterpret_cast<float2*>(static_cast<char*>(scratch) + scm_bytes);
     const unsigned nblk = (CSS_NBINS + MV_BINS - 1) / MV_BINS;
     CssProfScope prof(9, (double)n_chunks * T * CSS_NBINS * (7 * 8.0 + 3 * 4.0 + 2 * 8.0), st);
+    ScmMaps maps;
+    {
+        int rc0;
+        const unsigned long long KP2 = 2ULL * CSS_KP;
+        const unsigned long long dx[3] = {KP2, MV_M, (unsigned long long)frames}, sx[2] = {(unsigned long long)frames * CSS_KP * 8ULL, CSS_KP * 8ULL};
+        const unsigned long long de[3] = {KP2, MV_M, (unsigned long long)n_chunks}, se[2] = {(unsigned long long)n_chunks * CSS_KP * 8ULL, CSS_KP * 8ULL};
+        const unsigned long long dw[3] = {CSS_KP, 3, (unsigned long long)L}, sw[2] = {(unsigned long long)L * CSS_KP * 4ULL, CSS_KP * 4ULL};
+        const unsigned b5[3] = {2 * MV_BINS, MV_M, SC_F}, b1[3] = {2 * MV_BINS, MV_M, 1}, bw[3] = {MV_BINS, 3, SC_F};
+        if ((rc0 = css_make_f32_map3(&maps.x5, spec, dx, sx, b5)) || (rc0 = css_make_f32_map3(&maps.x1, spec, dx, sx, b1)) ||
+            (rc0 = css_make_f32_map3(&maps.e1, edge, de, se, b1)) || (rc0 = css_make_f32_map3(&maps.w5, stitched, dw, sw, bw))) {
+            cudaFreeAsync(scratch, st);
+            return rc0;
+        }
+    }
     mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 4), 0, st>>>(
-        (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
+        maps, (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
     int rc = css_check_launch("css_mvdr(scm)");
     if (!rc) {
         mvdr_solve_kernel<<<dim3(nblk, (unsigned)n_chunks, 2), 256, 0, st>>>(scm, wv);
