@@ -305,54 +305,74 @@ mvdr_solve_kernel(const float* __restrict__ scm, float2* __restrict__ wout /* [B
 }
 
 // ---- kernel 3: y[t] = sum_m conj(w_m) x_m[t];  grid (9, B); block (32 bins, 2 speakers); energy slot 0 = sum |y|^2
+// The frames arrive through the same TMA ring as in the covariance kernel (one box of 32 bins x 7 channels x 5 frames per stage,
+// shared by the two speakers' warps): with every thread loading its own operands the kernel waited for one round trip per
+// group of frames (ncu: long_scoreboard 23 of 27 warp-cycles per issue).
 __global__ void __launch_bounds__(64)
-mvdr_apply_kernel(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
-                  int hop_frames, int T, const float2* __restrict__ wv, float2* __restrict__ Y, float* __restrict__ energy) {
+mvdr_apply_kernel(const __grid_constant__ ScmMaps maps, int hop_frames, int T, const float2* __restrict__ wv, float2* __restrict__ Y,
+                  float* __restrict__ energy) {
+    __shared__ __align__(128) float2 Xs[SC_ST * SC_F * SC_XF];
+    __shared__ __align__(8) uint64_t full[SC_ST];
     const long b = blockIdx.y;
-    const int lane = threadIdx.x, mk = threadIdx.y;
-    const int k = blockIdx.x * MV_BINS + lane;
+    const int lane = threadIdx.x, mk = threadIdx.y, tid = mk * MV_BINS + lane;
+    const int k0 = blockIdx.x * MV_BINS, k = k0 + lane;
     const bool act = k < CSS_NBINS;
     float e_y = 0.f;
     float2* yrow = Y + ((b * 2 + mk) * (long)T) * CSS_KP + k;
-    if (act) {
-        // y = sum_d conj(w_d) x_d = (P.x + Q.y, P.y - Q.x) with P = sum_d wr_d * x_d, Q = sum_d wi_d * x_d: two packed fp32
-        // FMAs (FFMA2) per channel; the next frame's seven channels are requested before the current frame is consumed
-        float2 wx[MV_M], wy[MV_M];
+    // y = sum_d conj(w_d) x_d = (P.x + Q.y, P.y - Q.x) with P = sum_d wr_d * x_d, Q = sum_d wi_d * x_d: two packed fp32
+    // FMAs (FFMA2) per channel
+    float2 wx[MV_M], wy[MV_M];
 #pragma unroll
-        for (int i = 0; i < MV_M; ++i) {
-            const float2 w = wv[((b * 2 + mk) * MV_M + i) * (long)CSS_KP + k];
-            wx[i] = make_float2(w.x, w.x);
-            wy[i] = make_float2(w.y, w.y);
+    for (int i = 0; i < MV_M; ++i) {
+        const float2 w = act ? wv[((b * 2 + mk) * MV_M + i) * (long)CSS_KP + k] : make_float2(0.f, 0.f);
+        wx[i] = make_float2(w.x, w.x);
+        wy[i] = make_float2(w.y, w.y);
+    }
+    constexpr uint32_t kStageBytes = SC_F * SC_XF * 8;
+    auto load_stage = [&](int st) {
+        const int buf = st % SC_ST;
+        const int g0 = (int)(b * hop_frames) + st * SC_F;
+        sc_mbar_expect(&full[buf], kStageBytes);
+        float2* xd = Xs + (buf * SC_F) * SC_XF;
+        if (st == 0) {
+            sc_tma3(xd, &maps.e1, 2 * k0, 0, (int)b, &full[buf]);
+#pragma unroll
+            for (int f = 1; f < SC_F; ++f) sc_tma3(xd + f * SC_XF, &maps.x1, 2 * k0, 0, g0 + f - 1, &full[buf]);
+        } else {
+            sc_tma3(xd, &maps.x5, 2 * k0, 0, g0 - 1, &full[buf]);
         }
-        // frames in groups of AP_G: the group's 7 x AP_G loads are issued together (one frame ahead was one round trip per
-        // frame: ncu long_scoreboard = 23 of 27 warp-cycles per issue)
-        constexpr int AP_G = 4;
-        for (int t0 = 0; t0 < T; t0 += AP_G) {
-            float2 x[AP_G][MV_M];
+    };
+    const int n_st = (T + SC_F - 1) / SC_F;
+    if (tid == 0) {
 #pragma unroll
-            for (int g = 0; g < AP_G; ++g) {
-                const int t = t0 + g;
+        for (int i = 0; i < SC_ST; ++i) sc_mbar_init(&full[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (tid == 0) {
 #pragma unroll
-                for (int d = 0; d < MV_M; ++d)
-                    x[g][d] = (t < T) ? load_x(spec, edge, frames, n_chunks, b, hop_frames, d, t, k) : make_float2(0.f, 0.f);
+        for (int s0 = 0; s0 < SC_ST - 1; ++s0)
+            if (s0 < n_st) load_stage(s0);
+    }
+    for (int st = 0; st < n_st; ++st) {
+        const int buf = st % SC_ST, nf = min(SC_F, T - st * SC_F);
+        sc_mbar_wait(&full[buf], (uint32_t)(st / SC_ST) & 1u);
+        __syncthreads();                     // stage st - 1 has been consumed by both warps
+        if (tid == 0 && st + SC_ST - 1 < n_st) load_stage(st + SC_ST - 1);
+        for (int f = 0; f < nf; ++f) {
+            const int t = st * SC_F + f;
+            const float2* xf = Xs + (buf * SC_F + f) * SC_XF + lane;
+            float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int d = 0; d < MV_M; ++d) {
+                const float2 x = xf[d * MV_BINS];
+                P = __ffma2_rn(wx[d], x, P);
+                Q = __ffma2_rn(wy[d], x, Q);
             }
-#pragma unroll
-            for (int g = 0; g < AP_G; ++g) {
-                const int t = t0 + g;
-                if (t >= T) break;
-                float2 P = make_float2(0.f, 0.f), Q = make_float2(0.f, 0.f);
-#pragma unroll
-                for (int d = 0; d < MV_M; ++d) {
-                    P = __ffma2_rn(wx[d], x[g][d], P);
-                    Q = __ffma2_rn(wy[d], x[g][d], Q);
-                }
-                const float yr = P.x + Q.y, yi = P.y - Q.x;
-                yrow[(long)t * CSS_KP] = make_float2(yr, yi);
-                e_y += yr * yr + yi * yi;
-            }
+            const float yr = P.x + Q.y, yi = P.y - Q.x;      // zero for the padding bins (zero weights)
+            if (k < CSS_KP) yrow[(long)t * CSS_KP] = make_float2(yr, yi);
+            if (act) e_y += yr * yr + yi * yi;
         }
-    } else if (k < CSS_KP) {   // zero the bin padding of Y so later stages can read whole rows
-        for (int t = 0; t < T; ++t) yrow[(long)t * CSS_KP] = make_float2(0.f, 0.f);
     }
     e_y = warp_sum(e_y);
     if (lane == 0) energy[((b * 2 + mk) * gridDim.x + blockIdx.x) * 2] = e_y;
@@ -395,8 +415,7 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
         rc = css_check_launch("css_mvdr(solve)");
     }
     if (!rc) {
-        mvdr_apply_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 2), 0, st>>>(
-            (const float2*)spec, (const float2*)edge, frames, n_chunks, hop_frames, T, wv, (float2*)Y, energy);
+        mvdr_apply_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 2), 0, st>>>(maps, hop_frames, T, wv, (float2*)Y, energy);
         rc = css_check_launch("css_mvdr(apply)");
     }
     cudaFreeAsync(scratch, st);
