@@ -339,6 +339,7 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
                 v[i][0] = v[i][1] = make_float4(0, 0, 0, 0);
             }
         }
+        const float gw = -1.4426950408889634f * p.pw1_w1, gb = -1.4426950408889634f * p.pw1_b1;
         const float4 g0 = reinterpret_cast<const float4*>(p.ln_g)[lane], g1 = reinterpret_cast<const float4*>(p.ln_g)[lane + 32];
         const float4 b0 = reinterpret_cast<const float4*>(p.ln_b)[lane], b1 = reinterpret_cast<const float4*>(p.ln_b)[lane + 32];
 #pragma unroll
@@ -369,9 +370,14 @@ conv_module_kernel(const float* __restrict__ x, float* __restrict__ out, int T, 
                               (vv.z - mean) * rstd * g.z + bb.z, (vv.w - mean) * rstd * g.w + bb.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
+                    // a * sigmoid(gt) = a / (1 + 2^(-gt log2 e)): the gate's affine map carries the -log2 e, one MUFU.EX2 and one
+                    // MUFU.RCP (1 + 2^x is in [1, inf]: no range scaling needed, which div.approx would add)
                     const float a = y[e] * p.pw1_w0 + p.pw1_b0;
-                    const float gt = y[e] * p.pw1_w1 + p.pw1_b1;
-                    y[e] = __fdividef(a, 1.f + __expf(-gt));         // a * sigmoid(gt)
+                    const float ge = fmaf(y[e], gw, gb);
+                    float ex, rc;
+                    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(ex) : "f"(ge));
+                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rc) : "f"(1.f + ex));
+                    y[e] = a * rc;
                 }
                 urow[lane + 32 * hh] = make_float4(y[0], y[1], y[2], y[3]);
             }
