@@ -22,9 +22,6 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-# stdout carries the ONE JSON line: if the environment switches NCCL's log on (NCCL_DEBUG=VERSION / INFO), send it to stderr
-os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-
 METRIC = "audio_seconds_separated_per_second_7ch_conformer_css"
 UNIT = "xRT"
 SR = 16000
