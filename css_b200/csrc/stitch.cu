@@ -88,7 +88,7 @@ doa_merge_kernel(const float2* __restrict__ spec, long stride_d, long stride_chu
             // NaN when the radicand rounds < 0 (Q7): sqrt.approx keeps that, and its 1-2 ulp are below what the order of the
             // 9,150-term sums already differs from torch's by (IEEE sqrtf was six more instructions per angle and point)
             float l;
-            asm("sqrt.approx.f32 %0, %1;" : "=f"(l) : "f"(xpow - (re * re + im * im)));
+            asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(l) : "f"(xpow - (re * re + im * im)));   // .ftz: no denormal scaling sequence around the MUFU
             l = -l;
             acc[0][a] += b0 * l;
             acc[1][a] += b1 * l;
