@@ -395,7 +395,8 @@ features_planes_kernel(const float2* __restrict__ spec, long stride_d, long stri
                 const float n2 = w.x * w.x + w.y * w.y;
                 const bool odd = (a.y == 0.f && c.y == 0.f) || !(n2 >= 1e-30f && n2 <= 1e30f);
                 rare |= (odd ? 1u : 0u) << p;
-                float r = rsqrtf(n2);
+                float r;                                           // n2 is in [1e-30, 1e30] wherever the result is kept
+                asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(n2));
                 r = r * (1.5f - 0.5f * n2 * r * r);
                 const float2 u = odd ? make_float2(0.f, 0.f) : make_float2(w.x * r, w.y * r);
                 U[(p * T + t) * FP_BG + bin] = u;
