@@ -116,6 +116,24 @@ def test_separate_one_batch_matches_separate(cuda, case_a):
     assert rel_inf(masks, got["masks"][3:6]) < 1e-5 and rel_inf(mags, got["mags"][3:6]) < 1e-6
 
 
+def test_fused_front_end_equals_two_call_form(cuda, case_a):
+    """Separator with the fused front end (css_conformer_forward_spec: spectrum -> features -> MVN -> planes in front of the
+    network, the default) against the two-call form css_features + css_conformer_forward on the same recording: same
+    magnitudes bit for bit, masks to 2e-5 (the time statistics are summed in another order), same merge decisions."""
+    wav, _, pipe, got = case_a
+    sep = pipe.separator
+    assert sep.fused_front_end
+    sep.fused_front_end = False
+    try:
+        masks, mags = sep.separate(wav.to(cuda))
+        doa = sep.angle_merge_debug()
+    finally:
+        sep.fused_front_end = True
+    assert torch.equal(mags, got["mags"])
+    assert rel_inf(masks, got["masks"]) < 2e-5
+    assert doa is not None and doa[1].cpu().tolist() == got["doa"][1].cpu().tolist()
+
+
 def test_case_b_blstm_1ch(cuda, golden):
     from css_b200.pipeline import CssPipeline
 
