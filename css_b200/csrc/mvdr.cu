@@ -16,12 +16,6 @@
 #define MV_E (2 * MV_TRI)  // packed reals per covariance: (re, im) of (i, j >= i), row-major
 #define MV_BINS 32
 
-__device__ __forceinline__ float2 load_x(const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
-                                         long n_chunks, long b, int hop_frames, int d, int t, int k) {
-    return (t == 0) ? edge[((long)d * n_chunks + b) * CSS_KP + k]
-                    : spec[((long)d * frames + b * hop_frames + t - 1) * CSS_KP + k];
-}
-
 // ---- kernel 1: masked covariances.  grid (9 bin tiles, B); block (32 bins, 4 pair groups).
 // The outer product x_i conj(x_j) does not depend on the mask, so one thread forms it once and feeds the three masks'
 // accumulators (42 per thread); the 28 pairs (i, j >= i) are dealt to the four warps by rows {0}, {1,6}, {2,5}, {3,4}
@@ -84,9 +78,8 @@ __device__ __forceinline__ void sc_tma3(void* dst, const CUtensorMap* map, int c
 struct ScmMaps { CUtensorMap x5, x1, e1, w5; };
 
 template <int G>
-__device__ __forceinline__ void scm_group(const ScmMaps& maps, const float2* __restrict__ spec, const float2* __restrict__ edge, long frames,
-                                          long n_chunks, const float* __restrict__ stitched, long L, int hop_frames, int T,
-                                          float* __restrict__ scm, float* __restrict__ energy, float2* Xs, float* Ws, uint64_t* full) {
+__device__ __forceinline__ void scm_group(const ScmMaps& maps, int hop_frames, int T, float* __restrict__ scm,
+                                          float* __restrict__ energy, float2* Xs, float* Ws, uint64_t* full) {
     constexpr int R0 = G, R1 = (G == 0) ? -1 : MV_M - G;
     const long b = blockIdx.y;
     const int lane = threadIdx.x, tid = threadIdx.y * MV_BINS + threadIdx.x;
@@ -190,17 +183,15 @@ __device__ __forceinline__ void scm_group(const ScmMaps& maps, const float2* __r
 }
 
 __global__ void __launch_bounds__(128)
-mvdr_scm_kernel(const __grid_constant__ ScmMaps maps, const float2* __restrict__ spec, const float2* __restrict__ edge, long frames, long n_chunks,
-                const float* __restrict__ stitched, long L, int hop_frames, int T, float* __restrict__ scm,
-                float* __restrict__ energy) {
+mvdr_scm_kernel(const __grid_constant__ ScmMaps maps, int hop_frames, int T, float* __restrict__ scm, float* __restrict__ energy) {
     __shared__ __align__(128) float2 Xs[SC_ST * SC_F * SC_XF];
     __shared__ __align__(128) float Ws[SC_ST * SC_F * SC_WF];
     __shared__ __align__(8) uint64_t full[SC_ST];
     switch (threadIdx.y) {      // warp-uniform; every arm runs the same copy / barrier sequence
-        case 0: scm_group<0>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        case 1: scm_group<1>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        case 2: scm_group<2>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
-        default: scm_group<3>(maps, spec, edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 0: scm_group<0>(maps, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 1: scm_group<1>(maps, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        case 2: scm_group<2>(maps, hop_frames, T, scm, energy, Xs, Ws, full); break;
+        default: scm_group<3>(maps, hop_frames, T, scm, energy, Xs, Ws, full); break;
     }
 }
 
@@ -407,8 +398,7 @@ extern "C" int css_mvdr(const void* spec, const void* edge, long frames, long n_
             return rc0;
         }
     }
-    mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 4), 0, st>>>(
-        maps, (const float2*)spec, (const float2*)edge, frames, n_chunks, stitched, L, hop_frames, T, scm, energy);
+    mvdr_scm_kernel<<<dim3(nblk, (unsigned)n_chunks), dim3(MV_BINS, 4), 0, st>>>(maps, hop_frames, T, scm, energy);
     int rc = css_check_launch("css_mvdr(scm)");
     if (!rc) {
         mvdr_solve_kernel<<<dim3(nblk, (unsigned)n_chunks, 2), 256, 0, st>>>(scm, wv);
