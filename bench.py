@@ -355,8 +355,13 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    # One CUDA graph per step (CssPipeline.capture: the ~800 launches of a session replayed by one call): issuing them one by
+    # one takes the host ~18 ms per 26 ms step, so a host that is descheduled for a moment (seen on the GPU boxes: 0.5 s stalls)
+    # starves the GPU and halves the number.  CSS_B200_GRAPHS=0: eager launches.
+    graph = None
+
     def step_resident():
-        return pipe(wav_dev)
+        return graph.replay() if graph is not None else pipe(wav_dev)
 
     def step_e2e():
         out = pipe(wav_host)                       # H2D of the session inside the public call
@@ -366,13 +371,23 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step_resident()
     step_e2e()
+    if os.environ.get("CSS_B200_GRAPHS", "1") != "0":
+        try:
+            graph = pipe.capture(wav_dev)
+            for _ in range(3):
+                step_resident()
+        except Exception as e:      # capture is an optimisation of the launch path, not of the kernels: fall back to eager launches
+            print(f"[bench] CUDA graph capture failed, eager launches: {e!r}", file=sys.stderr, flush=True)
+            graph = None
+            torch.cuda.synchronize()
     barrier()
 
     # ---- timed region 1: inputs resident in HBM (value) ----
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    lib.css_profile_enable(1)
+    if graph is None:
+        lib.css_profile_enable(1)
     nv.launch_count(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -387,6 +402,20 @@ def run_b200(args):
     import ctypes
     ncat = 11
     ms_c, work_c, cnt_c = (ctypes.c_double * ncat)(), (ctypes.c_double * ncat)(), (ctypes.c_long * ncat)()
+    ms_prof_total = ms_total
+    if graph is not None:
+        # per-kernel CUDA events cannot bracket the kernels of a replayed graph: the same K steps once more, launched eagerly
+        # with the events around every instrumented launch (roofline, hbm_kernels, share_of_step, gpu_launches come from here)
+        lib.css_profile_enable(1)
+        nv.launch_count(reset=True)
+        barrier()
+        e0.record()
+        for _ in range(args.steps):
+            pipe(wav_dev)
+        e1.record()
+        barrier()
+        ms_prof_total = max_over_ranks(e0.elapsed_time(e1))
+        launches = nv.launch_count()
     nv.check(lib.css_profile_collect(ms_c, work_c, cnt_c, ncat), "css_profile_collect")
     lib.css_profile_enable(0)
 
@@ -454,7 +483,7 @@ def run_b200(args):
     achieved = g_flop / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
     names = ("gemm", "attention", "conv_module", "layernorm", "lstm_step", "stft", "features_mvn", "doa_merge", "stitch", "mvdr",
              "istft_peak")
-    shares = {names[i]: round(ms_c[i] / ms_total, 4) for i in range(ncat) if cnt_c[i]}
+    shares = {names[i]: round(ms_c[i] / ms_prof_total, 4) for i in range(ncat) if cnt_c[i]}
     # HBM-bound kernels (north_star: STFT, mask, MVDR, stitch): algorithmic bytes / CUDA-event time vs measured copy peak
     hbm = {names[i]: {"achieved_GBps": round(work_c[i] / (ms_c[i] * 1e-3) / 1e9, 1), "frac": round(work_c[i] / (ms_c[i] * 1e-3) / 1e9 / pk["hbm"], 4),
                       "ms_per_step": round(ms_c[i] / args.steps, 4), "algorithmic_MB_per_step": round(work_c[i] / args.steps / 1e6, 1)}
@@ -469,7 +498,10 @@ def run_b200(args):
             "frac": achieved / pk["tensor"], "peak_source": f"{pk['src']} bf16 sustained (kernel timed inside a long step)",
             "traffic": traffic, "traffic_note": "ncu dram bytes per launch, mean over the six GEMMs of one block (profiles/r2_traffic.json)",
             "launches": int(g_n), "avg_launch_ms": g_ms / max(1, g_n),
-            "algorithmic_flop_per_step": g_flop / args.steps, "share_of_step": shares}
+            "algorithmic_flop_per_step": g_flop / args.steps, "share_of_step": shares,
+            "measured_in": ("the same K steps launched eagerly right after the timed region, CUDA events around every instrumented "
+                            f"launch ({ms_prof_total / args.steps:.3f} ms per step there); the timed region replays one CUDA graph per step"
+                            if graph is not None else "the timed region (eager launches)")}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {0: "f32", 1: "bf16x3->f32", 2: "bf16"}[gemm_mode], "data": "synthetic",
@@ -477,7 +509,9 @@ def run_b200(args):
                                    f"7-mic LibriCSS-shaped {audio_s:g} s session per GPU per step",
                        "session_seconds": audio_s, "chunks_per_session": B, "blocks": args.blocks, "sessions_per_step": world,
                        "l2": f"inputs larger than L2 (waveform {wav_dev.numel() * 4 / 1e6:.0f} MB, features {B * 150 * 1856 * 4 / 1e6:.0f} MB vs 126 MB L2)",
-                       "parallelism": f"dp{world} (independent sessions, no data-path collective)", "gemm_mode": gemm_mode},
+                       "parallelism": f"dp{world} (independent sessions, no data-path collective)", "gemm_mode": gemm_mode,
+                       "launch": (f"one CUDA graph replay per step ({int(launches) // max(1, args.steps)} kernels captured once, CssPipeline.capture); "
+                                  "e2e: CssPipeline.run_many over two captured graphs" if graph is not None else "eager launches")},
             "clocks": clocks, "roofline": roof, "hbm_kernels": {"peak_GBps": pk["hbm"], "kernels": hbm},
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e2e / args.steps, "ms_per_step_runs": [round(t / args.steps, 3) for t in e2e_runs],
                     "h2d_bytes_per_step": wav_host.numel() * 4, "d2h_bytes_per_step": out_host.numel() * 4},

@@ -6,6 +6,8 @@
 STFT is computed once and shared by the feature kernel and the MVDR kernel, the permutation bits and
 the stitched masks stay in HBM, and only the two separated waveforms are read back.
 """
+import os
+
 import torch
 import yaml
 
@@ -36,6 +38,17 @@ CONFIG_1CH = {
 def load_config(path):
     with open(path) as f:
         return yaml.load(f, Loader=yaml.FullLoader)
+
+
+class GraphedPipeline:
+    """One captured recording shape of a CssPipeline (``CssPipeline.capture``)."""
+
+    def __init__(self, graph, inp, out):
+        self.graph, self.input, self.output = graph, inp, out
+
+    def replay(self):
+        self.graph.replay()
+        return self.output
 
 
 class CssPipeline:
@@ -72,14 +85,96 @@ class CssPipeline:
                     "sims": self.stitcher.last_sims, "doa": self.separator.angle_merge_debug()}
         return out if beamform else stitched
 
-    def run_many(self, recordings, outputs=None):
+    def capture(self, wav, pool=None):
+        """Capture the whole path for recordings of ``wav``'s shape into ONE CUDA graph (about 800 kernel launches for a
+        10-minute 7-channel session).  ``wav`` (device, (D, T) fp32) becomes the graph's static input buffer: write the next
+        recording into ``g.input`` and call ``g.replay()``; the result is ``g.output`` (static as well: consume it, or copy
+        it out, before the next replay).  One replay costs the host a few microseconds instead of the ~18 ms it takes to
+        issue the launches one by one, which is within 1.5x of the GPU time: a host that is descheduled for a moment no
+        longer starves the GPU.  Same kernels, same bits as the eager call (tests/test_gpu_pipeline.py)."""
+        if not (isinstance(wav, torch.Tensor) and wav.is_cuda and wav.dtype == torch.float32 and wav.dim() == 2):
+            raise RuntimeError("capture needs a (D, T) fp32 CUDA tensor as the static input buffer")
+        self(wav)                                   # eager once: lazy set-up (weight planes, workspaces, placement plans)
+        torch.cuda.synchronize(wav.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, pool=pool):
+            out = self(wav)
+        return GraphedPipeline(g, wav, out)
+
+    def _graph_slots(self, shape):
+        """Two captured graphs (one per staging buffer) for recordings of this shape.  Each has its own memory pool: with a
+        shared pool one graph's intermediates may sit where the other's OUTPUT sits, and a replay could then overwrite a result
+        whose device-to-host copy is still in flight."""
+        if getattr(self, "_graphs", None) is None:
+            self._graphs = {}
+        if shape not in self._graphs:
+            a = self.capture(torch.zeros(shape, dtype=torch.float32, device=self.device))
+            b = self.capture(torch.zeros(shape, dtype=torch.float32, device=self.device))
+            self._graphs[shape] = (a, b)
+        return self._graphs[shape]
+
+    def run_many(self, recordings, outputs=None, graphs=None):
         """Separate a list of pinned host recordings (D, T_i) back to back, as the session loop of
         scripts/python/separate_libricss.py:65-82 does, with the transfers double-buffered around the compute: the H2D
         copy of recording i+1 and the D2H copy of result i-1 run on their own streams while recording i is separated.
 
         outputs: optional list of pinned host tensors (2, T_i) to receive the results; returned (allocated if None).
+        graphs: replay captured CUDA graphs (``capture``) instead of issuing the launches when all recordings have one
+        shape and are multi-channel; default on (``CSS_B200_GRAPHS=0`` or ``graphs=False``: eager).
         The call returns when every result has landed on the host.
         """
+        if graphs is None:
+            graphs = os.environ.get("CSS_B200_GRAPHS", "1") != "0"
+        if graphs and len(recordings) > 1 and recordings[0].shape[0] > 1 and all(r.shape == recordings[0].shape for r in recordings):
+            return self._run_many_graphed(recordings, outputs)
+        return self._run_many_eager(recordings, outputs)
+
+    def _run_many_graphed(self, recordings, outputs):
+        dev = self.device
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_h2d", None) is None:
+            self._h2d, self._d2h = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+        n = len(recordings)
+        if outputs is None:
+            outputs = [torch.empty(2, r.shape[1], dtype=torch.float32).pin_memory() for r in recordings]
+        slots = self._graph_slots(tuple(recordings[0].shape))
+        staged, freed, copied = [None] * n, [None, None], [None, None]
+
+        def stage(i):
+            slot = i % 2
+            with torch.cuda.stream(self._h2d):
+                if freed[slot] is not None:
+                    self._h2d.wait_event(freed[slot])          # the previous recording in this input buffer has been separated
+                slots[slot].input.copy_(recordings[i], non_blocking=True)
+                staged[i] = torch.cuda.Event()
+                staged[i].record(self._h2d)
+
+        self._h2d.wait_stream(main)
+        stage(0)
+        done = []
+        for i in range(n):
+            slot = i % 2
+            if i + 1 < n:
+                stage(i + 1)
+            main.wait_event(staged[i])
+            if copied[slot] is not None:
+                main.wait_event(copied[slot])                  # the previous result in this output buffer has left
+            slots[slot].replay()
+            ev = torch.cuda.Event()
+            ev.record(main)
+            freed[slot] = ev
+            with torch.cuda.stream(self._d2h):
+                self._d2h.wait_event(ev)
+                outputs[i].copy_(slots[slot].output, non_blocking=True)
+                fin = torch.cuda.Event()
+                fin.record(self._d2h)
+                copied[slot] = fin
+                done.append(fin)
+        for fin in done:
+            fin.synchronize()
+        return outputs
+
+    def _run_many_eager(self, recordings, outputs=None):
         dev = self.device
         main = torch.cuda.current_stream(dev)
         if getattr(self, "_h2d", None) is None:

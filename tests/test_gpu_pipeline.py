@@ -134,6 +134,24 @@ def test_fused_front_end_equals_two_call_form(cuda, case_a):
     assert doa is not None and doa[1].cpu().tolist() == got["doa"][1].cpu().tolist()
 
 
+def test_cuda_graph_replay_and_graphed_run_many_equal_eager(cuda, case_a):
+    """CssPipeline.capture: one CUDA graph for the whole path, bit-equal to the eager call, also after the static input has
+    been overwritten with another recording; run_many over captured graphs (the default) equals run_many issued eagerly."""
+    wav, _, pipe, got = case_a
+    x = wav.to(cuda)
+    g = pipe.capture(x.clone())
+    assert torch.equal(g.replay(), got["wavs"])
+    other = torch.roll(x, 4321, dims=1) * 0.7
+    g.input.copy_(other)
+    assert torch.equal(g.replay(), pipe(other))
+    recs = [wav.pin_memory(), (torch.roll(wav, 999, dims=1) * 0.5).pin_memory(), wav.flip(0).contiguous().pin_memory()]
+    eager = [o.clone() for o in pipe.run_many(recs, graphs=False)]
+    graphed = pipe.run_many(recs, graphs=True)
+    for a_, b_ in zip(eager, graphed):
+        assert torch.equal(a_, b_)
+    assert torch.equal(eager[0].to(cuda), got["wavs"])
+
+
 def test_case_b_blstm_1ch(cuda, golden):
     from css_b200.pipeline import CssPipeline
 
