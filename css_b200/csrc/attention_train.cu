@@ -48,13 +48,16 @@ __device__ __forceinline__ void mma_tf32(float* c, const uint32_t* a, uint32_t b
 template <bool TA, bool TB, bool SPLIT>
 __global__ void __launch_bounds__(128)
 bgemm_kernel(BMat A, BMat B, BOut C, int M, int N, int K, int Nb, float alpha, int acc_mode, int ksplit) {
-    __shared__ float As[BT][PITCH];
-    __shared__ float Bs[BT][PITCH];
+    __shared__ __align__(16) float As[BT][PITCH];
+    __shared__ __align__(16) float Bs[BT][PITCH];
     const int split = blockIdx.z % ksplit, b = blockIdx.z / ksplit;
     const int h = b / Nb, n = b - h * Nb;
     const float* Ap = A.p + h * A.s_h + n * A.s_n;
     const float* Bp = B.p + h * B.s_h + n * B.s_n;
     float* Cp = C.p + h * C.s_h + n * C.s_n;
+    // 16-byte loads need the batch's base and every row start on a 16-byte boundary (uniform over the block)
+    const bool vecA = ((reinterpret_cast<uintptr_t>(Ap) & 15) == 0) && (A.ld & 3) == 0;
+    const bool vecB = ((reinterpret_cast<uintptr_t>(Bp) & 15) == 0) && (B.ld & 3) == 0;
     const int m0 = blockIdx.y * BT, n0 = blockIdx.x * BT;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int g = lane >> 2, q = lane & 3;
@@ -70,22 +73,68 @@ bgemm_kernel(BMat A, BMat B, BOut C, int M, int N, int K, int Nb, float alpha, i
     for (int kt = kt0; kt < kt1; ++kt) {
         const int k0 = kt * BK;
         __syncthreads();
+        // operands into shared memory, four elements per thread and step: one 16-byte load where the operand's pitch and the tile
+        // allow it (vecA / vecB), element loads otherwise; without the split the values are rounded to TF32 here, once, instead of
+        // at every fragment load (the kernel issued 13 instructions per MMA)
 #pragma unroll
-        for (int i = 0; i < (BT * BK) / 128; ++i) {
+        for (int i = 0; i < (BT * BK) / (128 * 4); ++i) {
             const int idx = threadIdx.x + 128 * i;
+            float va[4], vb[4];
             if (!TA) {
-                const int r = idx >> 5, c = idx & 31;
-                As[r][c] = (m0 + r < M && k0 + c < K) ? Ap[(long)(m0 + r) * A.ld + k0 + c] : 0.f;
+                const int r = idx >> 3, c = (idx & 7) * 4;
+                const float* src = Ap + (long)(m0 + r) * A.ld + k0 + c;
+                if (vecA && m0 + r < M && k0 + c + 3 < K) {
+                    const float4 t = *reinterpret_cast<const float4*>(src);
+                    va[0] = t.x; va[1] = t.y; va[2] = t.z; va[3] = t.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) va[e] = (m0 + r < M && k0 + c + e < K) ? src[e] : 0.f;
+                }
+                if (!SPLIT) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) va[e] = __uint_as_float(to_tf32(va[e]));
+                }
+                *reinterpret_cast<float4*>(&As[r][c]) = make_float4(va[0], va[1], va[2], va[3]);
             } else {
-                const int kk = idx >> 6, r = idx & 63;
-                As[r][kk] = (m0 + r < M && k0 + kk < K) ? Ap[(long)(k0 + kk) * A.ld + m0 + r] : 0.f;
+                const int kk = idx >> 4, r = (idx & 15) * 4;
+                const float* src = Ap + (long)(k0 + kk) * A.ld + m0 + r;
+                if (vecA && k0 + kk < K && m0 + r + 3 < M) {
+                    const float4 t = *reinterpret_cast<const float4*>(src);
+                    va[0] = t.x; va[1] = t.y; va[2] = t.z; va[3] = t.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) va[e] = (k0 + kk < K && m0 + r + e < M) ? src[e] : 0.f;
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) As[r + e][kk] = SPLIT ? va[e] : __uint_as_float(to_tf32(va[e]));
             }
             if (!TB) {
-                const int r = idx >> 5, c = idx & 31;
-                Bs[r][c] = (n0 + r < N && k0 + c < K) ? Bp[(long)(n0 + r) * B.ld + k0 + c] : 0.f;
+                const int r = idx >> 3, c = (idx & 7) * 4;
+                const float* src = Bp + (long)(n0 + r) * B.ld + k0 + c;
+                if (vecB && n0 + r < N && k0 + c + 3 < K) {
+                    const float4 t = *reinterpret_cast<const float4*>(src);
+                    vb[0] = t.x; vb[1] = t.y; vb[2] = t.z; vb[3] = t.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) vb[e] = (n0 + r < N && k0 + c + e < K) ? src[e] : 0.f;
+                }
+                if (!SPLIT) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) vb[e] = __uint_as_float(to_tf32(vb[e]));
+                }
+                *reinterpret_cast<float4*>(&Bs[r][c]) = make_float4(vb[0], vb[1], vb[2], vb[3]);
             } else {
-                const int kk = idx >> 6, r = idx & 63;
-                Bs[r][kk] = (n0 + r < N && k0 + kk < K) ? Bp[(long)(k0 + kk) * B.ld + n0 + r] : 0.f;
+                const int kk = idx >> 4, r = (idx & 15) * 4;
+                const float* src = Bp + (long)(k0 + kk) * B.ld + n0 + r;
+                if (vecB && k0 + kk < K && n0 + r + 3 < N) {
+                    const float4 t = *reinterpret_cast<const float4*>(src);
+                    vb[0] = t.x; vb[1] = t.y; vb[2] = t.z; vb[3] = t.w;
+                } else {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) vb[e] = (k0 + kk < K && n0 + r + e < N) ? src[e] : 0.f;
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) Bs[r + e][kk] = SPLIT ? vb[e] : __uint_as_float(to_tf32(vb[e]));
             }
         }
         __syncthreads();
@@ -98,7 +147,7 @@ bgemm_kernel(BMat A, BMat B, BOut C, int M, int N, int K, int Nb, float alpha, i
                                     As[wm + 16 * i + g][8 * ks + q + 4], As[wm + 16 * i + g + 8][8 * ks + q + 4]};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
-                    ah[i][e] = to_tf32(v[e]);
+                    ah[i][e] = SPLIT ? to_tf32(v[e]) : __float_as_uint(v[e]);
                     if (SPLIT) al[i][e] = to_tf32(v[e] - __uint_as_float(ah[i][e]));
                 }
             }
@@ -107,7 +156,7 @@ bgemm_kernel(BMat A, BMat B, BOut C, int M, int N, int K, int Nb, float alpha, i
                 const float v[2] = {Bs[wn + 8 * j + g][8 * ks + q], Bs[wn + 8 * j + g][8 * ks + q + 4]};
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
-                    bh[j][e] = to_tf32(v[e]);
+                    bh[j][e] = SPLIT ? to_tf32(v[e]) : __float_as_uint(v[e]);
                     if (SPLIT) bl[j][e] = to_tf32(v[e] - __uint_as_float(bh[j][e]));
                 }
             }
