@@ -125,9 +125,25 @@ class CssPipeline:
         """
         if graphs is None:
             graphs = os.environ.get("CSS_B200_GRAPHS", "1") != "0"
-        if graphs and len(recordings) > 1 and recordings[0].shape[0] > 1 and all(r.shape == recordings[0].shape for r in recordings):
+        # a captured graph keeps its intermediates (about 6.6 GB per 10-minute 7-channel session, two graphs): recordings beyond
+        # GRAPH_MAX_SECONDS are issued eagerly, and so is everything if a capture fails (out of memory, ...)
+        if graphs and len(recordings) > 1 and recordings[0].shape[0] > 1 and all(r.shape == recordings[0].shape for r in recordings) \
+                and recordings[0].shape[1] <= self.GRAPH_MAX_SECONDS * self.sr:
+            try:
+                self._graph_slots(tuple(recordings[0].shape))
+            except Exception:
+                self.release_graphs()
+                torch.cuda.synchronize(self.device)
+                return self._run_many_eager(recordings, outputs)
             return self._run_many_graphed(recordings, outputs)
         return self._run_many_eager(recordings, outputs)
+
+    GRAPH_MAX_SECONDS = 1500
+
+    def release_graphs(self):
+        """Drop the captured graphs (and the memory their pools hold)."""
+        self._graphs = None
+        torch.cuda.empty_cache()
 
     def _run_many_graphed(self, recordings, outputs):
         dev = self.device
