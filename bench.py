@@ -508,7 +508,7 @@ def run_b200(args):
             "config": {"workload": "configs[2]: 7-ch Conformer (conf/config_7ch.yaml) mask estimation + MVDR on a synthetic "
                                    f"7-mic LibriCSS-shaped {audio_s:g} s session per GPU per step",
                        "session_seconds": audio_s, "chunks_per_session": B, "blocks": args.blocks, "sessions_per_step": world,
-                       "l2": f"inputs larger than L2 (waveform {wav_dev.numel() * 4 / 1e6:.0f} MB, features {B * 150 * 1856 * 4 / 1e6:.0f} MB vs 126 MB L2)",
+                       "l2": f"inputs larger than L2 (waveform {wav_dev.numel() * 4 / 1e6:.0f} MB, spectrum {7 * (50 * (B - 1) + 150) * 264 * 8 / 1e6:.0f} MB, network input planes {B * 150 * 1856 * 4 / 1e6:.0f} MB vs 126 MB L2)",
                        "parallelism": f"dp{world} (independent sessions, no data-path collective)", "gemm_mode": gemm_mode,
                        "launch": (f"one CUDA graph replay per step ({int(launches) // max(1, args.steps)} kernels captured once, CssPipeline.capture); "
                                   "e2e: CssPipeline.run_many over two captured graphs" if graph is not None else "eager launches")},
